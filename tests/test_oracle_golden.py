@@ -1,0 +1,71 @@
+"""Oracle (oracle/oracle.py over oracle/pvv_oracle.c) against the fixtures the
+reference's own Python wrapper produced (tests/golden/make_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+from pvnet_b200 import synth
+
+RTOL = 1e-4  # BASELINE.json north_star: keypoints/means/covariances within 1e-4 relative
+
+
+def _cat_inputs(z):
+    mask, kp = synth.cat_fixture()
+    ys, xs = np.nonzero(mask)
+    vertex = np.zeros((1, 480, 640, 9, 2), np.float32)
+    vertex[0][ys, xs] = z["fg_vertex"]
+    return mask[None], vertex, kp
+
+
+@pytest.mark.parametrize("name", ["cat_exact", "cat_noisy"])
+def test_v3_cat(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, f"v3_{name}.npz"))
+    mask, vertex, kp = _cat_inputs(z)
+    out, dbg = orc.ransac_voting_layer_v3(mask, vertex, int(z["hn"]), float(z["thresh"]), min_num=int(z["min_num"]),
+                                          max_num=int(z["max_num"]), idxs=z["idxs"], return_debug=True)
+    assert np.array_equal(dbg[0]["counts"], z["counts"][0])          # integers: bit-exact
+    assert dbg[0]["coords"].shape[0] == 2289
+    np.testing.assert_allclose(out, z["out"], rtol=RTOL, atol=0)
+    if name == "cat_exact":   # exact field: every keypoint recovered, all pixels inliers
+        assert np.abs(out[0] - kp).max() < 1e-2
+        assert (dbg[0]["win_counts"] == 2289).all()
+
+
+def test_small_batch_v3_and_cov(golden_dir):
+    z = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    mask, vertex = z["mask"].astype(np.int64), z["vertex"]
+    hn, min_num, max_num = (int(v) for v in z["v3_args"])
+    out, dbg = orc.ransac_voting_layer_v3(mask, vertex, hn, 0.99, min_num=min_num, max_num=max_num,
+                                          idxs=z["v3_idxs"], selection=z["v3_sel"], return_debug=True)
+    assert dbg[1] is None and np.all(out[1] == 0)                    # skipped image -> zeros (:537-541)
+    for bi in (0, 2, 3):
+        assert np.array_equal(dbg[bi]["counts"], z["v3_counts"][bi])
+    assert dbg[2]["coords"].shape[0] < 1996                          # subsampled (:543-546)
+    np.testing.assert_allclose(out, z["v3_out"], rtol=RTOL, atol=0)
+
+    rh, mh, cmin, cmax = (int(v) for v in z["cov_args"])
+    mean, cov = orc.estimate_voting_distribution_with_mean(mask, vertex, z["cov_mean"], rh, mh, inlier_thresh=0.99,
+                                                           min_num=cmin, max_num=cmax, idxs=z["cov_idxs"],
+                                                           selection=z["cov_sel"])
+    np.testing.assert_allclose(cov, z["cov"], rtol=RTOL, atol=1e-6)
+    assert np.array_equal(mean, z["cov_mean"])
+
+
+def test_kernels_edge_cases():
+    # degenerate pair (parallel lines) leaves the zero-initialised hypothesis (kernel.cu:42-43,75)
+    direct = np.array([[[1.0, 0.0]], [[1.0, 0.0]], [[0.0, 1.0]]], np.float32)
+    coords = np.array([[0, 0], [5, 3], [2, 7]], np.float32)
+    hyp = orc.generate_hypothesis(direct, coords, np.array([[[0, 1]], [[0, 2]], [[1, 1]]], np.int32))
+    assert np.all(hyp[0] == 0) and np.all(hyp[2] == 0)
+    np.testing.assert_allclose(hyp[1, 0], [2.0, 0.0], atol=1e-6)     # y=0 line meets x=2 line
+    # zero direction or hypothesis on the pixel: skipped (kernel.cu:121)
+    L = orc.lib()
+    assert L.orc_inlier_test(0, 0, 1, 1, 5, 5, 0.5) == 0
+    assert L.orc_inlier_test(1, 0, 1, 1, 1, 1, 0.5) == 0
+    assert L.orc_inlier_test(1, 0, 1, 1, 5, 1, 0.99) == 1
+    assert L.orc_inlier_test(1, 0, 1, 1, -5, 1, -2.0) == 1           # any finite cosine beats thresh -2
+    # empty pixel set
+    assert orc.vote_counts(np.zeros((0, 2, 2), np.float32), np.zeros((0, 2), np.float32),
+                           np.ones((3, 2, 2), np.float32), 0.9).sum() == 0
