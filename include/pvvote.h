@@ -1,0 +1,171 @@
+/*
+ * pvvote.h -- C ABI of the B200-native RANSAC keypoint-voting library (libpvvote.so).
+ *
+ * This is the drop-in boundary for PVNet's voting hot path.  It replaces what the
+ * reference binds through pybind11 in
+ *     lib/ransac_voting_gpu_layer/src/ransac_voting.cpp:102-107   (module `ransac_voting`)
+ * and the per-image Python orchestration around it in
+ *     lib/ransac_voting_gpu_layer/ransac_voting_gpu.py:520-604    (ransac_voting_layer_v3)
+ *     lib/ransac_voting_gpu_layer/ransac_voting_gpu.py:333-406    (estimate_voting_distribution_with_mean)
+ * (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / ATen types cross this boundary;
+ *   - every entry point returns 0 (PVV_OK) or a negative pvv_status; nothing exits the process or throws
+ *     (the reference's gpuErrchk calls exit(), src/cuda_common.h:19-26);
+ *   - all work is enqueued on the caller's stream (`stream` is a cudaStream_t passed as void*), the current
+ *     device is the caller's; no host synchronisation happens inside the device-buffer entry points;
+ *   - the caller owns every buffer, including the scratch `workspace` sized by pvv_workspace_bytes();
+ *   - re-entrant and thread-safe: no global mutable state (DataParallel calls the layer from one thread
+ *     per GPU, tools/train_linemod.py:222-223).
+ */
+#ifndef PVVOTE_H_
+#define PVVOTE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum pvv_status {
+    PVV_OK = 0,
+    PVV_ERR_INVALID = -1,     /* bad argument (null pointer, non-positive size, unsupported dtype, thresh range) */
+    PVV_ERR_WORKSPACE = -2,   /* workspace too small for pvv_workspace_bytes() of this job */
+    PVV_ERR_CUDA = -3,        /* a CUDA runtime call failed; pvv_last_cuda_error() has the code */
+    PVV_ERR_UNSUPPORTED = -4  /* shape outside compiled limits (vn > 64, w or h > 65535) */
+} pvv_status;
+
+/* mask element types accepted (the reference takes whatever `.byte()` / `== 1` accept) */
+enum { PVV_MASK_U8 = 0, PVV_MASK_I32 = 1, PVV_MASK_I64 = 2, PVV_MASK_F32 = 3 };
+
+/* which foreground rule to apply */
+enum {
+    PVV_FG_BYTE = 0, /* ransac_voting_layer_v3:   fg = (uint8)mask != 0, count = sum of byte values (:533-534) */
+    PVV_FG_EQ1 = 1   /* estimate_voting_distribution_with_mean: fg = (mask == 1)                     (:339-340) */
+};
+
+/* bit flags written to pvv_debug.status / workspace status word (device side, sticky) */
+enum {
+    PVV_FLAG_POOL_OVERFLOW = 1 /* compacted pixels exceeded pool capacity: affected images were zeroed */
+};
+
+/*
+ * One voting job over a batch.  Layouts are the reference's:
+ *   mask    [b,h,w]      any PVV_MASK_* type, strides in ELEMENTS (mask_strides[3])
+ *   vertex  [b,h,w,vn,2] float32, strides in ELEMENTS (vertex_strides[5]); the network emits this as a
+ *           permuted view of [b,2+2vn,h,w] (tools/train_linemod.py:118-120) -- it is consumed in place.
+ * Random draws are either injected (parity runs) or produced by the library's counter-based generator
+ * keyed by (seed, image_id_base + image, hypothesis, keypoint):
+ *   idxs      int32 [b,hn_total,vn,2], each in [0,tn_image)  or NULL
+ *   selection float32 [b,h,w] uniforms in [0,1) used only for images with fg > max_num, or NULL
+ */
+typedef struct pvv_job {
+    const void *mask;
+    int32_t mask_dtype;
+    int32_t fg_rule;
+    int64_t mask_strides[3];
+    const float *vertex;
+    int64_t vertex_strides[5];
+    int32_t b, h, w, vn;
+    int32_t hn_total;         /* hypotheses per image and keypoint (v3: round_hyp_num; cov: rounds*round_hyp_num) */
+    float inlier_thresh;
+    int32_t min_num, max_num;
+    const int32_t *idxs;      /* device, optional */
+    const float *selection;   /* device, optional */
+    uint64_t seed;
+    int64_t image_id_base;    /* global id of image 0 of this shard (keeps draws shard-invariant) */
+    int64_t pool_capacity;    /* max compacted pixels over the whole batch; 0 = library default bound */
+    void *workspace;
+    size_t workspace_bytes;
+    void *stream;
+} pvv_job;
+
+/* Optional device-side introspection buffers (any may be NULL); used by the parity tests. */
+typedef struct pvv_debug {
+    int32_t *tn;          /* [b]   compacted pixel count per image (0 for skipped images) */
+    int64_t *img_off;     /* [b]   offset of each image's pixels in the pool */
+    uint32_t *pix_xy;     /* [pool] x | y<<16 in row-major compaction order */
+    float *pix_dir;       /* [vn][pool][2] raw direction vectors */
+    int32_t *idxs;        /* [b,hn_total,vn,2] the pixel-pair indices actually used */
+    float *hyp;           /* [b,hn_total,vn,2] hypotheses, reference layout */
+    int32_t *counts;      /* [b,hn_total,vn]   inlier counts, reference layout */
+    int32_t *win_idx;     /* [b,vn] argmax (first maximal index) */
+    int32_t *win_count;   /* [b,vn] */
+    float *win_pts;       /* [b,vn,2] winning hypotheses before refinement */
+    uint8_t *win_inlier;  /* [vn][pool] winner re-vote inlier flags */
+    double *normal_eq;    /* [b,vn,5] ATA00, ATA01, ATA11, ATb0, ATb1 */
+    int32_t *status;      /* [1] PVV_FLAG_* */
+    int64_t pool_capacity; /* capacity of the pool-sized arrays above, in pixels */
+    int32_t force_exact;  /* 1: disable the guard-banded fast filter, evaluate every test exactly */
+    uint64_t *amb_count;  /* [1] number of tests that took the exact path */
+} pvv_debug;
+
+/* Scratch size for a job (depends on b,h,w,vn,hn_total,max_num,pool_capacity only). */
+size_t pvv_workspace_bytes(const pvv_job *job);
+/* Default pool capacity the library would pick for this job (pixels). */
+int64_t pvv_default_pool_capacity(const pvv_job *job);
+
+/*
+ * ransac_voting_layer_v3 (ransac_voting_gpu.py:520-604): out_kp [b,vn,2] float32 (device).
+ * `confidence` and `max_iter` are accepted for signature fidelity; in the reference every round re-votes the
+ * same hypotheses (idxs drawn once at :553), so the result is a function of the first round only.
+ */
+int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, const pvv_debug *dbg);
+
+/*
+ * estimate_voting_distribution_with_mean (ransac_voting_gpu.py:333-406):
+ * mean [b,vn,2] float32 in, out_cov [b,vn,2,2] float32 out (device). job->hn_total = ceil(min_hyp/round_hyp)*round_hyp,
+ * job->fg_rule must be PVV_FG_EQ1.
+ */
+int pvv_cov(const pvv_job *job, const float *mean, float *out_cov, const pvv_debug *dbg);
+
+/*
+ * Host-buffer variants (the reference-facing call with HOST memory): mask / vertex / idxs / selection / mean are host
+ * pointers, outputs are host pointers; copies are issued on job->stream and the call returns after the result has
+ * landed (it synchronises the stream).  `workspace` is still device memory, sized by pvv_workspace_bytes_host().
+ * Pinned (cudaHostAlloc / cudaHostRegister) inputs are read in place over PCIe: only the mask and the foreground
+ * vertex vectors cross the bus.  Pageable inputs are staged with a full copy.
+ * h2d_bytes / d2h_bytes (optional) receive the bytes that crossed the bus.
+ */
+size_t pvv_workspace_bytes_host(const pvv_job *job);
+int pvv_v3_host(const pvv_job *job, float confidence, int max_iter, float *out_kp_host,
+                int64_t *h2d_bytes, int64_t *d2h_bytes);
+int pvv_cov_host(const pvv_job *job, const float *mean_host, float *out_cov_host,
+                 int64_t *h2d_bytes, int64_t *d2h_bytes);
+
+/*
+ * Primitive-compatible entry points with the reference's AoS layouts, so that the other wrappers of
+ * ransac_voting_gpu.py (v1, v2, v4-v6, generate_hypothesis at :989) keep working unchanged:
+ *   generate_hypothesis   (src/ransac_voting.cpp:20-31 -> ransac_voting_kernel.cu:11-86)
+ *   voting_for_hypothesis (src/ransac_voting.cpp:41-55 -> ransac_voting_kernel.cu:88-167)
+ * direct [tn,vn,2] f32, coords [tn,2] f32 (x,y), idxs [hn,vn,2] i32, hyp [hn,vn,2] f32 (written, zero for
+ * degenerate pairs), inliers [hn,vn,tn] u8 (in place: only 1s are written, caller pre-zeroes).
+ */
+int pvv_generate_hypothesis(const float *direct, const float *coords, const int32_t *idxs, int tn, int vn, int hn,
+                            float *hyp, void *stream);
+int pvv_voting_for_hypothesis(const float *direct, const float *coords, const float *hyp, uint8_t *inliers, int tn,
+                              int vn, int hn, float inlier_thresh, void *stream);
+/* fused form of voting_for_hypothesis + torch.sum(inliers, 2): counts int32 [hn,vn], never materialises the matrix */
+int pvv_vote_counts(const float *direct, const float *coords, const float *hyp, int tn, int vn, int hn,
+                    float inlier_thresh, int32_t *counts, void *stream);
+
+/* The library's draw streams, materialised (for feeding the oracle / the reference wrapper the same draws). */
+int pvv_make_idxs(uint64_t seed, int64_t image_id_base, int b, int hn_total, int vn, const int32_t *tn /*device [b]*/,
+                  int32_t *idxs /*device [b,hn_total,vn,2]*/, void *stream);
+int pvv_make_selection(uint64_t seed, int64_t image_id_base, int b, int h, int w, float *selection /*device [b,h,w]*/,
+                       void *stream);
+
+/* FP32 roofline probe: runs an FFMA-only kernel for `iters` and returns achieved TFLOP/s (0 on error). */
+double pvv_fp32_peak_tflops(int iters, void *stream);
+
+/* Number of kernel launches the last pvv_v3 / pvv_cov call on this thread enqueued. */
+int pvv_last_launch_count(void);
+int pvv_last_cuda_error(void);
+const char *pvv_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PVVOTE_H_ */

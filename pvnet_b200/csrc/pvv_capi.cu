@@ -1,0 +1,190 @@
+// pvv_capi.cu -- the extern "C" surface of libpvvote.so (include/pvvote.h): argument validation, workspace
+// carving, launch sequencing on the caller's stream.  No torch types, no global mutable state, no exit().
+#include <math.h>
+#include <string.h>
+
+#include "pvv_internal.cuh"
+
+namespace {
+
+thread_local int t_last_launches = 0;
+thread_local int t_last_cuda_error = 0;
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int fail_cuda(cudaError_t e)
+{
+    t_last_cuda_error = (int)e;
+    return PVV_ERR_CUDA;
+}
+
+int validate(const pvv_job *j)
+{
+    if (!j || !j->mask || !j->vertex || !j->workspace) return PVV_ERR_INVALID;
+    if (j->b <= 0 || j->h <= 0 || j->w <= 0 || j->vn <= 0 || j->hn_total <= 0) return PVV_ERR_INVALID;
+    if (j->mask_dtype < PVV_MASK_U8 || j->mask_dtype > PVV_MASK_F32) return PVV_ERR_INVALID;
+    if (j->fg_rule != PVV_FG_BYTE && j->fg_rule != PVV_FG_EQ1) return PVV_ERR_INVALID;
+    if (!(j->inlier_thresh == j->inlier_thresh)) return PVV_ERR_INVALID;
+    if (j->vn > PVV_MAX_VN || j->h > 65535 || j->w > 65535 || (long long)j->h * j->w > (1LL << 23) || j->b > 65535)
+        return PVV_ERR_UNSUPPORTED;
+    return PVV_OK;
+}
+
+long long default_cap(const pvv_job *j)
+{
+    const long long npx = (long long)j->h * j->w;
+    long long per = npx;
+    if (j->max_num >= 0 && j->max_num < npx) {
+        // fg <= max_num is kept whole; above it a Bernoulli(max_num/fg) draw keeps ~max_num +- sqrt(max_num)
+        const long long bound = (long long)j->max_num + (long long)(8.0 * sqrt((double)j->max_num)) + 256;
+        per = bound < npx ? bound : npx;
+    }
+    long long cap = per * j->b;
+    return (cap + 63) / 64 * 64;
+}
+
+struct layout {
+    size_t zero_bytes, total_bytes;
+    size_t o_counters, o_img_fg, o_counts, o_flags, o_tn, o_img_off, o_chunk, o_tile_cnt, o_tile_off, o_xy, o_dir, o_hyp;
+    long long cap;
+    int ntiles, hn_pad;
+};
+
+layout make_layout(const pvv_job *j)
+{
+    layout L;
+    L.cap = j->pool_capacity > 0 ? (j->pool_capacity + 63) / 64 * 64 : default_cap(j);
+    L.ntiles = (int)(((long long)j->h * j->w + PVV_TILE_PX - 1) / PVV_TILE_PX);
+    L.hn_pad = (j->hn_total + 3) / 4 * 4;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { const size_t at = o; o = align_up(o + bytes, 256); return at; };
+    L.o_counters = take(16 * sizeof(unsigned));
+    L.o_img_fg = take(sizeof(long long) * j->b);
+    L.o_counts = take(sizeof(int) * (size_t)j->b * j->vn * L.hn_pad);
+    L.zero_bytes = o;
+    L.o_flags = take(sizeof(int) * j->b);
+    L.o_tn = take(sizeof(int) * j->b);
+    L.o_img_off = take(sizeof(long long) * j->b);
+    L.o_chunk = take(sizeof(int) * (j->b + 1));
+    L.o_tile_cnt = take(sizeof(int) * (size_t)j->b * L.ntiles);
+    L.o_tile_off = take(sizeof(int) * (size_t)j->b * L.ntiles);
+    L.o_xy = take(sizeof(uint32_t) * (size_t)L.cap);
+    L.o_dir = take(sizeof(float2) * (size_t)L.cap * j->vn);
+    L.o_hyp = take(sizeof(float2) * (size_t)j->b * j->vn * L.hn_pad);
+    L.total_bytes = o;
+    return L;
+}
+
+pvv_ws carve(const layout &L, void *base)
+{
+    char *p = (char *)base;
+    pvv_ws ws;
+    ws.counters = (unsigned *)(p + L.o_counters);
+    ws.img_fg = (long long *)(p + L.o_img_fg);
+    ws.counts = (int *)(p + L.o_counts);
+    ws.img_flags = (int *)(p + L.o_flags);
+    ws.tn = (int *)(p + L.o_tn);
+    ws.img_off = (long long *)(p + L.o_img_off);
+    ws.chunk_start = (int *)(p + L.o_chunk);
+    ws.tile_cnt = (int *)(p + L.o_tile_cnt);
+    ws.tile_off = (int *)(p + L.o_tile_off);
+    ws.pix_xy = (uint32_t *)(p + L.o_xy);
+    ws.pix_dir = (float2 *)(p + L.o_dir);
+    ws.hyp = (float2 *)(p + L.o_hyp);
+    ws.idxs_used = nullptr;
+    ws.cap = L.cap;
+    ws.ntiles = L.ntiles;
+    ws.hn_pad = L.hn_pad;
+    return ws;
+}
+
+pvv_dims make_dims(const pvv_job *j)
+{
+    pvv_dims d;
+    d.b = j->b; d.h = j->h; d.w = j->w; d.vn = j->vn; d.hn = j->hn_total;
+    d.fg_rule = j->fg_rule; d.mask_dtype = j->mask_dtype;
+    d.min_num = j->min_num; d.max_num = j->max_num;
+    d.thresh = j->inlier_thresh;
+    d.seed = j->seed; d.image_id_base = j->image_id_base;
+    for (int i = 0; i < 3; ++i) d.ms[i] = j->mask_strides[i];
+    for (int i = 0; i < 5; ++i) d.vs[i] = j->vertex_strides[i];
+    return d;
+}
+
+// shared front half of pvv_v3 / pvv_cov: compaction -> hypotheses -> fused counting
+int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *ws_out, int *launches)
+{
+    const int v = validate(j);
+    if (v != PVV_OK) return v;
+    const layout L = make_layout(j);
+    if (j->workspace_bytes < L.total_bytes || ((uintptr_t)j->workspace & 255)) return PVV_ERR_WORKSPACE;
+    if (dbg && (dbg->pix_xy || dbg->pix_dir || dbg->win_inlier) && dbg->pool_capacity != L.cap) return PVV_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)j->stream;
+    pvv_ws ws = carve(L, j->workspace);
+    if (dbg) ws.idxs_used = dbg->idxs;
+    const pvv_dims d = make_dims(j);
+    cudaError_t e = cudaMemsetAsync(j->workspace, 0, L.zero_bytes, st);
+    if (e) return fail_cuda(e);
+    if ((e = pvv_launch_compact(d, j->mask, j->vertex, j->selection, ws, st, launches))) return fail_cuda(e);
+    if ((e = pvv_launch_hypotheses(d, j->idxs, ws, dbg ? dbg->hyp : nullptr, st, launches))) return fail_cuda(e);
+    if ((e = pvv_launch_count(d, ws, dbg ? dbg->force_exact : 0, st, launches))) return fail_cuda(e);
+    *d_out = d;
+    *ws_out = ws;
+    return PVV_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *pvv_version(void) { return "pvvote 0.1 (sm_100a)"; }
+int pvv_last_launch_count(void) { return t_last_launches; }
+int pvv_last_cuda_error(void) { return t_last_cuda_error; }
+
+int64_t pvv_default_pool_capacity(const pvv_job *job)
+{
+    if (!job || job->b <= 0 || job->h <= 0 || job->w <= 0) return 0;
+    return job->pool_capacity > 0 ? (job->pool_capacity + 63) / 64 * 64 : default_cap(job);
+}
+
+size_t pvv_workspace_bytes(const pvv_job *job)
+{
+    if (!job || job->b <= 0 || job->h <= 0 || job->w <= 0 || job->vn <= 0 || job->hn_total <= 0) return 0;
+    return make_layout(job).total_bytes;
+}
+
+int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, const pvv_debug *dbg)
+{
+    (void)confidence; (void)max_iter;  // unobservable in the reference: every round re-votes the same idxs (:553-582)
+    if (!out_kp) return PVV_ERR_INVALID;
+    if (job && job->fg_rule != PVV_FG_BYTE && job->fg_rule != PVV_FG_EQ1) return PVV_ERR_INVALID;
+    int launches = 0;
+    pvv_dims d;
+    pvv_ws ws;
+    const int r = run_front(job, dbg, &d, &ws, &launches);
+    if (r != PVV_OK) return r;
+    cudaStream_t st = (cudaStream_t)job->stream;
+    cudaError_t e;
+    if ((e = pvv_launch_v3_finalize(d, ws, out_kp, dbg, st, &launches))) return fail_cuda(e);
+    if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
+    t_last_launches = launches;
+    return PVV_OK;
+}
+
+int pvv_cov(const pvv_job *job, const float *mean, float *out_cov, const pvv_debug *dbg)
+{
+    if (!mean || !out_cov) return PVV_ERR_INVALID;
+    int launches = 0;
+    pvv_dims d;
+    pvv_ws ws;
+    const int r = run_front(job, dbg, &d, &ws, &launches);
+    if (r != PVV_OK) return r;
+    cudaStream_t st = (cudaStream_t)job->stream;
+    cudaError_t e;
+    if ((e = pvv_launch_cov_finalize(d, ws, mean, out_cov, st, &launches))) return fail_cuda(e);
+    if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
+    t_last_launches = launches;
+    return PVV_OK;
+}
+
+}  // extern "C"

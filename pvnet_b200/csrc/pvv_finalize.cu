@@ -1,0 +1,217 @@
+// pvv_finalize.cu -- K4 (argmax + winner re-vote + least-squares refinement) and K5 (weighted covariance).
+//
+// K4 replaces, per (image, keypoint) and with no host round-trip,
+//   torch.max(counts, 0) / gather / keep-best                      ransac_voting_gpu.py:568-575
+//   winner re-vote                                                 :585-590
+//   weighted normal equations + 2x2 solve (b_inv)                  :593-601, :503-518
+// K5 replaces the covariance algebra of estimate_voting_distribution_with_mean, :375, :394-401.
+// Integer decisions (argmax, inlier flags) are bit-exact; the sums are accumulated in float64 from the same
+// float32 terms the reference forms (its own float32 sum order is library-defined; parity bar 1e-4 relative).
+#include "pvv_internal.cuh"
+
+namespace {
+
+constexpr int kFinThreads = 256;
+
+__device__ __forceinline__ double block_sum(double v, double *s_buf)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_buf[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < kFinThreads / 32; ++i) t += s_buf[i];
+    return t;
+}
+
+// max count with lowest-index tie rule (torch.max(dim) returns the first maximal index)
+__device__ __forceinline__ void block_argmax(const int *row, int hn, int *best_cnt, int *best_h)
+{
+    __shared__ long long s_key[kFinThreads / 32];
+    // key = count in the high word, (INT_MAX - h) in the low word: max key <=> max count, then min h
+    long long key = -1;
+    for (int h = threadIdx.x; h < hn; h += kFinThreads) {
+        const long long k = ((long long)row[h] << 32) | (unsigned)(0x7fffffff - h);
+        key = k > key ? k : key;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const long long other = __shfl_xor_sync(0xffffffffu, key, o);
+        key = other > key ? other : key;
+    }
+    if ((threadIdx.x & 31) == 0) s_key[threadIdx.x >> 5] = key;
+    __syncthreads();
+    long long best = -1;
+#pragma unroll
+    for (int i = 0; i < kFinThreads / 32; ++i) best = s_key[i] > best ? s_key[i] : best;
+    *best_cnt = (int)(best >> 32);
+    *best_h = 0x7fffffff - (int)(best & 0xffffffffLL);
+    __syncthreads();
+}
+
+struct v3_dbg {
+    int32_t *win_idx, *win_count;
+    float *win_pts;
+    uint8_t *win_inlier;
+    double *normal_eq;
+    long long dbg_cap;
+};
+
+__global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws ws, float *out_kp, v3_dbg g)
+{
+    __shared__ double s_buf[kFinThreads / 32];
+    const int img = blockIdx.y, vi = blockIdx.x;
+    const int tn = ws.tn[img];
+    const long long o = (long long)img * d.vn + vi;
+    if (tn == 0) {  // skipped image: zeros (:537-541)
+        if (threadIdx.x == 0) {
+            out_kp[o * 2] = 0.f; out_kp[o * 2 + 1] = 0.f;
+            if (g.win_idx) g.win_idx[o] = 0;
+            if (g.win_count) g.win_count[o] = 0;
+            if (g.win_pts) { g.win_pts[o * 2] = 0.f; g.win_pts[o * 2 + 1] = 0.f; }
+            if (g.normal_eq) for (int i = 0; i < 5; ++i) g.normal_eq[o * 5 + i] = 0.0;
+        }
+        return;
+    }
+    const long long row = o * ws.hn_pad;
+    int best_cnt, best_h;
+    block_argmax(ws.counts + row, d.hn, &best_cnt, &best_h);
+    // all_win_ratio starts at 0 and is only replaced by a strictly larger ratio (:573): count 0 keeps (0,0)
+    const float2 win = best_cnt > 0 ? ws.hyp[row + best_h] : make_float2(0.f, 0.f);
+
+    const long long off = ws.img_off[img];
+    double s00 = 0, s01 = 0, s11 = 0, b0 = 0, b1 = 0;
+    for (int t = threadIdx.x; t < tn; t += kFinThreads) {
+        const uint32_t xy = ws.pix_xy[off + t];
+        const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + t];
+        const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
+        const bool inl = pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), cx, cy, win.x, win.y, d.thresh);
+        if (g.win_inlier) g.win_inlier[(long long)vi * g.dbg_cap + off + t] = inl ? 1 : 0;
+        if (inl) {
+            const float nx = dir.y, ny = -dir.x;                                 // :586-587
+            const float bb = __fadd_rn(__fmul_rn(nx, cx), __fmul_rn(ny, cy));    // :596 (fp32 products, 2-term sum)
+            s00 += (double)nx * nx; s01 += (double)nx * ny; s11 += (double)ny * ny;
+            b0 += (double)__fmul_rn(nx, bb);                                     // :598
+            b1 += (double)__fmul_rn(ny, bb);
+        }
+    }
+    s00 = block_sum(s00, s_buf); s01 = block_sum(s01, s_buf); s11 = block_sum(s11, s_buf);
+    b0 = block_sum(b0, s_buf); b1 = block_sum(b1, s_buf);
+    if (threadIdx.x == 0) {
+        const double det = s00 * s11 - s01 * s01;
+        double x = b0, y = b1;  // b_inv's identity fallback (:516-517), applied per keypoint
+        if (det != 0.0 && isfinite(det)) {
+            x = (s11 * b0 - s01 * b1) / det;
+            y = (s00 * b1 - s01 * b0) / det;
+        }
+        out_kp[o * 2] = (float)x;
+        out_kp[o * 2 + 1] = (float)y;
+        if (g.win_idx) g.win_idx[o] = best_h;
+        if (g.win_count) g.win_count[o] = best_cnt;
+        if (g.win_pts) { g.win_pts[o * 2] = win.x; g.win_pts[o * 2 + 1] = win.y; }
+        if (g.normal_eq) {
+            double *q = g.normal_eq + o * 5;
+            q[0] = s00; q[1] = s01; q[2] = s11; q[3] = b0; q[4] = b1;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kFinThreads) k_cov_finalize(pvv_dims d, pvv_ws ws, const float *mean, float *out_cov)
+{
+    __shared__ double s_buf[kFinThreads / 32];
+    const int img = blockIdx.y, vi = blockIdx.x;
+    const int tn = ws.tn[img];
+    const long long o = (long long)img * d.vn + vi;
+    const float mx = mean[o * 2], my = mean[o * 2 + 1];
+    const long long row = o * ws.hn_pad;
+    double c00 = 0, c01 = 0, c10 = 0, c11 = 0, sw = 0;
+    if (tn == 0) {
+        // skipped image: hypotheses are zeros and every ratio is one (:343-348) -> threshold 0.9 keeps all
+        if (threadIdx.x == 0) {
+            const float dx = __fsub_rn(0.f, mx), dy = __fsub_rn(0.f, my);
+            c00 = (double)dx * dx * d.hn; c01 = (double)dx * dy * d.hn; c10 = c01; c11 = (double)dy * dy * d.hn;
+            sw = (double)d.hn;
+        }
+    } else {
+        int best_cnt, best_h;
+        block_argmax(ws.counts + row, d.hn, &best_cnt, &best_h);
+        const float ftn = (float)tn;
+        const float thr = __fsub_rn(__fdiv_rn((float)best_cnt, ftn), 0.1f);          // :394
+        for (int h = threadIdx.x; h < d.hn; h += kFinThreads) {
+            const float r = __fdiv_rn((float)ws.counts[row + h], ftn);              // :375
+            const float w = r < thr ? 0.f : r;                                      // :395
+            const float2 hv = ws.hyp[row + h];
+            const float dx = __fsub_rn(hv.x, mx), dy = __fsub_rn(hv.y, my);          // :398
+            const float wx = __fmul_rn(dx, w), wy = __fmul_rn(dy, w);                // :399
+            c00 += (double)dx * wx; c01 += (double)dx * wy; c10 += (double)dy * wx; c11 += (double)dy * wy;  // :400
+            sw += (double)w;
+        }
+    }
+    c00 = block_sum(c00, s_buf); c01 = block_sum(c01, s_buf); c10 = block_sum(c10, s_buf);
+    c11 = block_sum(c11, s_buf); sw = block_sum(sw, s_buf);
+    if (threadIdx.x == 0) {
+        const double den = sw + 1e-3;                                               // :401
+        out_cov[o * 4 + 0] = (float)(c00 / den);
+        out_cov[o * 4 + 1] = (float)(c01 / den);
+        out_cov[o * 4 + 2] = (float)(c10 / den);
+        out_cov[o * 4 + 3] = (float)(c11 / den);
+    }
+}
+
+// counts [b][vn][hn_pad] -> reference layout [b][hn][vn]
+__global__ void k_export_counts(pvv_dims d, pvv_ws ws, int32_t *counts_out)
+{
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long total = (long long)d.b * d.hn * d.vn;
+    if (e >= total) return;
+    const int vi = (int)(e % d.vn);
+    const long long r = e / d.vn;
+    const int hi = (int)(r % d.hn);
+    const int img = (int)(r / d.hn);
+    counts_out[e] = ws.counts[((long long)img * d.vn + vi) * ws.hn_pad + hi];
+}
+
+}  // namespace
+
+cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, const pvv_debug *dbg,
+                                   cudaStream_t st, int *launches)
+{
+    v3_dbg g = {nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+    if (dbg) {
+        g.win_idx = dbg->win_idx; g.win_count = dbg->win_count; g.win_pts = dbg->win_pts;
+        g.win_inlier = dbg->win_inlier; g.normal_eq = dbg->normal_eq; g.dbg_cap = dbg->pool_capacity;
+    }
+    k_v3_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, out_kp, g);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t pvv_launch_cov_finalize(const pvv_dims &d, const pvv_ws &ws, const float *mean, float *out_cov,
+                                    cudaStream_t st, int *launches)
+{
+    k_cov_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, mean, out_cov);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t pvv_launch_debug_export(const pvv_dims &d, const pvv_ws &ws, const pvv_debug *dbg, cudaStream_t st,
+                                    int *launches)
+{
+    if (!dbg) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    if (dbg->tn) e = cudaMemcpyAsync(dbg->tn, ws.tn, sizeof(int) * d.b, cudaMemcpyDeviceToDevice, st);
+    if (!e && dbg->img_off) e = cudaMemcpyAsync(dbg->img_off, ws.img_off, sizeof(long long) * d.b, cudaMemcpyDeviceToDevice, st);
+    if (!e && dbg->pix_xy) e = cudaMemcpyAsync(dbg->pix_xy, ws.pix_xy, sizeof(uint32_t) * ws.cap, cudaMemcpyDeviceToDevice, st);
+    if (!e && dbg->pix_dir) e = cudaMemcpyAsync(dbg->pix_dir, ws.pix_dir, sizeof(float2) * ws.cap * d.vn, cudaMemcpyDeviceToDevice, st);
+    if (!e && dbg->status) e = cudaMemcpyAsync(dbg->status, &ws.counters[PVV_CTR_STATUS], sizeof(int), cudaMemcpyDeviceToDevice, st);
+    if (!e && dbg->amb_count) e = cudaMemcpyAsync(dbg->amb_count, &ws.counters[PVV_CTR_AMB_LO], sizeof(uint64_t), cudaMemcpyDeviceToDevice, st);
+    if (!e && dbg->counts) {
+        const long long total = (long long)d.b * d.hn * d.vn;
+        k_export_counts<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d, ws, dbg->counts);
+        ++*launches;
+        e = cudaGetLastError();
+    }
+    return e;
+}

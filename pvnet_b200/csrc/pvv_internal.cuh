@@ -1,0 +1,54 @@
+// pvv_internal.cuh -- workspace view and kernel launcher prototypes shared by the .cu files of libpvvote.
+#pragma once
+#include "pvv_common.cuh"
+
+// Device workspace, carved out of pvv_job.workspace by pvv_capi.cu.  All pointers are device pointers.
+struct pvv_ws {
+    // --- zeroed at the start of every call (one contiguous memset) ---
+    unsigned int *counters;       // [16] see PVV_CTR_*
+    long long *img_fg;            // [b]  v3: sum of byte values; eq1: number of ==1 pixels   (K1a, atomics)
+    int *counts;                  // [b][vn][hn]  inlier counts (K3, atomics)
+    // --- written before read ---
+    int *img_flags;               // [b]  PVV_IMG_*
+    int *tn;                      // [b]  compacted pixels per image (0 when skipped)
+    long long *img_off;           // [b]  offset of the image's pixels in the pool
+    int *chunk_start;             // [b+1] first voting chunk of each image; [b] = total
+    int *tile_cnt;                // [b][ntiles] foreground pixels per compaction tile
+    int *tile_off;                // [b][ntiles] exclusive prefix of tile_cnt within the image
+    uint32_t *pix_xy;             // [cap]      x | y<<16
+    float2 *pix_dir;              // [vn][cap]  raw direction vectors (SoA over keypoints)
+    float2 *hyp;                  // [b][vn][hn] hypotheses
+    int32_t *idxs_used;           // optional debug [b][hn][vn][2]
+    long long cap;
+    int ntiles;
+    int hn_pad;                   // hn rounded up to a multiple of 4 (hyp / counts row pitch)
+};
+
+enum { PVV_CTR_TICKET = 0, PVV_CTR_WORK = 1, PVV_CTR_STATUS = 2, PVV_CTR_AMB_LO = 4, PVV_CTR_AMB_HI = 5 };
+enum { PVV_IMG_SKIPPED = 1, PVV_IMG_SUBSAMPLED = 2, PVV_IMG_OVERFLOW = 4 };
+
+struct pvv_dims {
+    int b, h, w, vn, hn;
+    int fg_rule, mask_dtype;
+    int min_num, max_num;
+    float thresh;
+    unsigned long long seed;
+    long long image_id_base;
+    long long ms[3];   // mask strides (elements)
+    long long vs[5];   // vertex strides (elements)
+};
+
+// K1: compaction (pvv_compact.cu)
+cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float *vertex, const float *selection,
+                               const pvv_ws &ws, cudaStream_t st, int *launches);
+// K2 + K3: hypotheses and fused inlier counting (pvv_vote.cu)
+cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out,
+                                  cudaStream_t st, int *launches);
+cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches);
+// K4 / K5: finalisation (pvv_finalize.cu)
+cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, const pvv_debug *dbg,
+                                   cudaStream_t st, int *launches);
+cudaError_t pvv_launch_cov_finalize(const pvv_dims &d, const pvv_ws &ws, const float *mean, float *out_cov,
+                                    cudaStream_t st, int *launches);
+cudaError_t pvv_launch_debug_export(const pvv_dims &d, const pvv_ws &ws, const pvv_debug *dbg, cudaStream_t st,
+                                    int *launches);

@@ -1,0 +1,249 @@
+// pvv_vote.cu -- K2 (hypothesis generation) and K3 (fused inlier counting, the FP32-bound hot loop).
+//
+// K2 replaces generate_hypothesis (ransac_voting_kernel.cu:11-86) for the whole batch.
+// K3 replaces  zeros([hn,vn,tn]) + voting_for_hypothesis (ransac_voting_kernel.cu:88-167) + torch.sum(inlier, 2)
+//              (ransac_voting_gpu.py:563-567 / :371-374): the [hn,vn,tn] uint8 matrix is never materialised.
+//
+// K3 design (DESIGN.md "K3"):
+//   * persistent CTAs, dynamic work queue of (pixel chunk, keypoint) items;
+//   * the chunk's pixels are staged in shared memory as 6 derived floats per pixel, read back as warp-broadcast
+//     LDS.128 + LDS.64; every thread keeps H hypotheses and H integer counters in registers, so the inner loop has
+//     no atomics, no shuffles and no global traffic;
+//   * decision by a guard-banded filter in a rotated frame:  inlier  <=>  a > tau*|c|  with a = d.n^, c = d x n^,
+//     tau = t/sqrt(1-t^2): 4 FFMA + 2 FSETP per test.  Tests that fall inside the band (|a-|c'|| <= eps_rel*a+eps_abs)
+//     are re-evaluated with the reference's exact rounding sequence (pvv_exact_test), which makes the counts
+//     bit-identical to the reference kernel's (error analysis in DESIGN.md "Guard band").
+#include "pvv_internal.cuh"
+
+namespace {
+
+// ---- K2 -------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out)
+{
+    const int img = blockIdx.y;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= d.vn * d.hn) return;
+    const int vi = e / d.hn, hi = e - vi * d.hn;
+    const int tn = ws.tn[img];
+    float2 out = make_float2(0.f, 0.f);
+    int t0 = 0, t1 = 0;
+    if (tn > 0) {
+        if (idxs) {
+            const long long o = (((long long)img * d.hn + hi) * d.vn + vi) * 2;
+            t0 = idxs[o];
+            t1 = idxs[o + 1];
+        } else {
+            pvv_draw_pair(d.seed, d.image_id_base + img, hi, vi, d.vn, tn, t0, t1);
+        }
+        if ((unsigned)t0 < (unsigned)tn && (unsigned)t1 < (unsigned)tn) {
+            const long long off = ws.img_off[img];
+            const uint32_t xy0 = ws.pix_xy[off + t0], xy1 = ws.pix_xy[off + t1];
+            const float2 d0 = ws.pix_dir[(long long)vi * ws.cap + off + t0];
+            const float2 d1 = ws.pix_dir[(long long)vi * ws.cap + off + t1];
+            float x, y;
+            if (pvv_intersect(d0.x, d0.y, (float)(xy0 & 0xffffu), (float)(xy0 >> 16), d1.x, d1.y,
+                              (float)(xy1 & 0xffffu), (float)(xy1 >> 16), x, y))
+                out = make_float2(x, y);
+        }
+    }
+    ws.hyp[((long long)img * d.vn + vi) * ws.hn_pad + hi] = out;
+    const long long ro = (((long long)img * d.hn + hi) * d.vn + vi) * 2;
+    if (hyp_out) { hyp_out[ro] = out.x; hyp_out[ro + 1] = out.y; }
+    if (ws.idxs_used) { ws.idxs_used[ro] = t0; ws.idxs_used[ro + 1] = t1; }
+}
+
+// ---- K3 -------------------------------------------------------------------------------------------
+constexpr int kCountThreads = 128;
+
+struct band_consts {
+    float tau;        // t / sqrt(1 - t^2)
+    float erel;       // relative half-width of the band (in units of a)
+    float kabs;       // absolute half-width per unit of coordinate magnitude
+    float abs_floor;  // catches ||d|| < 1e-6 (reference skips those)
+};
+
+template <int H, bool EXACT>
+__global__ void __launch_bounds__(kCountThreads) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
+{
+    __shared__ float4 sA[PVV_CHUNK_PX];   // n^x, n^y, -s, tau*n^y
+    __shared__ float2 sB[PVV_CHUNK_PX];   // -tau*n^x, -tau*s2
+    __shared__ float2 sD[PVV_CHUNK_PX];   // raw direction
+    __shared__ uint32_t sXY[PVV_CHUNK_PX];
+    __shared__ int s_item, s_P;
+
+    const int tid = threadIdx.x;
+    const int total_items = ws.chunk_start[d.b] * d.vn;
+    unsigned long long amb_local = 0;
+
+    while (true) {
+        __syncthreads();  // previous item's smem fully consumed
+        if (tid == 0) { s_item = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u); s_P = 0; }
+        __syncthreads();
+        const int item = s_item;
+        if (item >= total_items) break;
+        const int ci = item / d.vn, vi = item - ci * d.vn;
+        int lo = 0, hi = d.b;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (ws.chunk_start[mid] <= ci) lo = mid; else hi = mid;
+        }
+        const int img = lo;
+        const int tn = ws.tn[img];
+        const long long off = ws.img_off[img];
+        const int p0 = (ci - ws.chunk_start[img]) * PVV_CHUNK_PX;
+        const int n = min(PVV_CHUNK_PX, tn - p0);
+        const uint32_t xy0 = ws.pix_xy[off + p0];
+        const int ox = (int)(xy0 & 0xffffu), oy = (int)(xy0 >> 16);
+
+        // ---- stage the chunk: raw values + derived constants in a chunk-local frame ----
+        for (int j = tid; j < n; j += kCountThreads) {
+            const uint32_t xy = ws.pix_xy[off + p0 + j];
+            const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + p0 + j];
+            sXY[j] = xy;
+            sD[j] = dir;
+            if (!EXACT) {
+                const float n1 = pvv_norm1(dir.x, dir.y);
+                float4 A;
+                float2 B;
+                if (!((double)n1 >= 1e-6) || !(n1 < 3.0e38f)) {
+                    // reference skips the pixel (||n|| < 1e-6) or its cosine degenerates: never an inlier
+                    A = make_float4(0.f, 0.f, -1e30f, 0.f);
+                    B = make_float2(0.f, 0.f);
+                } else {
+                    const double inv = rsqrt((double)dir.x * dir.x + (double)dir.y * dir.y);
+                    const int px = (int)(xy & 0xffffu) - ox, py = (int)(xy >> 16) - oy;
+                    A.x = (float)(dir.x * inv);
+                    A.y = (float)(dir.y * inv);
+                    A.w = (float)((double)bc.tau * (dir.y * inv));
+                    B.x = (float)(-(double)bc.tau * (dir.x * inv));
+                    A.z = (float)(-((double)px * A.x + (double)py * A.y));
+                    B.y = (float)(-((double)px * A.w + (double)py * B.x));
+                    atomicMax(&s_P, abs(px) + abs(py));
+                }
+                sA[j] = A;
+                sB[j] = B;
+            }
+        }
+        __syncthreads();
+        const float P = (float)s_P;
+        const long long row = ((long long)img * d.vn + vi) * ws.hn_pad;
+
+        for (int hbase = 0; hbase < d.hn; hbase += kCountThreads * H) {
+            if (hbase + (tid & ~31) >= d.hn) continue;  // warp-uniform: this warp has no hypothesis in the pass
+            float hxr[H], hyr[H];
+            int cnt[H];
+#pragma unroll
+            for (int k = 0; k < H; ++k) {
+                const int h = hbase + k * kCountThreads + tid;
+                const float2 hv = h < d.hn ? ws.hyp[row + h] : make_float2(0.f, 0.f);
+                hxr[k] = hv.x; hyr[k] = hv.y; cnt[k] = 0;
+            }
+            if (EXACT) {
+                for (int j = 0; j < n; ++j) {
+                    const uint32_t xy = sXY[j];
+                    const float2 dir = sD[j];
+                    const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
+                    const float n1 = pvv_norm1(dir.x, dir.y);
+#pragma unroll
+                    for (int k = 0; k < H; ++k) cnt[k] += pvv_exact_test(dir.x, dir.y, n1, cx, cy, hxr[k], hyr[k], d.thresh);
+                }
+            } else {
+                float hx[H], hy[H], eabs[H];
+#pragma unroll
+                for (int k = 0; k < H; ++k) {
+                    hx[k] = hxr[k] - (float)ox;
+                    hy[k] = hyr[k] - (float)oy;
+                    const float m = fabsf(hx[k]) + fabsf(hy[k]) + P;
+                    // far-away / non-finite hypotheses: always take the exact path (overflow behaviour of the reference)
+                    eabs[k] = (m < 1e15f) ? fmaf(bc.kabs, m, bc.abs_floor) : __int_as_float(0x7f800000);
+                }
+#pragma unroll 2
+                for (int j = 0; j < n; ++j) {
+                    const float4 A = sA[j];
+                    const float2 B = sB[j];
+                    bool amb = false;
+                    bool ambk[H];
+#pragma unroll
+                    for (int k = 0; k < H; ++k) {
+                        const float a = fmaf(hx[k], A.x, fmaf(hy[k], A.y, A.z));
+                        const float c = fmaf(hx[k], A.w, fmaf(hy[k], B.x, B.y));
+                        const float e = a - fabsf(c);
+                        const float t1 = fmaf(bc.erel, a, eabs[k]);
+                        ambk[k] = fabsf(e) <= t1;
+                        amb |= ambk[k];
+                        cnt[k] += (e > t1) ? 1 : 0;
+                    }
+                    if (amb) {
+                        const uint32_t xy = sXY[j];
+                        const float2 dir = sD[j];
+                        const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
+                        const float n1 = pvv_norm1(dir.x, dir.y);
+#pragma unroll
+                        for (int k = 0; k < H; ++k)
+                            if (ambk[k]) {
+                                cnt[k] += pvv_exact_test(dir.x, dir.y, n1, cx, cy, hxr[k], hyr[k], d.thresh);
+                                ++amb_local;
+                            }
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < H; ++k) {
+                const int h = hbase + k * kCountThreads + tid;
+                if (h < d.hn && cnt[k]) atomicAdd(&ws.counts[row + h], cnt[k]);
+            }
+        }
+    }
+    if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
+}
+
+}  // namespace
+
+cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out,
+                                  cudaStream_t st, int *launches)
+{
+    const dim3 grid((d.vn * d.hn + 255) / 256, d.b);
+    k_hypotheses<<<grid, 256, 0, st>>>(d, idxs, ws, hyp_out);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// Guard-band constants for threshold t (DESIGN.md "Guard band").  Returns false when the fast filter does
+// not apply (t outside [0.5, 0.99999]): the caller then runs the exact-only kernel.
+static bool pvv_band_for(float t, band_consts *bc)
+{
+    if (!(t >= 0.5f && t <= 0.99999f)) return false;
+    const double u = 5.9604644775390625e-8;  // 2^-24
+    const double td = (double)t;
+    const double one_m = 1.0 - td * td;
+    const double tau = td / sqrt(one_m);
+    const double eq = (8.0 + 4.0 / td) * u;         // bound on the relative rounding error of the reference's quotient
+    const double etau = eq / one_m;                 // induced relative uncertainty of tau
+    if (etau > 0.05) return false;
+    bc->tau = (float)tau;
+    bc->erel = (float)(1.5 * etau / (1.0 - etau) + 8.0 * u);
+    bc->kabs = (float)(8.0 * u * (1.0 + tau) * (1.0 + etau));
+    bc->abs_floor = (float)(4e-6 * (1.0 + tau));
+    return true;
+}
+
+cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches)
+{
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    band_consts bc = {0.f, 0.f, 0.f, 0.f};
+    const bool fast = !force_exact && pvv_band_for(d.thresh, &bc);
+    int per_sm = 8;
+    if (fast) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<4, false>, kCountThreads, 0);
+        if (per_sm < 1) per_sm = 1;
+        k_count<4, false><<<sms * per_sm, kCountThreads, 0, st>>>(d, ws, bc);
+    } else {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<4, true>, kCountThreads, 0);
+        if (per_sm < 1) per_sm = 1;
+        k_count<4, true><<<sms * per_sm, kCountThreads, 0, st>>>(d, ws, bc);
+    }
+    ++*launches;
+    return cudaGetLastError();
+}

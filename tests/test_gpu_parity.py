@@ -1,0 +1,303 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via pvnet_b200.ransac_voting_gpu) against the CPU oracle,
+the committed golden fixtures and -- when oracle/_ref was built -- the reference's own CUDA kernels.
+Integer / index / byte outputs are compared bit for bit; keypoints and covariances within 1e-4 relative
+(BASELINE.json north_star), tolerance written at each assert."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as orc
+from oracle import ref_driver
+from pvnet_b200 import synth
+from pvnet_b200 import ransac_voting_gpu as pv
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4
+DEV = "cuda:0"
+
+
+def _bits(t):
+    return t.detach().cpu().contiguous().view(torch.int32).numpy() if isinstance(t, torch.Tensor) else \
+        np.ascontiguousarray(t, np.float32).view(np.int32)
+
+
+def _unpack_pool(dbg, bi, vn):
+    tn = int(dbg["tn"][bi])
+    off = int(dbg["img_off"][bi])
+    xy = dbg["pix_xy"][off:off + tn].cpu().numpy().astype(np.int64) & 0xffffffff
+    coords = np.stack([xy & 0xffff, xy >> 16], 1).astype(np.float32)
+    direct = dbg["pix_dir"][:, off:off + tn].permute(1, 0, 2).cpu().numpy()
+    inl = dbg["win_inlier"][:, off:off + tn].cpu().numpy()
+    return tn, coords, direct, inl
+
+
+def _check_v3_against_oracle(mask, vertex, hn, thresh, min_num, max_num, idxs, selection, out, dbg):
+    o_out, o_dbg = orc.ransac_voting_layer_v3(mask, vertex, hn, thresh, min_num=min_num, max_num=max_num, idxs=idxs,
+                                              selection=selection, return_debug=True)
+    b, vn = out.shape[:2]
+    for bi in range(b):
+        if o_dbg[bi] is None:
+            assert int(dbg["tn"][bi]) == 0 and np.all(out[bi].cpu().numpy() == 0)
+            continue
+        tn, coords, direct, inl = _unpack_pool(dbg, bi, vn)
+        assert tn == o_dbg[bi]["coords"].shape[0]
+        assert np.array_equal(coords, o_dbg[bi]["coords"])                                  # compacted set + order
+        assert np.array_equal(_bits(direct), _bits(o_dbg[bi]["direct"]))                    # gathered vectors, bits
+        assert np.array_equal(_bits(dbg["hyp"][bi]), _bits(o_dbg[bi]["hyp"]))               # hypotheses, bits
+        assert np.array_equal(dbg["counts"][bi].cpu().numpy(), o_dbg[bi]["counts"])         # inlier counts
+        assert np.array_equal(dbg["win_idx"][bi].cpu().numpy(), o_dbg[bi]["win_idx"])       # argmax
+        assert np.array_equal(inl, o_dbg[bi]["inlier"])                                     # winner inlier flags
+    np.testing.assert_allclose(out.cpu().numpy(), o_out, rtol=RTOL, atol=0)
+    return o_out, o_dbg
+
+
+def _cat_inputs(z):
+    mask, kp = synth.cat_fixture()
+    ys, xs = np.nonzero(mask)
+    vertex = np.zeros((1, 480, 640, 9, 2), np.float32)
+    vertex[0][ys, xs] = z["fg_vertex"]
+    return mask[None], vertex
+
+
+@pytest.mark.parametrize("name", ["cat_exact", "cat_noisy"])
+def test_golden_cat(golden_dir, name):
+    """configs[0]: the fixture produced by the reference's Python wrapper."""
+    z = np.load(os.path.join(golden_dir, f"v3_{name}.npz"))
+    mask, vertex = _cat_inputs(z)
+    out, dbg = pv.ransac_voting_layer_v3(torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV),
+                                         int(z["hn"]), float(z["thresh"]), idxs=torch.from_numpy(z["idxs"]),
+                                         return_debug=True)
+    assert np.array_equal(dbg["counts"][0].cpu().numpy(), z["counts"][0])
+    np.testing.assert_allclose(out.cpu().numpy(), z["out"], rtol=RTOL, atol=0)
+    _check_v3_against_oracle(mask, vertex, int(z["hn"]), float(z["thresh"]), 100, 30000, z["idxs"], None, out, dbg)
+
+
+def test_golden_small_batch(golden_dir):
+    """skipped image, subsampled image (injected selection), labels > 1, and the covariance path."""
+    z = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    mask, vertex = z["mask"].astype(np.int64), z["vertex"]
+    hn, min_num, max_num = (int(v) for v in z["v3_args"])
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, 0.99, min_num=min_num, max_num=max_num,
+                                         idxs=torch.from_numpy(z["v3_idxs"]), selection=torch.from_numpy(z["v3_sel"]),
+                                         return_debug=True)
+    for bi in (0, 2, 3):
+        assert np.array_equal(dbg["counts"][bi].cpu().numpy(), z["v3_counts"][bi])
+    np.testing.assert_allclose(out.cpu().numpy(), z["v3_out"], rtol=RTOL, atol=0)
+    _check_v3_against_oracle(mask, vertex, hn, 0.99, min_num, max_num, z["v3_idxs"], z["v3_sel"], out, dbg)
+    rh, mh, cmin, cmax = (int(v) for v in z["cov_args"])
+    mean, cov = pv.estimate_voting_distribution_with_mean(tm, tv, torch.from_numpy(z["cov_mean"]).to(DEV), rh, mh,
+                                                          inlier_thresh=0.99, min_num=cmin, max_num=cmax,
+                                                          idxs=torch.from_numpy(z["cov_idxs"]),
+                                                          selection=torch.from_numpy(z["cov_sel"]))
+    np.testing.assert_allclose(cov.cpu().numpy(), z["cov"], rtol=RTOL, atol=1e-6)
+
+
+@pytest.mark.parametrize("thresh", [0.99, 0.999])
+def test_batch_vs_oracle_library_draws(thresh):
+    """4 images of configs[1] shape, network memory layout, library-generated idxs fed back to the oracle."""
+    b, vn, hn = 4, 9, 128
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=77)
+    mask[1] = 0                                   # empty image -> skipped
+    tm = torch.from_numpy(mask).to(DEV)
+    tv = synth.as_net_output(vertex, device=DEV)  # non-contiguous [b,h,w,vn,2] view of [b,2+2vn,h,w]
+    assert not tv.is_contiguous()
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=5, return_debug=True)
+    idxs = dbg["idxs"].cpu().numpy()
+    # the materialised stream equals what the kernels drew in-flight
+    assert torch.equal(pv.make_idxs(5, dbg["tn"], hn, vn), dbg["idxs"])
+    _check_v3_against_oracle(mask, vertex, hn, thresh, 100, 30000, idxs, None, out, dbg)
+    # injecting the same draws reproduces the run bit for bit; contiguous input gives the same answer
+    out2 = pv.ransac_voting_layer_v3(tm, torch.from_numpy(vertex).to(DEV), hn, thresh, idxs=dbg["idxs"])
+    assert torch.equal(out, out2)
+    assert int(dbg["status"]) == 0
+
+
+def test_fast_filter_equals_exact_full_size():
+    """Full configs[1] size (32 x 480x640, 9 kp, 512 hyp): the guard-banded filter must reproduce the exact-only
+    kernel's counts bit for bit (size-independent property; the oracle would take minutes here)."""
+    b, vn, hn = 32, 9, 512
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=1234)
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    for thresh in (0.999, 0.99):
+        o1, d1 = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=0, return_debug=True)
+        o2, d2 = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=0, return_debug=True, force_exact=True)
+        assert torch.equal(d1["counts"], d2["counts"])
+        assert torch.equal(d1["win_idx"], d2["win_idx"]) and torch.equal(o1, o2)
+        tests = float(d1["tn"].sum()) * vn * hn
+        amb = int(d1["amb_count"])
+        assert 0 < amb < 0.01 * tests, (amb, tests)      # the exact path is taken, and rarely
+        assert int(d2["amb_count"]) == 0
+        # round trip: noisy field around known keypoints -> recovered keypoints close to truth
+    kp = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=1234)[2]
+    assert np.abs(o1.cpu().numpy() - kp).max() < 5.0
+
+
+def test_adversarial_band_cases():
+    """Hypotheses placed exactly on / around the decision cone, on pixels, far away, non-finite: fast == exact."""
+    rng = np.random.default_rng(3)
+    h, w, vn, hn = 64, 96, 3, 256
+    mask = np.ones((1, h, w), np.int64)
+    vertex = rng.standard_normal((1, h, w, vn, 2)).astype(np.float32)
+    vertex[0, :8] *= 1e-7            # ||n|| < 1e-6 rows: skipped by the reference
+    vertex[0, 8:10] = 0.0
+    vertex[0, 10:12] *= 1e18
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    for thresh in (0.5, 0.9, 0.99, 0.999, 0.99999):
+        o1, d1 = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=9, max_num=10 ** 6, return_debug=True)
+        o2, d2 = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=9, max_num=10 ** 6, return_debug=True,
+                                           force_exact=True)
+        assert torch.equal(d1["counts"], d2["counts"]), thresh
+    # thresholds outside the filter's range run the exact kernel directly
+    for thresh in (0.3, -0.5, 0.9999999, 1.5):
+        o1, d1 = pv.ransac_voting_layer_v3(tm, tv, 64, thresh, seed=9, max_num=10 ** 6, return_debug=True)
+        tn, coords, direct, _ = _unpack_pool(d1, 0, vn)
+        ref = orc.vote_counts(direct, coords, d1["hyp"][0].cpu().numpy(), thresh)
+        assert np.array_equal(d1["counts"][0].cpu().numpy(), ref), thresh
+
+
+def test_primitives_vs_oracle_and_reference_kernels():
+    """pvv_generate_hypothesis / pvv_voting_for_hypothesis / pvv_vote_counts on the reference's AoS layouts; when the
+    reference's own CUDA build is present (oracle/_ref) all three implementations must agree bit for bit."""
+    rng = np.random.default_rng(11)
+    tn, vn, hn = 3000, 9, 96
+    mask, vertex, _ = synth.make_batch(1, vn=vn, frac=0.02, sigma=0.1, seed=5)
+    cp = orc.compact(mask[0], vertex[0], "v3", 1, 10 ** 9)
+    coords, direct = cp[0][:tn], cp[1][:tn]
+    tn = coords.shape[0]
+    idxs = rng.integers(0, tn, size=(hn, vn, 2)).astype(np.int32)
+    idxs[0] = idxs[0][:, :1]                                  # identical pair -> degenerate -> zeros
+    td, tc, ti = (torch.from_numpy(a).to(DEV) for a in (direct, coords, idxs))
+    hyp = pv.ransac_voting.generate_hypothesis(td, tc, ti)
+    o_hyp = orc.generate_hypothesis(direct, coords, idxs)
+    assert np.array_equal(_bits(hyp), _bits(o_hyp)) and np.all(o_hyp[0] == 0)
+    for thresh in (0.99, 0.999, 0.2):
+        inl = torch.zeros((hn, vn, tn), dtype=torch.uint8, device=DEV)
+        pv.ransac_voting.voting_for_hypothesis(td, tc, hyp, inl, thresh)
+        o_inl = np.zeros((hn, vn, tn), np.uint8)
+        orc.voting_for_hypothesis(direct, coords, o_hyp, o_inl, thresh)
+        assert np.array_equal(inl.cpu().numpy(), o_inl)
+        cnt = pv.ransac_voting.vote_counts(td, tc, hyp, thresh)
+        assert np.array_equal(cnt.cpu().numpy(), o_inl.astype(np.int64).sum(2))
+        if ref_driver.available():
+            rv = ref_driver.ext()
+            r_hyp = rv.generate_hypothesis(td, tc, ti)
+            assert np.array_equal(_bits(r_hyp), _bits(hyp))
+            r_inl = torch.zeros((hn, vn, tn), dtype=torch.uint8, device=DEV)
+            rv.voting_for_hypothesis(td, tc, r_hyp, r_inl, thresh)
+            assert torch.equal(r_inl, inl)
+    with pytest.raises(RuntimeError):
+        pv.ransac_voting.generate_hypothesis(td.cpu(), tc, ti)              # CHECK_CUDA
+    with pytest.raises(RuntimeError):
+        pv.ransac_voting.generate_hypothesis(td.transpose(0, 1), tc, ti)    # CHECK_CONTIGUOUS
+
+
+@pytest.mark.skipif(not ref_driver.available(), reason="oracle/_ref (reference CUDA build) not present")
+def test_v3_and_cov_vs_reference_cuda_layer():
+    """configs[1]/[2] slices against the reference's own kernels driven by oracle/ref_driver.py on the same GPU."""
+    b, vn, hn = 6, 9, 512
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=99)
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, 0.999, seed=21, return_debug=True)
+    r_out, r_dbg = ref_driver.v3(tm, tv, hn, 0.999, 100, 30000, dbg["idxs"])
+    for bi in range(b):
+        tn, coords, direct, inl = _unpack_pool(dbg, bi, vn)
+        assert np.array_equal(coords, r_dbg[bi]["coords"].cpu().numpy())
+        assert np.array_equal(_bits(direct), _bits(r_dbg[bi]["direct"]))
+        assert np.array_equal(_bits(dbg["hyp"][bi]), _bits(r_dbg[bi]["hyp"]))
+        assert np.array_equal(dbg["counts"][bi].cpu().numpy(), r_dbg[bi]["counts"].cpu().numpy())
+        assert np.array_equal(dbg["win_idx"][bi].cpu().numpy(), r_dbg[bi]["win_idx"].cpu().numpy())
+        assert np.array_equal(inl, r_dbg[bi]["inlier"].cpu().numpy())
+    np.testing.assert_allclose(out.cpu().numpy(), r_out.cpu().numpy(), rtol=RTOL, atol=0)
+    # covariance path, reduced hypothesis budget to keep the reference's [hn,vn,tn] matrix small
+    mean, cov, cdbg = pv.estimate_voting_distribution_with_mean(tm, tv, out, 128, 512, inlier_thresh=0.99, seed=22,
+                                                                return_debug=True)
+    ridx = cdbg["idxs"].view(b, 4, 128, vn, 2)
+    _, r_cov = ref_driver.cov(tm, tv, out, 128, 512, 0.99, 20, 30000, ridx)
+    np.testing.assert_allclose(cov.cpu().numpy(), r_cov.cpu().numpy(), rtol=RTOL, atol=1e-6)
+
+
+def test_cov_vs_oracle_and_subsampling_with_library_selection():
+    """configs[2]-style covariance on a small batch + fg > max_num with the library's own selection stream."""
+    b, vn = 3, 9
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.05, sigma=0.08, seed=31, h=120, w=160)
+    mask[2] = 0
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    kp = pv.ransac_voting_layer_v3(tm, tv, 128, 0.99, seed=1, min_num=20, max_num=500)
+    mean, cov, dbg = pv.estimate_voting_distribution_with_mean(tm, tv, kp, 64, 256, inlier_thresh=0.99, min_num=20,
+                                                               max_num=500, seed=2, return_debug=True)
+    assert int(dbg["tn"][0]) < int(mask[0].sum())                       # subsampled
+    sel = pv.make_selection(2, b, 120, 160, DEV).cpu().numpy()
+    idxs = dbg["idxs"].view(b, 4, 64, vn, 2).cpu().numpy()
+    _, o_cov, o_dbg = orc.estimate_voting_distribution_with_mean(mask, vertex, kp.cpu().numpy(), 64, 256,
+                                                                 inlier_thresh=0.99, min_num=20, max_num=500,
+                                                                 idxs=idxs, selection=sel, return_debug=True)
+    for bi in range(2):
+        assert np.array_equal(dbg["counts"][bi].cpu().numpy(), o_dbg[bi]["counts"])
+    np.testing.assert_allclose(cov.cpu().numpy(), o_cov, rtol=RTOL, atol=1e-6)
+    assert mean is kp
+    # skipped image: hyp zeros, ratio ones -> cov ~= mean mean^T (ransac_voting_gpu.py:343-348)
+    m = kp[2].cpu().numpy().astype(np.float64)
+    np.testing.assert_allclose(cov[2].cpu().numpy(), m[:, :, None] * m[:, None, :] * 256 / 256.001, rtol=RTOL, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.uint8, torch.bool, torch.int32, torch.int64, torch.float32, torch.int16])
+def test_mask_dtypes_and_strides(dtype):
+    mask, vertex, _ = synth.make_batch(2, vn=4, frac=0.1, sigma=0.05, seed=8, h=48, w=64)
+    tv = torch.from_numpy(vertex).to(DEV)
+    base = pv.ransac_voting_layer_v3(torch.from_numpy(mask).to(DEV), tv, 64, 0.99, seed=3, min_num=10)
+    m = torch.from_numpy(mask).to(DEV).to(dtype)
+    assert torch.equal(pv.ransac_voting_layer_v3(m, tv, 64, 0.99, seed=3, min_num=10), base)
+    # strided mask view (every other column of a wider tensor)
+    wide = torch.zeros((2, 48, 128), dtype=m.dtype, device=DEV)
+    wide[:, :, ::2] = m
+    assert torch.equal(pv.ransac_voting_layer_v3(wide[:, :, ::2], tv, 64, 0.99, seed=3, min_num=10), base)
+
+
+def test_byte_wrap_and_label_rules():
+    """v3 uses mask.byte() (256 wraps to background, 2 stays foreground); the distribution uses mask == 1."""
+    mask, vertex, _ = synth.make_batch(1, vn=3, frac=0.2, sigma=0.05, seed=4, h=48, w=64)
+    lab = mask.copy()
+    lab[0, :24][lab[0, :24] == 1] = 256      # wraps to 0 under .byte()
+    lab[0, 24:][lab[0, 24:] == 1] = 2        # foreground for v3, background for == 1
+    tm, tv = torch.from_numpy(lab).to(DEV), torch.from_numpy(vertex).to(DEV)
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, 32, 0.99, seed=1, min_num=5, return_debug=True)
+    assert int(dbg["tn"][0]) == int((lab[0] == 2).sum())
+    _, _, cdbg = pv.estimate_voting_distribution_with_mean(tm, tv, out, 32, 64, min_num=5, seed=1, return_debug=True)
+    assert int(cdbg["tn"][0]) == 0
+    _check_v3_against_oracle(lab, vertex, 32, 0.99, 5, 30000, dbg["idxs"].cpu().numpy(), None, out, dbg)
+
+
+def test_host_buffers_match_device_path():
+    mask, vertex, _ = synth.make_batch(3, vn=9, frac=0.03, sigma=0.05, seed=55)
+    tm_h = torch.from_numpy(mask)
+    dev_out = pv.ransac_voting_layer_v3(tm_h.to(DEV), torch.from_numpy(vertex).to(DEV), 128, 0.99, seed=7)
+    for pin in (True, False):
+        tv_h = synth.as_net_output(vertex, pin=pin)                       # host, network layout
+        out = pv.ransac_voting_layer_v3(tm_h.pin_memory() if pin else tm_h, tv_h, 128, 0.99, seed=7)
+        assert not out.is_cuda and torch.equal(out, dev_out.cpu())
+        h2d, d2h = out.transfer_bytes
+        full = tv_h.numel() * 4
+        assert (h2d < mask.nbytes + 0.2 * full) if pin else (h2d >= mask.nbytes + full)
+    cov_d = pv.estimate_voting_distribution_with_mean(tm_h.to(DEV), torch.from_numpy(vertex).to(DEV), dev_out, 64, 128, seed=7)[1]
+    cov_h = pv.estimate_voting_distribution_with_mean(tm_h, torch.from_numpy(vertex), dev_out.cpu(), 64, 128, seed=7)[1]
+    assert torch.equal(cov_h, cov_d.cpu())
+
+
+def test_shard_invariance_and_errors():
+    """image_id_base keys the draw stream by GLOBAL image id: a shard reproduces its slice of the full batch."""
+    mask, vertex, _ = synth.make_batch(4, vn=5, frac=0.05, sigma=0.05, seed=66, h=96, w=128)
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    full = pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13)
+    part = pv.ransac_voting_layer_v3(tm[2:], tv[2:], 64, 0.99, seed=13, image_id_base=2)
+    assert torch.equal(full[2:], part)
+    with pytest.raises(ValueError):
+        pv.ransac_voting_layer_v3(tm[:, :10], tv, 64)
+    with pytest.raises(TypeError):
+        pv.ransac_voting_layer_v3(tm, tv.double(), 64)
+    # pool overflow is reported, not silent
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13, return_debug=True, pool_capacity=64)
+    assert int(dbg["status"]) & 1
+    assert pv.last_launch_count() >= 6
