@@ -100,6 +100,8 @@ typedef struct pvv_debug {
     int64_t pool_capacity; /* capacity of the pool-sized arrays above, in pixels */
     int32_t force_exact;  /* 1: disable the guard-banded fast filter, evaluate every test exactly */
     uint64_t *amb_count;  /* [1] number of tests that took the exact path */
+    float *stage_ms;      /* HOST pointer [5] or NULL: device time of compaction, hypotheses, counting, finalise and the
+                             whole call, from CUDA events on job->stream.  Setting it makes the call synchronise. */
 } pvv_debug;
 
 /* Scratch size for a job (depends on b,h,w,vn,hn_total,max_num,pool_capacity only). */

@@ -33,6 +33,7 @@ class Debug(C.Structure):
         ("idxs", C.c_void_p), ("hyp", C.c_void_p), ("counts", C.c_void_p), ("win_idx", C.c_void_p),
         ("win_count", C.c_void_p), ("win_pts", C.c_void_p), ("win_inlier", C.c_void_p), ("normal_eq", C.c_void_p),
         ("status", C.c_void_p), ("pool_capacity", C.c_int64), ("force_exact", C.c_int32), ("amb_count", C.c_void_p),
+        ("stage_ms", C.c_void_p),
     ]
 
 

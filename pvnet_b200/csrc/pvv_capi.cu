@@ -111,8 +111,31 @@ pvv_dims make_dims(const pvv_job *j)
     return d;
 }
 
+// optional per-stage device timing (pvv_debug.stage_ms): events on the job's stream, read back after a sync
+struct stage_timer {
+    cudaEvent_t ev[5];
+    float *out;
+    cudaStream_t st;
+    int n;
+    stage_timer(const pvv_debug *dbg, cudaStream_t s) : out(dbg ? dbg->stage_ms : nullptr), st(s), n(0)
+    {
+        if (out) for (int i = 0; i < 5; ++i) cudaEventCreate(&ev[i]);
+    }
+    void mark() { if (out && n < 5) cudaEventRecord(ev[n++], st); }
+    void finish()
+    {
+        if (!out) return;
+        cudaEventSynchronize(ev[n - 1]);
+        for (int i = 0; i + 1 < n; ++i) cudaEventElapsedTime(&out[i], ev[i], ev[i + 1]);
+        cudaEventElapsedTime(&out[4], ev[0], ev[n - 1]);
+        for (int i = 0; i < 5; ++i) cudaEventDestroy(ev[i]);
+        out = nullptr;
+    }
+    ~stage_timer() { if (out) for (int i = 0; i < 5; ++i) cudaEventDestroy(ev[i]); }
+};
+
 // shared front half of pvv_v3 / pvv_cov: compaction -> hypotheses -> fused counting
-int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *ws_out, int *launches)
+int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *ws_out, int *launches, stage_timer &tm)
 {
     const int v = validate(j);
     if (v != PVV_OK) return v;
@@ -125,9 +148,13 @@ int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *w
     const pvv_dims d = make_dims(j);
     cudaError_t e = cudaMemsetAsync(j->workspace, 0, L.zero_bytes, st);
     if (e) return fail_cuda(e);
+    tm.mark();
     if ((e = pvv_launch_compact(d, j->mask, j->vertex, j->selection, ws, st, launches))) return fail_cuda(e);
+    tm.mark();
     if ((e = pvv_launch_hypotheses(d, j->idxs, ws, dbg ? dbg->hyp : nullptr, st, launches))) return fail_cuda(e);
+    tm.mark();
     if ((e = pvv_launch_count(d, ws, dbg ? dbg->force_exact : 0, st, launches))) return fail_cuda(e);
+    tm.mark();
     *d_out = d;
     *ws_out = ws;
     return PVV_OK;
@@ -161,11 +188,15 @@ int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, co
     int launches = 0;
     pvv_dims d;
     pvv_ws ws;
-    const int r = run_front(job, dbg, &d, &ws, &launches);
+    if (!job) return PVV_ERR_INVALID;
+    stage_timer tm(dbg, (cudaStream_t)job->stream);
+    const int r = run_front(job, dbg, &d, &ws, &launches, tm);
     if (r != PVV_OK) return r;
     cudaStream_t st = (cudaStream_t)job->stream;
     cudaError_t e;
     if ((e = pvv_launch_v3_finalize(d, ws, out_kp, dbg, st, &launches))) return fail_cuda(e);
+    tm.mark();
+    tm.finish();
     if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
     t_last_launches = launches;
     return PVV_OK;
@@ -177,11 +208,15 @@ int pvv_cov(const pvv_job *job, const float *mean, float *out_cov, const pvv_deb
     int launches = 0;
     pvv_dims d;
     pvv_ws ws;
-    const int r = run_front(job, dbg, &d, &ws, &launches);
+    if (!job) return PVV_ERR_INVALID;
+    stage_timer tm(dbg, (cudaStream_t)job->stream);
+    const int r = run_front(job, dbg, &d, &ws, &launches, tm);
     if (r != PVV_OK) return r;
     cudaStream_t st = (cudaStream_t)job->stream;
     cudaError_t e;
     if ((e = pvv_launch_cov_finalize(d, ws, mean, out_cov, st, &launches))) return fail_cuda(e);
+    tm.mark();
+    tm.finish();
     if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
     t_last_launches = launches;
     return PVV_OK;
