@@ -100,7 +100,7 @@ def _alloc_debug(job, dev, b, vn, hn, want_pool):
 
 
 def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_num, max_num, idxs, selection, seed,
-         image_id_base, return_debug, force_exact, pool_capacity):
+         image_id_base, return_debug, force_exact, pool_capacity, stage_ms=None):
     L = _lib.lib()
     b, h, w, vn, _ = vertex.shape
     fg_rule = _lib.FG_BYTE if kind == "v3" else _lib.FG_EQ1
@@ -150,6 +150,12 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
             d, dbg_t = _alloc_debug(job, dev, b, vn, hn_total, want_pool=return_debug)
             d.force_exact = 1 if force_exact else 0
             dbg_ref = C.byref(d)
+        elif stage_ms is not None:
+            d = _lib.Debug()
+            dbg_ref = C.byref(d)
+        if stage_ms is not None:
+            buf = (C.c_float * 5)()
+            d.stage_ms = C.cast(buf, C.c_void_p)
         if kind == "v3":
             st = L.pvv_v3(C.byref(job), float(confidence), int(max_iter), out.data_ptr(), dbg_ref)
         else:
@@ -157,6 +163,8 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
             st = L.pvv_cov(C.byref(job), mean_d.data_ptr(), out.data_ptr(), dbg_ref)
         _lib.check(st, f"pvv_{kind}")
         ws.record_stream(torch.cuda.current_stream(dev))
+        if stage_ms is not None:
+            stage_ms.append(dict(zip(("compact", "hypotheses", "count", "finalize", "total"), list(buf))))
     if return_debug:
         dbg_t["seed"] = seed
         return out, dbg_t
@@ -165,25 +173,25 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
 
 def ransac_voting_layer_v3(mask, vertex, round_hyp_num, inlier_thresh=0.99, confidence=0.99, max_iter=100,
                            min_num=100, max_num=30000, *, idxs=None, selection=None, seed=None, image_id_base=0,
-                           return_debug=False, force_exact=False, pool_capacity=None):
+                           return_debug=False, force_exact=False, pool_capacity=None, stage_ms=None):
     """mask [b,h,w] (any integer dtype), vertex [b,h,w,vn,2] float32 (any strides) -> keypoints [b,vn,2] float32.
 
     Reference: ransac_voting_gpu.py:520-604.  Images with fewer than `min_num` foreground pixels give zeros; images
     with more than `max_num` are Bernoulli-subsampled.  `confidence` / `max_iter` are accepted but cannot change the
     result: the reference draws idxs once (:553) and re-votes the same hypotheses every round."""
     return _run("v3", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
-                selection, seed, image_id_base, return_debug, force_exact, pool_capacity)
+                selection, seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms)
 
 
 def estimate_voting_distribution_with_mean(mask, vertex, mean, round_hyp_num=256, min_hyp_num=4096, topk=128,
                                            inlier_thresh=0.99, min_num=20, max_num=30000, output_hyp=False, *,
                                            idxs=None, selection=None, seed=None, image_id_base=0, return_debug=False,
-                                           force_exact=False, pool_capacity=None):
+                                           force_exact=False, pool_capacity=None, stage_ms=None):
     """-> (mean, cov [b,vn,2,2]).  Reference: ransac_voting_gpu.py:333-406 (`topk`, `output_hyp` are ignored there too).
     `idxs`, when injected, is int32 [b, rounds, round_hyp_num, vn, 2] with rounds = ceil(min_hyp_num/round_hyp_num)."""
     rounds = int(math.ceil(min_hyp_num / round_hyp_num))
     r = _run("cov", mask, vertex, mean, rounds * round_hyp_num, inlier_thresh, 0.0, 0, min_num, max_num, idxs, selection,
-             seed, image_id_base, return_debug, force_exact, pool_capacity)
+             seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms)
     if return_debug:
         return mean, r[0], r[1]
     return mean, r
