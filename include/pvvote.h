@@ -161,6 +161,8 @@ int pvv_make_selection(uint64_t seed, int64_t image_id_base, int b, int h, int w
 
 /* FP32 roofline probe: runs an FFMA-only kernel for `iters` and returns achieved TFLOP/s (0 on error). */
 double pvv_fp32_peak_tflops(int iters, void *stream);
+/* diagnostic: kind 0 = scalar FFMA chains (same as above), kind 1 = packed fma.rn.f32x2 chains */
+double pvv_probe_tflops(int kind, int iters, void *stream);
 
 /* Number of kernel launches the last pvv_v3 / pvv_cov call on this thread enqueued. */
 int pvv_last_launch_count(void);

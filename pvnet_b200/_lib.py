@@ -41,7 +41,7 @@ class Debug(C.Structure):
 SYMBOLS = [
     "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_cov", "pvv_workspace_bytes_host",
     "pvv_v3_host", "pvv_cov_host", "pvv_generate_hypothesis", "pvv_voting_for_hypothesis", "pvv_vote_counts",
-    "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
+    "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_probe_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
     "pvv_version",
 ]
 
@@ -75,6 +75,8 @@ def lib():
     L.pvv_make_selection.argtypes = [C.c_uint64, C.c_int64, I, I, I, V, V]
     L.pvv_fp32_peak_tflops.argtypes = [I, V]
     L.pvv_fp32_peak_tflops.restype = C.c_double
+    L.pvv_probe_tflops.argtypes = [I, I, V]
+    L.pvv_probe_tflops.restype = C.c_double
     L.pvv_version.restype = C.c_char_p
     _lib = L
     return L

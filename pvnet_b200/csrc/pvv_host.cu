@@ -180,6 +180,30 @@ __global__ void __launch_bounds__(256) k_ffma_probe(float *out, int iters, float
     if (s == 12345.678f) out[0] = s;  // never true in practice; keeps the chains alive
 }
 
+// packed variant: fma.rn.f32x2 (FFMA2 in SASS), two FMAs per instruction and thread
+__global__ void __launch_bounds__(256) k_ffma2_probe(float *out, int iters, float a, float b)
+{
+    unsigned long long r[8], av, bv;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(av) : "f"(a));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(bv) : "f"(b));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float x = threadIdx.x + i;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(r[i]) : "f"(x));
+    }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(r[k]) : "l"(av), "l"(bv));
+        }
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s ^= r[i];
+    if (s == 0x123456789ull) out[0] = 1.f;
+}
+
 }  // namespace
 
 extern "C" {
@@ -222,7 +246,10 @@ int pvv_make_selection(uint64_t seed, int64_t image_id_base, int b, int h, int w
     return cudaGetLastError() == cudaSuccess ? PVV_OK : PVV_ERR_CUDA;
 }
 
-double pvv_fp32_peak_tflops(int iters, void *stream)
+double pvv_probe_tflops(int kind, int iters, void *stream);
+double pvv_fp32_peak_tflops(int iters, void *stream) { return pvv_probe_tflops(0, iters, stream); }
+
+double pvv_probe_tflops(int kind, int iters, void *stream)
 {
     cudaStream_t st = (cudaStream_t)stream;
     int dev = 0, sms = 148;
@@ -235,16 +262,19 @@ double pvv_fp32_peak_tflops(int iters, void *stream)
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const int blocks = sms * 8;
-    k_ffma_probe<<<blocks, 256, 0, st>>>(out, 64, 1.0000001f, 1e-9f);  // warm-up
+    const double per_instr = kind == 1 ? 4.0 : 2.0;
+    if (kind == 1) k_ffma2_probe<<<blocks, 256, 0, st>>>(out, 64, 1.0000001f, 1e-9f);
+    else k_ffma_probe<<<blocks, 256, 0, st>>>(out, 64, 1.0000001f, 1e-9f);  // warm-up
     double best = 0.0;
     for (int rep = 0; rep < 3; ++rep) {
         cudaEventRecord(e0, st);
-        k_ffma_probe<<<blocks, 256, 0, st>>>(out, iters, 1.0000001f, 1e-9f);
+        if (kind == 1) k_ffma2_probe<<<blocks, 256, 0, st>>>(out, iters, 1.0000001f, 1e-9f);
+        else k_ffma_probe<<<blocks, 256, 0, st>>>(out, iters, 1.0000001f, 1e-9f);
         cudaEventRecord(e1, st);
         if (cudaEventSynchronize(e1) != cudaSuccess) { best = 0.0; break; }
         float ms = 0.f;
         cudaEventElapsedTime(&ms, e0, e1);
-        const double flop = 2.0 * 8 * 16 * (double)iters * 256.0 * blocks;
+        const double flop = per_instr * 8 * 16 * (double)iters * 256.0 * blocks;
         const double tf = flop / (ms * 1e-3) / 1e12;
         if (tf > best) best = tf;
     }

@@ -13,6 +13,8 @@
 //     tau = t/sqrt(1-t^2): 4 FFMA + 2 FSETP per test.  Tests that fall inside the band (|a-|c'|| <= eps_rel*a+eps_abs)
 //     are re-evaluated with the reference's exact rounding sequence (pvv_exact_test), which makes the counts
 //     bit-identical to the reference kernel's (error analysis in DESIGN.md "Guard band").
+#include <stdlib.h>
+
 #include "pvv_internal.cuh"
 
 namespace {
@@ -53,8 +55,6 @@ __global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *i
 }
 
 // ---- K3 -------------------------------------------------------------------------------------------
-constexpr int kCountThreads = 128;
-
 struct band_consts {
     float tau;        // t / sqrt(1 - t^2)
     float erel;       // relative half-width of the band (in units of a)
@@ -62,14 +62,68 @@ struct band_consts {
     float abs_floor;  // catches ||d|| < 1e-6 (reference skips those)
 };
 
-template <int H, bool EXACT>
-__global__ void __launch_bounds__(kCountThreads) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
+constexpr int K3_QCAP = 1024;  // deferred (thread, pixel) entries per work item; overflow is resolved in line
+
+// Hypothesis in the chunk-local frame and its absolute band term.  Used verbatim by the hot loop's set-up and by
+// the deferred pass, so both see bit-identical band tests (explicit _rn intrinsics: nothing may be re-contracted).
+__device__ __forceinline__ void k3_local_hyp(float hxr, float hyr, int ox, int oy, float P, const band_consts &bc,
+                                             float &hx, float &hy, float &eabs)
 {
-    __shared__ float4 sA[PVV_CHUNK_PX];   // n^x, n^y, -s, tau*n^y
-    __shared__ float2 sB[PVV_CHUNK_PX];   // -tau*n^x, -tau*s2
-    __shared__ float2 sD[PVV_CHUNK_PX];   // raw direction
+    hx = __fsub_rn(hxr, (float)ox);
+    hy = __fsub_rn(hyr, (float)oy);
+    const float m = __fadd_rn(__fadd_rn(fabsf(hx), fabsf(hy)), P);
+    if (m < 1e15f) {
+        eabs = __fmaf_rn(bc.kabs, m, bc.abs_floor);
+    } else {
+        // far-away / non-finite hypothesis: every test takes the exact path (the reference's overflow behaviour);
+        // finite stand-ins keep NaN out of the sign-bit counting
+        hx = 0.f; hy = 0.f; eabs = __int_as_float(0x7f800000);
+    }
+}
+
+// e = a - |c'| and the band half-width t1 for one test; A = {n^x, n^y, -s, tau n^y}, Q = {-tau n^x, -tau s2, ., .}
+__device__ __forceinline__ void k3_band(float hx, float hy, float eabs, float erel, const float4 &A, const float4 &Q,
+                                        float &e, float &t1)
+{
+    const float a = __fmaf_rn(hx, A.x, __fmaf_rn(hy, A.y, A.z));
+    const float c = __fmaf_rn(hx, A.w, __fmaf_rn(hy, Q.x, Q.y));
+    e = __fsub_rn(a, fabsf(c));
+    t1 = __fmaf_rn(erel, a, eabs);
+}
+
+// Exact re-evaluation of the tests of thread `t` at pixel `j` that fell inside the guard band.  The hot loop counted
+// those as "not inlier"; here they get the reference's exact decision, added straight to the global counts.
+template <int H, int THREADS>
+__device__ __forceinline__ void k3_resolve_one(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, long long row,
+                                               int hbase, int t, int j, int ox, int oy, float P, float4 A, float4 Q,
+                                               uint32_t xy, unsigned long long *amb)
+{
+    const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
+    const float n1 = pvv_norm1(Q.z, Q.w);
+#pragma unroll
+    for (int k = 0; k < H; ++k) {
+        const int h = hbase + k * THREADS + t;
+        if (h >= d.hn) continue;
+        const float2 hv = ws.hyp[row + h];
+        float hx, hy, eabs, e, t1;
+        k3_local_hyp(hv.x, hv.y, ox, oy, P, bc, hx, hy, eabs);
+        k3_band(hx, hy, eabs, bc.erel, A, Q, e, t1);
+        if (!(fabsf(e) > t1)) {
+            if (pvv_exact_test(Q.z, Q.w, n1, cx, cy, hv.x, hv.y, d.thresh)) atomicAdd(&ws.counts[row + h], 1);
+            ++*amb;
+        }
+    }
+}
+
+
+template <int H, int THREADS, bool EXACT>
+__global__ void __launch_bounds__(THREADS) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
+{
+    // per pixel two float4: {n^x, n^y, -s, tau*n^y} and {-tau*n^x, -tau*s2, raw dir.x, raw dir.y}
+    __shared__ float4 sP[2 * PVV_CHUNK_PX];
     __shared__ uint32_t sXY[PVV_CHUNK_PX];
-    __shared__ int s_item, s_P;
+    __shared__ uint32_t s_q[EXACT ? 1 : K3_QCAP];
+    __shared__ int s_item, s_P, s_qn;
 
     const int tid = threadIdx.x;
     const int total_items = ws.chunk_start[d.b] * d.vn;
@@ -96,12 +150,13 @@ __global__ void __launch_bounds__(kCountThreads) k_count(pvv_dims d, pvv_ws ws, 
         const int ox = (int)(xy0 & 0xffffu), oy = (int)(xy0 >> 16);
 
         // ---- stage the chunk: raw values + derived constants in a chunk-local frame ----
-        for (int j = tid; j < n; j += kCountThreads) {
+        for (int j = tid; j < n; j += THREADS) {
             const uint32_t xy = ws.pix_xy[off + p0 + j];
             const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + p0 + j];
             sXY[j] = xy;
-            sD[j] = dir;
-            if (!EXACT) {
+            if (EXACT) {
+                sP[2 * j + 1] = make_float4(0.f, 0.f, dir.x, dir.y);
+            } else {
                 const float n1 = pvv_norm1(dir.x, dir.y);
                 float4 A;
                 float2 B;
@@ -120,83 +175,84 @@ __global__ void __launch_bounds__(kCountThreads) k_count(pvv_dims d, pvv_ws ws, 
                     B.y = (float)(-((double)px * A.w + (double)py * B.x));
                     atomicMax(&s_P, abs(px) + abs(py));
                 }
-                sA[j] = A;
-                sB[j] = B;
+                sP[2 * j] = A;
+                sP[2 * j + 1] = make_float4(B.x, B.y, dir.x, dir.y);
             }
         }
         __syncthreads();
         const float P = (float)s_P;
         const long long row = ((long long)img * d.vn + vi) * ws.hn_pad;
 
-        for (int hbase = 0; hbase < d.hn; hbase += kCountThreads * H) {
-            if (hbase + (tid & ~31) >= d.hn) continue;  // warp-uniform: this warp has no hypothesis in the pass
-            float hxr[H], hyr[H];
-            int cnt[H];
-#pragma unroll
-            for (int k = 0; k < H; ++k) {
-                const int h = hbase + k * kCountThreads + tid;
-                const float2 hv = h < d.hn ? ws.hyp[row + h] : make_float2(0.f, 0.f);
-                hxr[k] = hv.x; hyr[k] = hv.y; cnt[k] = 0;
-            }
-            if (EXACT) {
-                for (int j = 0; j < n; ++j) {
-                    const uint32_t xy = sXY[j];
-                    const float2 dir = sD[j];
-                    const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
-                    const float n1 = pvv_norm1(dir.x, dir.y);
-#pragma unroll
-                    for (int k = 0; k < H; ++k) cnt[k] += pvv_exact_test(dir.x, dir.y, n1, cx, cy, hxr[k], hyr[k], d.thresh);
-                }
-            } else {
-                float hx[H], hy[H], eabs[H];
+        for (int hbase = 0; hbase < d.hn; hbase += THREADS * H) {
+            const bool active = hbase + (tid & ~31) < d.hn;  // warp-uniform: does this warp own hypotheses in the pass
+            if (tid == 0) s_qn = 0;
+            __syncthreads();
+            if (active) {
+                float hxr[H], hyr[H];
+                int cnt[H];
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
-                    hx[k] = hxr[k] - (float)ox;
-                    hy[k] = hyr[k] - (float)oy;
-                    const float m = fabsf(hx[k]) + fabsf(hy[k]) + P;
-                    // far-away / non-finite hypotheses: always take the exact path (overflow behaviour of the reference)
-                    eabs[k] = (m < 1e15f) ? fmaf(bc.kabs, m, bc.abs_floor) : __int_as_float(0x7f800000);
+                    const int h = hbase + k * THREADS + tid;
+                    const float2 hv = h < d.hn ? ws.hyp[row + h] : make_float2(0.f, 0.f);
+                    hxr[k] = hv.x; hyr[k] = hv.y; cnt[k] = 0;
                 }
-#pragma unroll 2
-                for (int j = 0; j < n; ++j) {
-                    const float4 A = sA[j];
-                    const float2 B = sB[j];
-                    bool amb = false;
-                    bool ambk[H];
-#pragma unroll
-                    for (int k = 0; k < H; ++k) {
-                        const float a = fmaf(hx[k], A.x, fmaf(hy[k], A.y, A.z));
-                        const float c = fmaf(hx[k], A.w, fmaf(hy[k], B.x, B.y));
-                        const float e = a - fabsf(c);
-                        const float t1 = fmaf(bc.erel, a, eabs[k]);
-                        ambk[k] = fabsf(e) <= t1;
-                        amb |= ambk[k];
-                        cnt[k] += (e > t1) ? 1 : 0;
-                    }
-                    if (amb) {
+                if (EXACT) {
+                    for (int j = 0; j < n; ++j) {
                         const uint32_t xy = sXY[j];
-                        const float2 dir = sD[j];
+                        const float4 q = sP[2 * j + 1];
                         const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
-                        const float n1 = pvv_norm1(dir.x, dir.y);
+                        const float n1 = pvv_norm1(q.z, q.w);
 #pragma unroll
-                        for (int k = 0; k < H; ++k)
-                            if (ambk[k]) {
-                                cnt[k] += pvv_exact_test(dir.x, dir.y, n1, cx, cy, hxr[k], hyr[k], d.thresh);
-                                ++amb_local;
-                            }
+                        for (int k = 0; k < H; ++k) cnt[k] += pvv_exact_test(q.z, q.w, n1, cx, cy, hxr[k], hyr[k], d.thresh);
                     }
+                } else {
+                    float hx[H], hy[H], eabs[H];
+#pragma unroll
+                    for (int k = 0; k < H; ++k) k3_local_hyp(hxr[k], hyr[k], ox, oy, P, bc, hx[k], hy[k], eabs[k]);
+                    const float4 *pp = sP;
+                    const float4 *const pend = sP + 2 * n;
+#pragma unroll 4
+                    for (; pp < pend; pp += 2) {
+                        const float4 A = pp[0];
+                        const float4 Q = pp[1];
+                        bool clear = true;
+#pragma unroll
+                        for (int k = 0; k < H; ++k) {
+                            float e, t1;
+                            k3_band(hx[k], hy[k], eabs[k], bc.erel, A, Q, e, t1);
+                            const float g = __fsub_rn(t1, e);             // < 0  <=>  e > t1: definitely an inlier
+                            cnt[k] += (int)(__float_as_uint(g) >> 31);    // NaN cannot reach here (k3_local_hyp)
+                            clear = clear && (fabsf(e) > t1);
+                        }
+                        if (!clear) {
+                            // some test of this (thread, pixel) fell inside the guard band: defer it to the dense
+                            // exact pass below (the hot loop stays divergence-free)
+                            const int j = (int)(pp - sP) >> 1;
+                            const int q = atomicAdd(&s_qn, 1);
+                            if (q < K3_QCAP) s_q[q] = ((uint32_t)j << 16) | (uint32_t)tid;
+                            else k3_resolve_one<H, THREADS>(d, ws, bc, row, hbase, tid, j, ox, oy, P, A, Q, sXY[j], &amb_local);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < H; ++k) {
+                    const int h = hbase + k * THREADS + tid;
+                    if (h < d.hn && cnt[k]) atomicAdd(&ws.counts[row + h], cnt[k]);
                 }
             }
-#pragma unroll
-            for (int k = 0; k < H; ++k) {
-                const int h = hbase + k * kCountThreads + tid;
-                if (h < d.hn && cnt[k]) atomicAdd(&ws.counts[row + h], cnt[k]);
+            __syncthreads();
+            if (!EXACT) {
+                const int qn = min(s_qn, K3_QCAP);
+                for (int e = tid; e < qn; e += THREADS) {
+                    const uint32_t ent = s_q[e];
+                    const int j = (int)(ent >> 16), t = (int)(ent & 0xffffu);
+                    k3_resolve_one<H, THREADS>(d, ws, bc, row, hbase, t, j, ox, oy, P, sP[2 * j], sP[2 * j + 1], sXY[j], &amb_local);
+                }
             }
         }
     }
     if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
 }
-
 }  // namespace
 
 cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out,
@@ -217,14 +273,26 @@ static bool pvv_band_for(float t, band_consts *bc)
     const double td = (double)t;
     const double one_m = 1.0 - td * td;
     const double tau = td / sqrt(one_m);
-    const double eq = (8.0 + 4.0 / td) * u;         // bound on the relative rounding error of the reference's quotient
+    // first-order bound on the relative rounding error of the reference's quotient num/(n1*n2):
+    // n1, n2: 2u each (fma + sqrt), den: +u, num: (1 + 1/t)u (no cancellation near the threshold), div: +u
+    const double eq = (7.0 + 1.0 / td) * u;
     const double etau = eq / one_m;                 // induced relative uncertainty of tau
     if (etau > 0.05) return false;
     bc->tau = (float)tau;
-    bc->erel = (float)(1.5 * etau / (1.0 - etau) + 8.0 * u);
+    bc->erel = (float)(1.10 * etau / (1.0 - etau) + 8.0 * u);
     bc->kabs = (float)(8.0 * u * (1.0 + tau) * (1.0 + etau));
     bc->abs_floor = (float)(4e-6 * (1.0 + tau));
     return true;
+}
+
+template <int H, int THREADS, bool EXACT>
+static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st)
+{
+    int per_sm = 8;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS, EXACT>, THREADS, 0);
+    if (per_sm < 1) per_sm = 1;
+    k_count<H, THREADS, EXACT><<<sms * per_sm, THREADS, 0, st>>>(d, ws, bc);
+    return cudaGetLastError();
 }
 
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches)
@@ -234,16 +302,14 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {0.f, 0.f, 0.f, 0.f};
     const bool fast = !force_exact && pvv_band_for(d.thresh, &bc);
-    int per_sm = 8;
-    if (fast) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<4, false>, kCountThreads, 0);
-        if (per_sm < 1) per_sm = 1;
-        k_count<4, false><<<sms * per_sm, kCountThreads, 0, st>>>(d, ws, bc);
-    } else {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<4, true>, kCountThreads, 0);
-        if (per_sm < 1) per_sm = 1;
-        k_count<4, true><<<sms * per_sm, kCountThreads, 0, st>>>(d, ws, bc);
-    }
+    const char *venv = getenv("PVV_K3_VARIANT");  // tuning knob for experiments
+    const int variant = venv ? atoi(venv) : 0;
+    cudaError_t e;
+    if (!fast) e = launch_count_t<4, 128, true>(d, ws, bc, sms, st);
+    else if (variant == 1) e = launch_count_t<8, 64, false>(d, ws, bc, sms, st);
+    else if (variant == 2) e = launch_count_t<8, 128, false>(d, ws, bc, sms, st);
+    else if (variant == 3) e = launch_count_t<2, 256, false>(d, ws, bc, sms, st);
+    else e = launch_count_t<4, 128, false>(d, ws, bc, sms, st);
     ++*launches;
-    return cudaGetLastError();
+    return e;
 }

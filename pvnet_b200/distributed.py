@@ -1,0 +1,66 @@
+"""Multi-GPU voting: shard by image, no data-path collective, one packed gather at the end.
+
+The reference's only parallel strategy is single-process torch.nn.DataParallel over the batch dimension
+(tools/train_linemod.py:222-223): scatter images to GPUs, gather the [b,vn,2] keypoints on GPU 0.  Here it is one
+process per GPU (torchrun), each rank votes on its own contiguous slice of the batch, and ONE collective
+(all_gather_into_tensor over NCCL/NVLink; gloo in the CPU tests) assembles keypoints (+ covariances) on every rank.
+Images are independent, so there is no exchange step inside the path; the draw streams are keyed by the GLOBAL image
+id (pvv_job.image_id_base), which makes results independent of the number of ranks.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(global_b: int, world: int, rank: int):
+    """Contiguous partition of [0, global_b): the first (global_b % world) ranks get one extra image."""
+    base, rem = divmod(global_b, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def gather_packed(local: torch.Tensor, global_b: int, group=None) -> torch.Tensor:
+    """local [b_local, ...] float32 on every rank (contiguous partition by shard_bounds) -> [global_b, ...] on every rank.
+    Uneven shards are padded to the largest shard so that a single all_gather_into_tensor is enough."""
+    world = dist.get_world_size(group)
+    if world == 1:
+        return local
+    per = -(-global_b // world)
+    tail = tuple(local.shape[1:])
+    send = local
+    if local.shape[0] != per:
+        send = torch.zeros((per,) + tail, dtype=local.dtype, device=local.device)
+        send[: local.shape[0]] = local
+    recv = torch.empty((world * per,) + tail, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(recv, send.contiguous(), group=group)
+    if global_b % world == 0:
+        return recv
+    parts = []
+    for r in range(world):
+        lo, hi = shard_bounds(global_b, world, r)
+        parts.append(recv[r * per: r * per + (hi - lo)])
+    return torch.cat(parts, 0)
+
+
+def ransac_voting_layer_v3_sharded(mask_local, vertex_local, round_hyp_num, global_b, *, group=None, seed=0,
+                                   with_cov=False, cov_kwargs=None, vote_fn=None, cov_fn=None, **kwargs):
+    """Each rank passes ITS slice (shard_bounds) of the batch.  Returns keypoints [global_b,vn,2] (and, with
+    with_cov=True, covariances [global_b,vn,2,2] from estimate_voting_distribution_with_mean) on every rank.
+    `vote_fn` / `cov_fn` default to the CUDA entry points; the CPU tests inject stand-ins to exercise the plumbing."""
+    if vote_fn is None or (with_cov and cov_fn is None):
+        from . import ransac_voting_gpu as pv
+        vote_fn = vote_fn or pv.ransac_voting_layer_v3
+        cov_fn = cov_fn or pv.estimate_voting_distribution_with_mean
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    lo, hi = shard_bounds(global_b, world, rank)
+    if mask_local.shape[0] != hi - lo:
+        raise ValueError(f"rank {rank} owns images [{lo},{hi}) but was given {mask_local.shape[0]}")
+    kp = vote_fn(mask_local, vertex_local, round_hyp_num, seed=seed, image_id_base=lo, **kwargs)
+    if not with_cov:
+        return gather_packed(kp, global_b, group) if world > 1 else kp
+    _, cov = cov_fn(mask_local, vertex_local, kp, seed=seed + 1, image_id_base=lo, **(cov_kwargs or {}))
+    packed = torch.cat([kp, cov.reshape(cov.shape[0], cov.shape[1], 4)], 2)  # [b_local, vn, 6]: one collective
+    full = gather_packed(packed, global_b, group) if world > 1 else packed
+    return full[:, :, :2].contiguous(), full[:, :, 2:].reshape(full.shape[0], full.shape[1], 2, 2)
