@@ -62,6 +62,7 @@ struct band_consts {
     float abs_floor;  // catches ||d|| < 1e-6 (reference skips those)
 };
 
+constexpr int K3_GROUP = 4;   // pixels per band-check group in the hot loop (PVV_CHUNK_PX is a multiple)
 constexpr int K3_QCAP = 1024;  // deferred (thread, pixel) entries per work item; overflow is resolved in line
 
 // Hypothesis in the chunk-local frame and its absolute band term.  Used verbatim by the hot loop's set-up and by
@@ -179,6 +180,13 @@ __global__ void __launch_bounds__(THREADS) k_count(pvv_dims d, pvv_ws ws, band_c
                 sP[2 * j + 1] = make_float4(B.x, B.y, dir.x, dir.y);
             }
         }
+        if (!EXACT) {  // pad to a whole group with never-inlier pixels
+            const int npad = (n + K3_GROUP - 1) / K3_GROUP * K3_GROUP;
+            for (int j = n + tid; j < npad; j += THREADS) {
+                sP[2 * j] = make_float4(0.f, 0.f, -1e30f, 0.f);
+                sP[2 * j + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
         __syncthreads();
         const float P = (float)s_P;
         const long long row = ((long long)img * d.vn + vi) * ws.hn_pad;
@@ -209,28 +217,36 @@ __global__ void __launch_bounds__(THREADS) k_count(pvv_dims d, pvv_ws ws, band_c
                     float hx[H], hy[H], eabs[H];
 #pragma unroll
                     for (int k = 0; k < H; ++k) k3_local_hyp(hxr[k], hyr[k], ox, oy, P, bc, hx[k], hy[k], eabs[k]);
+                    // groups of K3_GROUP pixels share one band check / one (rare) branch
                     const float4 *pp = sP;
                     const float4 *const pend = sP + 2 * n;
-#pragma unroll 4
-                    for (; pp < pend; pp += 2) {
-                        const float4 A = pp[0];
-                        const float4 Q = pp[1];
+                    for (; pp < pend; pp += 2 * K3_GROUP) {
                         bool clear = true;
 #pragma unroll
-                        for (int k = 0; k < H; ++k) {
-                            float e, t1;
-                            k3_band(hx[k], hy[k], eabs[k], bc.erel, A, Q, e, t1);
-                            const float g = __fsub_rn(t1, e);             // < 0  <=>  e > t1: definitely an inlier
-                            cnt[k] += (int)(__float_as_uint(g) >> 31);    // NaN cannot reach here (k3_local_hyp)
-                            clear = clear && (fabsf(e) > t1);
+                        for (int u = 0; u < K3_GROUP; ++u) {
+                            const float4 A = pp[2 * u];
+                            const float4 Q = pp[2 * u + 1];
+#pragma unroll
+                            for (int k = 0; k < H; ++k) {
+                                float e, t1;
+                                k3_band(hx[k], hy[k], eabs[k], bc.erel, A, Q, e, t1);
+                                const float g = __fsub_rn(t1, e);             // < 0  <=>  e > t1: definitely an inlier
+                                cnt[k] += (int)(__float_as_uint(g) >> 31);    // NaN cannot reach here (k3_local_hyp)
+                                clear = clear && (fabsf(e) > t1);
+                            }
                         }
                         if (!clear) {
-                            // some test of this (thread, pixel) fell inside the guard band: defer it to the dense
-                            // exact pass below (the hot loop stays divergence-free)
-                            const int j = (int)(pp - sP) >> 1;
+                            // some test of this (thread, pixel group) fell inside the guard band: defer the group to the
+                            // dense exact pass below (the hot loop stays divergence-free)
+                            const int grp = (int)(pp - sP) / (2 * K3_GROUP);
                             const int q = atomicAdd(&s_qn, 1);
-                            if (q < K3_QCAP) s_q[q] = ((uint32_t)j << 16) | (uint32_t)tid;
-                            else k3_resolve_one<H, THREADS>(d, ws, bc, row, hbase, tid, j, ox, oy, P, A, Q, sXY[j], &amb_local);
+                            if (q < K3_QCAP) {
+                                s_q[q] = ((uint32_t)grp << 16) | (uint32_t)tid;
+                            } else {
+                                for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j)
+                                    k3_resolve_one<H, THREADS>(d, ws, bc, row, hbase, tid, j, ox, oy, P, sP[2 * j], sP[2 * j + 1],
+                                                               sXY[j], &amb_local);
+                            }
                         }
                     }
                 }
@@ -245,8 +261,10 @@ __global__ void __launch_bounds__(THREADS) k_count(pvv_dims d, pvv_ws ws, band_c
                 const int qn = min(s_qn, K3_QCAP);
                 for (int e = tid; e < qn; e += THREADS) {
                     const uint32_t ent = s_q[e];
-                    const int j = (int)(ent >> 16), t = (int)(ent & 0xffffu);
-                    k3_resolve_one<H, THREADS>(d, ws, bc, row, hbase, t, j, ox, oy, P, sP[2 * j], sP[2 * j + 1], sXY[j], &amb_local);
+                    const int grp = (int)(ent >> 16), t = (int)(ent & 0xffffu);
+                    for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j)
+                        k3_resolve_one<H, THREADS>(d, ws, bc, row, hbase, t, j, ox, oy, P, sP[2 * j], sP[2 * j + 1], sXY[j],
+                                                   &amb_local);
                 }
             }
         }
