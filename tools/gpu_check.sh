@@ -1,0 +1,22 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, bench (plain), ncu launch list and one full capture of the top kernel.
+# Usage under gpurun:  bash tools/gpu_check.sh [tag]
+set -u
+TAG=${1:-r01}
+OUT=gpurun_out
+mkdir -p $OUT
+nvidia-smi --query-gpu=index,name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/${TAG}_smi.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1
+echo "pytest exit $?" | tee -a $OUT/${TAG}_pytest.log
+tail -5 $OUT/${TAG}_pytest.log
+timeout 300 python __graft_entry__.py smoke > $OUT/${TAG}_smoke.log 2>&1; echo "smoke exit $?"; tail -2 $OUT/${TAG}_smoke.log
+timeout 600 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench exit $?"; cat $OUT/${TAG}_bench.json
+timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_ref.json 2> $OUT/${TAG}_bench_ref.err; echo "ref exit $?"; cat $OUT/${TAG}_bench_ref.json
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e"
+timeout 300 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu1.log 2>&1
+echo "ncu launches exit $?"
+timeout 300 $CMD > $OUT/${TAG}_plain2.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_count -s 3 -c 2 -f -o $OUT/${TAG}_k_count $CMD > $OUT/${TAG}_ncu2.log 2>&1
+echo "ncu full exit $?"
+ls -la $OUT

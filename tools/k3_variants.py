@@ -10,16 +10,14 @@ tm, tv = torch.from_numpy(mask).to(dev), synth.as_net_output(vertex, device=dev)
 tests = float((mask != 0).sum()) * 9 * 512
 L = _lib.lib()
 print("probe FFMA  TF:", L.pvv_probe_tflops(0, 4096, None), " FFMA2 TF:", L.pvv_probe_tflops(1, 4096, None))
-base = None
 for thresh in (0.999, 0.99):
-    for var in [int(v) for v in (sys.argv[1:] or ["0", "1", "2", "3"])]:
+    base = (thresh, pv.ransac_voting_layer_v3(tm, tv, 512, thresh, seed=0, return_debug=True, force_exact=True)[1]["counts"].clone())
+    for var in [int(v) for v in (sys.argv[1:] or ["0", "1", "2", "3", "4", "5", "6", "7"])]:
         os.environ["PVV_K3_VARIANT"] = str(var)
         st = []
         for i in range(12):
             out, dbg = pv.ransac_voting_layer_v3(tm, tv, 512, thresh, seed=0, stage_ms=st, return_debug=True)
         ms = float(np.median([s["count"] for s in st[2:]]))
         c = dbg["counts"].clone()
-        if base is None or base[0] != thresh:
-            base = (thresh, c)
         print(f"thresh {thresh} variant {var}: count {ms:.4f} ms  {tests/ms/1e9:.3f} T tests/s  amb {int(dbg['amb_count'])/tests:.2e}"
               f"  same_counts={torch.equal(c, base[1])}")
