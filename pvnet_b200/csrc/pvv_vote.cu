@@ -5,14 +5,18 @@
 //              (ransac_voting_gpu.py:563-567 / :371-374): the [hn,vn,tn] uint8 matrix is never materialised.
 //
 // K3 design (DESIGN.md "K3"):
-//   * persistent CTAs, dynamic work queue of (pixel chunk, keypoint) items;
-//   * the chunk's pixels are staged in shared memory as 6 derived floats per pixel, read back as warp-broadcast
-//     LDS.128 + LDS.64; every thread keeps H hypotheses and H integer counters in registers, so the inner loop has
-//     no atomics, no shuffles and no global traffic;
-//   * decision by a guard-banded filter in a rotated frame:  inlier  <=>  a > tau*|c|  with a = d.n^, c = d x n^,
-//     tau = t/sqrt(1-t^2): 4 FFMA + 2 FSETP per test.  Tests that fall inside the band (|a-|c'|| <= eps_rel*a+eps_abs)
-//     are re-evaluated with the reference's exact rounding sequence (pvv_exact_test), which makes the counts
-//     bit-identical to the reference kernel's (error analysis in DESIGN.md "Guard band").
+//   * persistent CTAs pull (256-pixel chunk, keypoint) items from a dynamic work queue; the raw pixels of the next
+//     item are prefetched with cp.async into a second shared-memory buffer while the current item is voted on;
+//   * per pixel, 6 derived floats turn the reference's cosine test into two half-plane tests through the pixel
+//     (cone a > tau|c|, tau = t/sqrt(1-t^2)):  e+- = hx*p + hy*q + r,  m = min(e+, e-),  inlier <=> m > 0.
+//     Pixels are stored as PAIRS so that one packed FFMA2 evaluates a term for two pixels: 2 FFMA2 + FMNMX + LEA.HI
+//     (+ half an FMNMX3 for the band) per test; every thread keeps 4 hypotheses and their counters in registers, so
+//     the inner loop has no atomics, no shuffles, no branches and no global traffic;
+//   * the filter is guard-banded: a test with |m| <= T (T bounds the filter's rounding plus the uncertainty of the
+//     reference's own fp32 quotient) only sets a bit in a per-thread mask; after the loop the flagged (hypothesis,
+//     8-pixel group) pairs are re-evaluated densely by the whole CTA and the tests truly inside the band get the
+//     reference's exact rounding sequence (pvv_exact_test).  Counts are bit-identical to the reference kernel's
+//     (error analysis in DESIGN.md "Guard band").
 #include <stdlib.h>
 
 #include "pvv_internal.cuh"
@@ -61,7 +65,7 @@ struct band_consts {
     float abs_floor;  // catches ||d|| < 1e-6 (reference skips those)
 };
 
-constexpr int K3_GROUP = 4;    // pixels per band-check group in the hot loop (two packed pixel pairs)
+constexpr int K3_GROUP = 8;    // pixels per band-check group in the hot loop (four packed pixel pairs)
 constexpr int K3_QCAP = 1024;  // deferred (thread, pixel group) entries per work item; overflow is resolved in line
 constexpr int K3_PAIRS = PVV_CHUNK_PX / 2;
 
@@ -77,12 +81,6 @@ __device__ __forceinline__ void unpk(f32x2 v, float &lo, float &hi)
 {
     asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
 }
-__device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b)
-{
-    f32x2 d;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
 __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
 {
     f32x2 d;
@@ -90,23 +88,26 @@ __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
     return d;
 }
 
-// Per-pixel constants of the filter, in the chunk-local frame (origin = first pixel of the chunk):
-//   a = hx*ax + hy*ay + az   (= d . n^)          c' = hx*cx + hy*cy + cz   (= tau * d x n^)
+// Per-pixel constants of the filter, in the chunk-local frame (origin = first pixel of the chunk).  With d = h - pixel,
+// n^ the unit direction, a = d . n^ and c = d x n^, the reference's test cos > t is the cone a > tau |c|, i.e. the
+// intersection of two half-planes through the pixel:
+//   e+ = a - tau c = hx*px + hy*py + pz > 0      and      e- = a + tau c = hx*qx + hy*qy + qz > 0,
+// so one test is two 2-FMA chains and m = min(e+, e-) = a - tau|c| carries the decision in its sign.
 // Shared-memory layout: pixel PAIRS, 12 floats (3 x LDS.128) per pair, every constant as {pixel 2q, pixel 2q+1} so
-// that one FFMA2 evaluates a term for two pixels:  [ax ax' ay ay'] [az az' cx cx'] [cy cy' cz cz'].
-struct px_consts { float ax, ay, az, cx, cy, cz; };
+// that one FFMA2 evaluates a term for two pixels:  [px px' py py'] [pz pz' qx qx'] [qy qy' qz qz'].
+struct px_consts { float px, py, pz, qx, qy, qz; };
 
 __device__ __forceinline__ px_consts k3_load_px(const float *sP, int j)
 {
     const float *q = sP + (j >> 1) * 12 + (j & 1);
     px_consts c;
-    c.ax = q[0]; c.ay = q[2]; c.az = q[4]; c.cx = q[6]; c.cy = q[8]; c.cz = q[10];
+    c.px = q[0]; c.py = q[2]; c.pz = q[4]; c.qx = q[6]; c.qy = q[8]; c.qz = q[10];
     return c;
 }
 __device__ __forceinline__ void k3_store_px(float *sP, int j, const px_consts &c)
 {
     float *q = sP + (j >> 1) * 12 + (j & 1);
-    q[0] = c.ax; q[2] = c.ay; q[4] = c.az; q[6] = c.cx; q[8] = c.cy; q[10] = c.cz;
+    q[0] = c.px; q[2] = c.py; q[4] = c.pz; q[6] = c.qx; q[8] = c.qy; q[10] = c.qz;
 }
 
 // Hypothesis in the chunk-local frame and its band half-width T (constant over the chunk: |a| <= |hx|+|hy|+P).
@@ -126,33 +127,12 @@ __device__ __forceinline__ void k3_local_hyp(float hxr, float hyr, int ox, int o
     }
 }
 
-// e = a - |c'| for one test, scalar form (the hot loop computes the same two FMA chains with FFMA2: identical bits)
-__device__ __forceinline__ float k3_e(float hx, float hy, const px_consts &c)
+// m = min(e+, e-) for one test, scalar form (the hot loop computes the same FMA chains with FFMA2: identical bits)
+__device__ __forceinline__ float k3_m(float hx, float hy, const px_consts &c)
 {
-    const float a = __fmaf_rn(hx, c.ax, __fmaf_rn(hy, c.ay, c.az));
-    const float cc = __fmaf_rn(hx, c.cx, __fmaf_rn(hy, c.cy, c.cz));
-    return __fsub_rn(a, fabsf(cc));
-}
-
-// Re-evaluation of ONE deferred test: hypothesis slot k of thread `t` at pixel `j`.  The hot loop counted every test
-// inside the guard band as "not inlier"; here those get the reference's exact decision, added straight to the global
-// counts.  The band test is recomputed from the same staged constants (sP, sH) with the same roundings as the hot loop.
-template <int THREADS>
-__device__ __forceinline__ void k3_resolve_one(const pvv_dims &d, const pvv_ws &ws, long long row, int hbase, int t, int j,
-                                               int k, int n, const float *sP, const float4 *sH, const float2 *sDir,
-                                               const uint32_t *sXY, unsigned long long *amb)
-{
-    const int h = hbase + k * THREADS + t;
-    if (j >= n || h >= d.hn) return;
-    const float4 hl = sH[k * THREADS + t];  // {hx, hy, T} in the chunk-local frame
-    const float e = k3_e(hl.x, hl.y, k3_load_px(sP, j));
-    if (fabsf(e) > hl.z) return;
-    const float2 hv = ws.hyp[row + h];
-    const float2 dir = sDir[j];
-    const uint32_t xy = sXY[j];
-    if (pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16), hv.x, hv.y, d.thresh))
-        atomicAdd(&ws.counts[row + h], 1);
-    ++*amb;
+    const float ep = __fmaf_rn(hx, c.px, __fmaf_rn(hy, c.py, c.pz));
+    const float em = __fmaf_rn(hx, c.qx, __fmaf_rn(hy, c.qy, c.qz));
+    return fminf(ep, em);
 }
 
 // work item -> (image, keypoint, pixel range)
@@ -227,164 +207,221 @@ __global__ void __launch_bounds__(THREADS) k_count_exact(pvv_dims d, pvv_ws ws)
     }
 }
 
-// guard-banded filter kernel (MODE: code-generation variants of the same arithmetic, see the constants below)
-template <int H, int THREADS, int MODE>
+// Guard-banded filter kernel.  The hot loop counts a test as inlier iff the sign bit of m is clear and flags, per
+// (hypothesis slot, group of K3_GROUP pixels), whether any |m| <= T.  Flagged groups are re-evaluated after the loop in
+// two dense phases: (A) recompute m for the tests of the group and queue the ones truly inside the band, (B) give those
+// the reference's exact decision and correct the count by (exact - provisional).
+// Software pipeline: while item i is being voted on, the raw pixels of item i+1 are already in flight to the other
+// shared-memory buffer (cp.async) and the id of item i+2 is being fetched from the work queue, so neither the global
+// load latency nor the atomic's round trip is exposed.
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async8(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <int H, int THREADS>
 __global__ void __launch_bounds__(THREADS) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
 {
-    constexpr bool MIN3 = (MODE & 1) != 0;   // band check by FMNMX3 min-tracking instead of an FSETP chain
-    constexpr bool PACKG = (MODE & 2) != 0;  // T - e for a pixel pair as one FADD2
+    static_assert(THREADS <= 256 && H <= 8 && PVV_CHUNK_PX / K3_GROUP <= 32, "entry packing");
     __shared__ __align__(16) float sP[12 * K3_PAIRS];
-    __shared__ float2 sDir[PVV_CHUNK_PX];
-    __shared__ uint32_t sXY[PVV_CHUNK_PX];
+    __shared__ __align__(8) float2 sDir[2][PVV_CHUNK_PX];  // raw pixels, double-buffered (current / prefetched item)
+    __shared__ uint32_t sXY[2][PVV_CHUNK_PX];
     __shared__ float4 sH[H * THREADS];  // this pass's hypotheses in the chunk-local frame: {hx, hy, T, -}
-    __shared__ uint32_t s_q[K3_QCAP];
-    __shared__ int s_item, s_P, s_qn;
+    __shared__ uint32_t s_q[K3_QCAP];   // phase A: (group << 16) | (k << 8) | thread
+    __shared__ uint32_t s_q2[K3_QCAP];  // phase B: (pixel << 16) | (k << 8) | thread
+    __shared__ int s_id[2], s_P[2], s_qn, s_q2n;
 
     const int tid = threadIdx.x;
     const int total_items = ws.chunk_start[d.b] * d.vn;
     unsigned long long amb_local = 0;
-    const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, 0.f};  // a = -1e30: never an inlier, never in the band
+    const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};  // m = -1e30: never an inlier, never in the band
 
-    while (true) {
-        __syncthreads();  // previous item's smem fully consumed
-        if (tid == 0) { s_item = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u); s_P = 0; }
-        __syncthreads();
-        const int item = s_item;
-        if (item >= total_items) break;
-        const k3_item it = k3_decode_item(d, ws, item);
+    auto prefetch = [&](const k3_item &it, int buf) {
+        for (int j = tid; j < it.n; j += THREADS) {
+            cp_async4(&sXY[buf][j], ws.pix_xy + it.off + it.p0 + j);
+            cp_async8(&sDir[buf][j], ws.pix_dir + (long long)it.vi * ws.cap + it.off + it.p0 + j);
+        }
+        cp_async_commit();
+    };
+
+    if (tid == 0) {
+        s_id[0] = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u);
+        s_P[0] = 0; s_P[1] = 0; s_qn = 0; s_q2n = 0;
+    }
+    __syncthreads();
+    int item = s_id[0];
+    if (item >= total_items) return;
+    k3_item it = k3_decode_item(d, ws, item);
+    prefetch(it, 0);
+    if (tid == 0) s_id[1] = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u);
+
+    for (int buf = 0;; buf ^= 1) {
+        cp_async_wait_all();
+        __syncthreads();  // raw pixels of `item` landed; s_id[buf ^ 1] visible; previous item's smem fully consumed
+        const int next = s_id[buf ^ 1];
         const int n = it.n, ox = it.ox, oy = it.oy;
+        const float2 *rDir = sDir[buf];
+        const uint32_t *rXY = sXY[buf];
 
-        // ---- stage the chunk: raw values + derived constants in a chunk-local frame ----
+        // ---- derived constants in the chunk-local frame ----
         const int npad = (n + K3_GROUP - 1) / K3_GROUP * K3_GROUP;
         for (int j = tid; j < npad; j += THREADS) {
             px_consts c = never;
             if (j < n) {
-                const uint32_t xy = ws.pix_xy[it.off + it.p0 + j];
-                const float2 dir = ws.pix_dir[(long long)it.vi * ws.cap + it.off + it.p0 + j];
-                sXY[j] = xy;
-                sDir[j] = dir;
+                const uint32_t xy = rXY[j];
+                const float2 dir = rDir[j];
                 const float n1 = pvv_norm1(dir.x, dir.y);
                 // the reference skips ||n|| < 1e-6; a non-finite norm degenerates its cosine: never an inlier either
                 if ((double)n1 >= 1e-6 && n1 < 3.0e38f) {
                     const double inv = rsqrt((double)dir.x * dir.x + (double)dir.y * dir.y);
-                    const int px = (int)(xy & 0xffffu) - ox, py = (int)(xy >> 16) - oy;
-                    c.ax = (float)(dir.x * inv);
-                    c.ay = (float)(dir.y * inv);
-                    c.cx = (float)((double)bc.tau * (dir.y * inv));
-                    c.cy = (float)(-(double)bc.tau * (dir.x * inv));
-                    c.az = (float)(-((double)px * c.ax + (double)py * c.ay));
-                    c.cz = (float)(-((double)px * c.cx + (double)py * c.cy));
-                    atomicMax(&s_P, abs(px) + abs(py));
+                    const double nx = dir.x * inv, ny = dir.y * inv, tau = (double)bc.tau;
+                    const int ix = (int)(xy & 0xffffu) - ox, iy = (int)(xy >> 16) - oy;
+                    c.px = (float)(nx - tau * ny);
+                    c.py = (float)(ny + tau * nx);
+                    c.qx = (float)(nx + tau * ny);
+                    c.qy = (float)(ny - tau * nx);
+                    c.pz = (float)(-((double)ix * c.px + (double)iy * c.py));
+                    c.qz = (float)(-((double)ix * c.qx + (double)iy * c.qy));
+                    atomicMax(&s_P[buf], abs(ix) + abs(iy));
                 }
             }
             k3_store_px(sP, j, c);
         }
-        __syncthreads();
-        const float P = (float)s_P;
+        // ---- prefetch the next item's raw pixels and the id of the one after it ----
+        k3_item nit = it;
+        if (next < total_items) {
+            nit = k3_decode_item(d, ws, next);
+            prefetch(nit, buf ^ 1);
+        }
+        if (tid == 0) {
+            s_id[buf] = next < total_items ? (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u) : next;
+            s_P[buf ^ 1] = 0;
+            s_q2n = 0;  // all threads passed phase B of the previous item (barrier above)
+        }
+        __syncthreads();  // constants and s_P complete
+        const float P = (float)s_P[buf];
         const long long row = ((long long)it.img * d.vn + it.vi) * ws.hn_pad;
+        const int ngroups = npad / K3_GROUP;
+
+        // exact decision for one in-band test, correcting the provisional count (sign bit of m clear = counted)
+        auto resolve = [&](int hbase, int t, int k, int j, float m) {
+            const int h = hbase + k * THREADS + t;
+            const float2 hv = ws.hyp[row + h];
+            const float2 dir = rDir[j];
+            const uint32_t xy = rXY[j];
+            const int exact = pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu),
+                                             (float)(xy >> 16), hv.x, hv.y, d.thresh) ? 1 : 0;
+            const int prov = (int)(__float_as_uint(m) >> 31) ^ 1;
+            if (exact != prov) atomicAdd(&ws.counts[row + h], exact - prov);
+            ++amb_local;
+        };
 
         for (int hbase = 0; hbase < d.hn; hbase += THREADS * H) {
             const bool active = hbase + (tid & ~31) < d.hn;  // warp-uniform: does this warp own hypotheses in the pass
-            if (tid == 0) s_qn = 0;
-            __syncthreads();  // also: the previous pass's deferred entries (s_q, sH) are consumed
+            if (hbase > 0) {
+                __syncthreads();  // the previous pass's deferred entries (s_q2, sH) are consumed
+                if (tid == 0) s_q2n = 0;
+            }
             if (active) {
-                f32x2 hx2[H], hy2[H];
-                float T[H];
-                int cnt[H];
+                float hx[H], hy[H], T[H];
+                int neg[H];
+                uint32_t dmask[H];
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
                     const int h = hbase + k * THREADS + tid;
                     const float2 hv = h < d.hn ? ws.hyp[row + h] : make_float2(0.f, 0.f);
-                    float hx, hy;
-                    k3_local_hyp(hv.x, hv.y, ox, oy, P, bc, hx, hy, T[k]);
-                    hx2[k] = pk(hx, hx);
-                    hy2[k] = pk(hy, hy);
-                    cnt[k] = 0;
-                    sH[k * THREADS + tid] = make_float4(hx, hy, T[k], 0.f);  // for the deferred pass
+                    k3_local_hyp(hv.x, hv.y, ox, oy, P, bc, hx[k], hy[k], T[k]);
+                    neg[k] = 0;
+                    dmask[k] = 0u;
+                    sH[k * THREADS + tid] = make_float4(hx[k], hy[k], T[k], 0.f);  // for the deferred pass
                 }
-                // Groups of K3_GROUP pixels (two packed pairs) share one band check.  A group with any test inside the
-                // guard band only sets a bit in a per-thread mask: the hot loop has no branch and no divergence.
-                uint32_t dmask[2] = {0u, 0u};
+                // The hot loop has no branch and no divergence: a (slot, group) with any test inside the guard band
+                // only sets a bit in a per-thread mask.
+                uint32_t bit = 1u;
                 const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(sP);
-                const int ngroups = npad / K3_GROUP;
+                for (int g = 0; g < ngroups; ++g, pp += 3 * (K3_GROUP / 2), bit <<= 1) {
+                    float mabs[H];
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    const int g_end = min(ngroups, 32 * (half + 1));
-                    uint32_t bit = 1u, dm = 0u;
-                    for (int g = 32 * half; g < g_end; ++g, pp += 3 * (K3_GROUP / 2), bit <<= 1) {
-                        bool clear = true;
-                        float mabs[H];
-                        if (MIN3) {
+                    for (int k = 0; k < H; ++k) mabs[k] = __int_as_float(0x7f800000);
 #pragma unroll
-                            for (int k = 0; k < H; ++k) mabs[k] = __int_as_float(0x7f800000);
+                    for (int u = 0; u < K3_GROUP / 2; ++u) {
+                        const ulonglong2 v0 = pp[3 * u], v1 = pp[3 * u + 1], v2 = pp[3 * u + 2];
+#pragma unroll
+                        for (int k = 0; k < H; ++k) {
+                            const f32x2 hxx = pk(hx[k], hx[k]), hyy = pk(hy[k], hy[k]);  // FFMA2 broadcast operands
+                            float ep0, ep1, em0, em1;
+                            unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
+                            unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
+                            const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
+                            neg[k] += (int)(__float_as_uint(m0) >> 31) + (int)(__float_as_uint(m1) >> 31);
+                            mabs[k] = fminf(fminf(mabs[k], fabsf(m0)), fabsf(m1));
                         }
-#pragma unroll
-                        for (int u = 0; u < K3_GROUP / 2; ++u) {
-                            const ulonglong2 v0 = pp[3 * u], v1 = pp[3 * u + 1], v2 = pp[3 * u + 2];
-#pragma unroll
-                            for (int k = 0; k < H; ++k) {
-                                const f32x2 a2 = ffma2(hx2[k], v0.x, ffma2(hy2[k], v0.y, v1.x));
-                                const f32x2 c2 = ffma2(hx2[k], v1.y, ffma2(hy2[k], v2.x, v2.y));
-                                float a0, a1, c0, c1;
-                                unpk(a2, a0, a1);
-                                unpk(c2, c0, c1);
-                                // ne = |c'| - a = -e.  T + ne < 0  <=>  e > T: definitely an inlier.  NaN cannot reach
-                                // here (k3_local_hyp).
-                                const float ne0 = __fsub_rn(fabsf(c0), a0), ne1 = __fsub_rn(fabsf(c1), a1);
-                                if (PACKG) {
-                                    float g0, g1;
-                                    unpk(fadd2(pk(T[k], T[k]), pk(ne0, ne1)), g0, g1);
-                                    cnt[k] += (int)(__float_as_uint(g0) >> 31);
-                                    cnt[k] += (int)(__float_as_uint(g1) >> 31);
-                                } else {
-                                    cnt[k] += (int)(__float_as_uint(__fadd_rn(T[k], ne0)) >> 31);
-                                    cnt[k] += (int)(__float_as_uint(__fadd_rn(T[k], ne1)) >> 31);
-                                }
-                                if (MIN3) mabs[k] = fminf(fminf(mabs[k], fabsf(ne0)), fabsf(ne1));
-                                else clear = clear && (fabsf(ne0) > T[k]) && (fabsf(ne1) > T[k]);
-                            }
-                        }
-                        if (MIN3) {
-#pragma unroll
-                            for (int k = 0; k < H; ++k) clear = clear && (mabs[k] > T[k]);
-                        }
-                        if (!clear) dm |= bit;
                     }
-                    dmask[half] = dm;
+#pragma unroll
+                    for (int k = 0; k < H; ++k)
+                        if (!(mabs[k] > T[k])) dmask[k] |= bit;
                 }
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
                     const int h = hbase + k * THREADS + tid;
-                    if (h < d.hn && cnt[k]) atomicAdd(&ws.counts[row + h], cnt[k]);
+                    const int cnt = npad - neg[k];  // padded and never-inlier pixels have m < 0
+                    if (h < d.hn && cnt) atomicAdd(&ws.counts[row + h], cnt);
                 }
-                // queue this thread's deferred groups for the dense exact pass
+                // queue this thread's flagged (slot, group) pairs for the dense passes below
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    uint32_t dm = dmask[half];
+                for (int k = 0; k < H; ++k) {
+                    uint32_t dm = hbase + k * THREADS + tid < d.hn ? dmask[k] : 0u;
                     while (dm) {
-                        const int grp = 32 * half + __ffs(dm) - 1;
+                        const int grp = __ffs(dm) - 1;
                         dm &= dm - 1;
                         const int q = atomicAdd(&s_qn, 1);
                         if (q < K3_QCAP) {
-                            s_q[q] = ((uint32_t)grp << 16) | (uint32_t)tid;
+                            s_q[q] = ((uint32_t)grp << 16) | ((uint32_t)k << 8) | (uint32_t)tid;
                         } else {  // queue full (pathological inputs): resolve in line
-                            for (int sub = 0; sub < K3_GROUP * H; ++sub)
-                                k3_resolve_one<THREADS>(d, ws, row, hbase, tid, grp * K3_GROUP + (sub % K3_GROUP), sub / K3_GROUP,
-                                                        n, sP, sH, sDir, sXY, &amb_local);
+                            const float4 hl = sH[k * THREADS + tid];  // this thread's own entry
+                            for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j) {
+                                const float m = k3_m(hl.x, hl.y, k3_load_px(sP, j));
+                                if (!(fabsf(m) > hl.z)) resolve(hbase, tid, k, j, m);
+                            }
                         }
                     }
                 }
             }
             __syncthreads();
-            // deferred pass: one (pixel, hypothesis) re-evaluation per thread and step, spread over the whole CTA
-            const int qtot = min(s_qn, K3_QCAP) * (K3_GROUP * H);
+            // phase A: one (pixel, hypothesis) band re-evaluation per thread and step, spread over the whole CTA
+            const int qtot = min(s_qn, K3_QCAP) * K3_GROUP;
             for (int idx = tid; idx < qtot; idx += THREADS) {
-                const uint32_t ent = s_q[idx / (K3_GROUP * H)];
-                const int sub = idx % (K3_GROUP * H);
-                k3_resolve_one<THREADS>(d, ws, row, hbase, (int)(ent & 0xffffu), (int)(ent >> 16) * K3_GROUP + (sub % K3_GROUP),
-                                        sub / K3_GROUP, n, sP, sH, sDir, sXY, &amb_local);
+                const uint32_t ent = s_q[idx / K3_GROUP];
+                const int t = (int)(ent & 0xffu), k = (int)((ent >> 8) & 0xffu);
+                const int j = (int)(ent >> 16) * K3_GROUP + idx % K3_GROUP;
+                if (j >= n) continue;
+                const float4 hl = sH[k * THREADS + t];
+                const float m = k3_m(hl.x, hl.y, k3_load_px(sP, j));
+                if (fabsf(m) > hl.z) continue;
+                const int q = atomicAdd(&s_q2n, 1);
+                if (q < K3_QCAP) s_q2[q] = ((uint32_t)j << 16) | ((uint32_t)k << 8) | (uint32_t)t;
+                else resolve(hbase, t, k, j, m);
+            }
+            __syncthreads();
+            if (tid == 0) s_qn = 0;  // every thread has read it; the next pushes come after another barrier
+            // phase B: exact decisions for the tests inside the band
+            const int q2 = min(s_q2n, K3_QCAP);
+            for (int idx = tid; idx < q2; idx += THREADS) {
+                const uint32_t ent = s_q2[idx];
+                const int t = (int)(ent & 0xffu), k = (int)((ent >> 8) & 0xffu), j = (int)(ent >> 16);
+                const float4 hl = sH[k * THREADS + t];
+                resolve(hbase, t, k, j, k3_m(hl.x, hl.y, k3_load_px(sP, j)));
             }
         }
+        if (next >= total_items) break;
+        item = next;
+        it = nit;
     }
     if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
 }
@@ -421,13 +458,13 @@ static bool pvv_band_for(float t, band_consts *bc)
     return true;
 }
 
-template <int H, int THREADS, int MODE>
+template <int H, int THREADS>
 static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st)
 {
     int per_sm = 8;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS, MODE>, THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS>, THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    k_count<H, THREADS, MODE><<<sms * per_sm, THREADS, 0, st>>>(d, ws, bc);
+    k_count<H, THREADS><<<sms * per_sm, THREADS, 0, st>>>(d, ws, bc);
     return cudaGetLastError();
 }
 
@@ -438,8 +475,10 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {0.f, 0.f, 0.f};
     const bool fast = !force_exact && pvv_band_for(d.thresh, &bc);
-    const char *venv = getenv("PVV_K3_VARIANT");  // tuning knob for experiments
-    const int variant = venv ? atoi(venv) : 0;
+    // CTA shape by hypothesis count: every thread owns 4 hypotheses, one pass covers 4 * THREADS of them
+    // (PVV_K3_VARIANT overrides the choice: a tuning knob for tools/k3_variants.py)
+    const char *venv = getenv("PVV_K3_VARIANT");
+    const int variant = venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 0);
     cudaError_t e;
     if (!fast) {
         int per_sm = 8;
@@ -447,14 +486,12 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         k_count_exact<4, 128><<<sms * (per_sm < 1 ? 1 : per_sm), 128, 0, st>>>(d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 1) e = launch_count_t<4, 128, 1>(d, ws, bc, sms, st);
-    else if (variant == 2) e = launch_count_t<4, 128, 2>(d, ws, bc, sms, st);
-    else if (variant == 3) e = launch_count_t<4, 128, 3>(d, ws, bc, sms, st);
-    else if (variant == 4) e = launch_count_t<8, 64, 0>(d, ws, bc, sms, st);
-    else if (variant == 5) e = launch_count_t<8, 64, 3>(d, ws, bc, sms, st);
-    else if (variant == 6) e = launch_count_t<8, 128, 3>(d, ws, bc, sms, st);
-    else if (variant == 7) e = launch_count_t<2, 256, 3>(d, ws, bc, sms, st);
-    else e = launch_count_t<4, 128, 0>(d, ws, bc, sms, st);
+    else if (variant == 1) e = launch_count_t<4, 64>(d, ws, bc, sms, st);
+    else if (variant == 2) e = launch_count_t<4, 32>(d, ws, bc, sms, st);
+    else if (variant == 3) e = launch_count_t<2, 256>(d, ws, bc, sms, st);
+    else if (variant == 4) e = launch_count_t<8, 64>(d, ws, bc, sms, st);
+    else if (variant == 5) e = launch_count_t<2, 128>(d, ws, bc, sms, st);
+    else e = launch_count_t<4, 128>(d, ws, bc, sms, st);
     ++*launches;
     return e;
 }
