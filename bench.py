@@ -34,6 +34,7 @@ FRAC, SIGMA = 0.03, 0.05
 N_SETS = 3  # rotating input sets: ~0.87 GB each, so a step never finds its inputs in the 126 MB L2
 WORKLOAD = "configs[1]: 32x480x640 per GPU, 9 kp, 512 hyp, thresh 0.999, ~3% fg"
 FLOP_PER_TEST = 12.0  # SURVEY.md section 8(d) figure of record
+METRIC = "voting images/sec (480x640, 9 kp, 512 hyp)"
 
 
 def parse():
@@ -42,7 +43,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-images", type=int, default=2, help="images in the bounded CPU sample")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU work in the bounded cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -96,44 +97,72 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_leg(images, steps=1, warmup=0):
-    """The oracle port timed on the host cores: v3 on `images` images of the workload per step."""
-    from oracle import oracle as orc
+def _cpu_inputs(images):
     from pvnet_b200 import synth
-
     mask, vertex, _ = synth.make_batch(images, vn=VN, frac=FRAC, sigma=SIGMA, seed=1234)
     rng = np.random.default_rng(0)
     tn = [(int((mask[i] != 0).sum())) for i in range(images)]
     idxs = np.stack([rng.integers(0, max(t, 1), size=(HN, VN, 2)).astype(np.int32) for t in tn])
-    for _ in range(warmup):
-        orc.ransac_voting_layer_v3(mask[:1], vertex[:1], HN, THRESH, idxs=idxs[:1])
+    return mask, vertex, idxs, tn
+
+
+def cpu_leg(target_s=12.0, max_s=30.0):
+    """cpu_baseline: the oracle port (OpenMP C kernels + numpy control flow) timed on the host cores over a bounded
+    sample of the workload: whole 32-image batches of configs[1] until about `target_s` seconds of CPU work."""
+    from oracle import oracle as orc
+
+    mask, vertex, idxs, tn = _cpu_inputs(B_PER_GPU)
+    orc.ransac_voting_layer_v3(mask[:2], vertex[:2], HN, THRESH, idxs=idxs[:2])  # warm-up (library load, threads)
     t0 = time.perf_counter()
-    for _ in range(steps):
+    steps = 0
+    while True:
         orc.ransac_voting_layer_v3(mask, vertex, HN, THRESH, idxs=idxs)
-    dt = time.perf_counter() - t0
+        steps += 1
+        dt = time.perf_counter() - t0
+        if dt >= target_s or dt + dt / steps > max_s:
+            break
     tests = float(sum(tn)) * VN * HN * steps
-    return {"value": images * steps / dt, "unit": "images/s", "cores": orc.num_threads(), "kind": "port",
-            "sample": f"{images} images of the workload x {steps} step(s), all {orc.num_threads()} host threads (OpenMP C "
-                      f"oracle + numpy control flow), {dt:.2f} s",
+    return {"value": B_PER_GPU * steps / dt, "unit": "images/s", "cores": orc.num_threads(), "kind": "port",
+            "sample": f"{steps} x the 32-image batch of the workload ({B_PER_GPU * steps} images, {tests:.3g} tests), all "
+                      f"{orc.num_threads()} host threads (OpenMP C restatement of the reference kernels + numpy control "
+                      f"flow, oracle/), {dt:.1f} s",
             "tests_per_s": tests / dt, "seconds": dt}
 
 
 def run_reference(args):
-    """--impl reference: the reference has no CPU voting path and its CUDA layer is not a CPU
-    baseline; per the tier contract this arm times the oracle port on the host cores."""
+    """--impl reference: the reference ships no CPU voting path and its CUDA layer is not a CPU
+    baseline; per the tier contract this arm times the oracle port of the reference kernels on the host cores, all
+    threads, on the same workload.  A step = v3 over a bounded sample (the first `n` images of the 32-image batch), `n`
+    sized from the warm-up rate so that K steps end within about a minute."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    c = cpu_leg(args.cpu_images, steps=max(1, min(args.steps, 5)), warmup=min(args.warmup, 1))
-    steps = max(1, min(args.steps, 5))
-    line = {"metric": "voting images/sec (480x640, 9 kp, 512 hyp)", "value": c["value"], "unit": "images/s",
-            "impl": "reference", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
-            "ms_per_step": 1e3 * c["seconds"] / steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample_images_per_step": args.cpu_images},
-            "cpu_baseline": {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")},
-            "e2e": {"value": c["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "hyp_pixel_tests_per_s": c["tests_per_s"], "gpu_launches": 0}
+    from oracle import oracle as orc
+
+    mask, vertex, idxs, tn = _cpu_inputs(B_PER_GPU)
+    warm = max(1, args.warmup)
+    t0 = time.perf_counter()
+    for _ in range(warm):
+        orc.ransac_voting_layer_v3(mask[:2], vertex[:2], HN, THRESH, idxs=idxs[:2])
+    rate = 2 * warm / (time.perf_counter() - t0)                      # images/s seen in the warm-up
+    n = int(max(1, min(B_PER_GPU, rate * 60.0 / max(1, args.steps))))  # images per step
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.ransac_voting_layer_v3(mask[:n], vertex[:n], HN, THRESH, idxs=idxs[:n])
+    dt = time.perf_counter() - t0
+    tests = float(sum(tn[:n])) * VN * HN * args.steps
+    value = n * args.steps / dt
+    cpu = {"value": value, "unit": "images/s", "cores": orc.num_threads(), "kind": "port",
+           "sample": f"{args.steps} steps x {n} images of the workload, all {orc.num_threads()} host threads (OpenMP C "
+                     f"restatement of the reference kernels + numpy control flow, oracle/), {dt:.1f} s"}
+    line = {"metric": METRIC, "value": value, "unit": "images/s", "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": warm, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample_images_per_step": n, "h": H, "w": W, "vn": VN, "hn": HN,
+                       "inlier_thresh": THRESH},
+            "cpu_baseline": cpu,
+            "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "hyp_pixel_tests_per_s": tests / dt, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
@@ -211,9 +240,16 @@ def run_ours(args):
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic, traffic_src = None, None
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` capture
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["k_count"]
+        traffic, traffic_src = t["dram_bytes_per_launch"], t["source"]
+    except Exception:
+        pass
     k1_bytes = mask.nbytes + tn_total * VN * 8 + tn_total * (4 + VN * 8) + mask.nbytes  # mask read twice (count, scatter)
     roofline = {"kernel": "k_count (K3 fused inlier counting)", "bound": "fp32", "achieved": achieved, "peak": peak,
-                "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
+                "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
+                "bound_note": "FP32 SIMT compare/reduce (north_star: no tensor cores); HBM traffic of this kernel is ~0.6% of peak",
                 "peak_source": "FFMA probe kernel run in this process (pvv_fp32_peak_tflops); MEASURED_PEAKS.json has no FP32 figure",
                 "flop_per_test": FLOP_PER_TEST, "tests_per_launch": tests_per_step, "kernel_ms": st["count"],
                 "tests_per_s": tests_per_step / (st["count"] * 1e-3),
@@ -252,9 +288,9 @@ def run_ours(args):
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
-            c = cpu_leg(args.cpu_images)
+            c = cpu_leg(args.cpu_seconds)
             cpu = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        line = {"metric": "voting images/sec (480x640, 9 kp, 512 hyp)", "value": value, "unit": "images/s",
+        line = {"metric": METRIC, "value": value, "unit": "images/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "images_per_gpu": b, "global_batch": world * b, "h": H, "w": W, "vn": VN,

@@ -1,8 +1,11 @@
-"""Build libpvvote.so (the C-ABI CUDA library) in-tree for sm_100a.
+"""Build the native pieces in-tree for sm_100a.
 
     python -m pvnet_b200.build [--force]
 
-Explicit nvcc, no torch involvement: the library has no torch/ATen dependency (include/pvvote.h).
+  libpvvote.so      the C-ABI CUDA library (include/pvvote.h).  Explicit nvcc, no torch involvement: the library has
+                    no torch/ATen dependency.
+  ransac_voting.so  the PyTorch C++ extension that replaces the reference's src/ransac_voting.cpp + .cu + setup.py:
+                    a thin shim (csrc/ransac_voting_shim.cpp, plain g++) over libpvvote.so.
 """
 from __future__ import annotations
 
@@ -61,5 +64,35 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+SHIM = os.path.join(HERE, "ransac_voting.so")
+
+
+def build_shim(force: bool = False) -> str:
+    """g++ the torch extension shim against torch's headers; links libpvvote.so by rpath ($ORIGIN)."""
+    src = os.path.join(CSRC, "ransac_voting_shim.cpp")
+    hdr = os.path.join(HERE, "..", "include", "pvvote.h")
+    if not force and not _stale(SHIM, [src, hdr, LIB]):
+        return SHIM
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as ce
+
+    inc = []
+    for p in ce.include_paths("cuda") + [sysconfig.get_paths()["include"], "/usr/local/cuda/include"]:
+        inc += ["-I", p]
+    libdir = os.path.join(os.path.dirname(torch.__file__), "lib")
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-w", "-DTORCH_EXTENSION_NAME=ransac_voting",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", f"-D_GLIBCXX_USE_CXX11_ABI={abi}", *inc, src, "-o", SHIM,
+           f"-L{HERE}", "-lpvvote", "-Wl,-rpath,$ORIGIN", f"-L{libdir}", f"-Wl,-rpath,{libdir}",
+           "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch", "-ltorch_python"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"shim build failed:\n{r.stdout}\n{r.stderr}")
+    return SHIM
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
+    print(build_shim(force="--force" in sys.argv))

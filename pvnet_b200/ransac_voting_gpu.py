@@ -21,7 +21,7 @@ import torch
 
 from . import _lib
 
-__all__ = ["ransac_voting_layer_v3", "estimate_voting_distribution_with_mean", "ransac_voting", "make_idxs",
+__all__ = ["ransac_voting_layer_v3", "estimate_voting_distribution_with_mean", "ransac_voting", "torch_extension", "make_idxs",
            "make_selection", "fp32_peak_tflops", "last_launch_count"]
 
 _MASK_DT = {torch.uint8: _lib.MASK_U8, torch.bool: _lib.MASK_U8, torch.int32: _lib.MASK_I32,
@@ -252,6 +252,26 @@ class _RansacVoting:
 
 
 ransac_voting = _RansacVoting()
+
+_EXT = None
+
+
+def torch_extension():
+    """The PyTorch C++ extension that replaces the reference's pybind module `ransac_voting`
+    (src/ransac_voting.cpp:102-107): pvnet_b200/ransac_voting.so, built by `python -m pvnet_b200.build` from
+    csrc/ransac_voting_shim.cpp -- a thin shim over the same C ABI.  Raises if it has not been built."""
+    global _EXT
+    if _EXT is None:
+        import importlib.util
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ransac_voting.so")
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} is missing: build it with `python -m pvnet_b200.build`")
+        _lib.lib()  # libpvvote.so first, so that the shim's DT_NEEDED entry resolves to the in-tree copy
+        spec = importlib.util.spec_from_file_location("ransac_voting", path)
+        _EXT = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(_EXT)
+    return _EXT
 
 
 def make_idxs(seed, tn, hn_total, vn, image_id_base=0):

@@ -172,3 +172,34 @@ def test_signatures_match_reference_api():
     assert pos == [("mask", inspect._empty), ("vertex", inspect._empty), ("mean", inspect._empty),
                    ("round_hyp_num", 256), ("min_hyp_num", 4096), ("topk", 128), ("inlier_thresh", 0.99),
                    ("min_num", 20), ("max_num", 30000), ("output_hyp", False)]
+
+
+def test_torch_extension_shim_builds_and_mirrors_the_reference_pybind_module(built_lib):
+    """pvnet_b200/ransac_voting.so replaces the reference's pybind module (src/ransac_voting.cpp:102-107): same module
+    name, same two primitive names, same CHECK_CUDA / CHECK_CONTIGUOUS errors."""
+    from pvnet_b200 import build as pbuild
+    from pvnet_b200 import ransac_voting_gpu as pv
+    assert os.path.exists(pbuild.build_shim())
+    ext = pv.torch_extension()
+    assert ext.__name__ == "ransac_voting"
+    for name in ("generate_hypothesis", "voting_for_hypothesis", "ransac_voting_layer_v3",
+                 "estimate_voting_distribution_with_mean"):
+        assert callable(getattr(ext, name))
+    d, c, i = torch.zeros(4, 2, 2), torch.zeros(4, 2), torch.zeros(3, 2, 2, dtype=torch.int32)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        ext.generate_hypothesis(d, c, i)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        ext.voting_for_hypothesis(d, c, torch.zeros(3, 2, 2), torch.zeros(3, 2, 4, dtype=torch.uint8), 0.99)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        ext.ransac_voting_layer_v3(torch.ones(1, 8, 8, dtype=torch.int64), torch.zeros(1, 8, 8, 2, 2), 16)
+
+
+def test_integration_stub_reexports_the_path():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ransac_voting_gpu_stub", os.path.join(ROOT, "integration", "ransac_voting_gpu.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    from pvnet_b200 import ransac_voting_gpu as pv
+    assert m.ransac_voting_layer_v3 is pv.ransac_voting_layer_v3
+    assert m.estimate_voting_distribution_with_mean is pv.estimate_voting_distribution_with_mean
+    assert hasattr(m.ransac_voting, "generate_hypothesis") and hasattr(m.ransac_voting, "voting_for_hypothesis")

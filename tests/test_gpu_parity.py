@@ -302,3 +302,37 @@ def test_shard_invariance_and_errors():
     out, dbg = pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13, return_debug=True, pool_capacity=64)
     assert int(dbg["status"]) & 1
     assert pv.last_launch_count() >= 6
+
+
+def test_torch_extension_shim_equals_ctypes_path():
+    """The PyTorch C++ extension (pvnet_b200/ransac_voting.so, replacing the reference's pybind module) and the ctypes
+    binding drive the same C ABI: identical bits, on the current stream, with the network's strided layout."""
+    ext = pv.torch_extension()
+    mask, vertex, _ = synth.make_batch(3, vn=9, frac=0.03, sigma=0.05, seed=17)
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    a = pv.ransac_voting_layer_v3(tm, tv, 128, 0.99, seed=4)
+    b = ext.ransac_voting_layer_v3(tm, tv, 128, 0.99, seed=4)
+    assert torch.equal(a, b)
+    _, ca = pv.estimate_voting_distribution_with_mean(tm, tv, a, 64, 256, seed=5)
+    mean, cb = ext.estimate_voting_distribution_with_mean(tm, tv, a, 64, 256, seed=5)
+    assert torch.equal(ca, cb) and mean is a
+    # primitives with the reference's AoS layouts
+    cp = orc.compact(mask[0], vertex[0], "v3", 1, 10 ** 9)
+    coords, direct = cp[0][:2000], cp[1][:2000]
+    idxs = np.random.default_rng(1).integers(0, coords.shape[0], size=(64, 9, 2)).astype(np.int32)
+    td, tc, ti = (torch.from_numpy(x).to(DEV) for x in (direct, coords, idxs))
+    hyp = ext.generate_hypothesis(td, tc, ti)
+    assert np.array_equal(_bits(hyp), _bits(orc.generate_hypothesis(direct, coords, idxs)))
+    inl = torch.zeros((64, 9, coords.shape[0]), dtype=torch.uint8, device=DEV)
+    ext.voting_for_hypothesis(td, tc, hyp, inl, 0.99)
+    o_inl = np.zeros(inl.shape, np.uint8)
+    orc.voting_for_hypothesis(direct, coords, hyp.cpu().numpy(), o_inl, 0.99)
+    assert np.array_equal(inl.cpu().numpy(), o_inl)
+    with pytest.raises(RuntimeError, match="contiguous"):
+        ext.generate_hypothesis(td.transpose(0, 1), tc, ti)
+    # a side stream is honoured (the reference launched on the legacy default stream)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        c = ext.ransac_voting_layer_v3(tm, tv, 128, 0.99, seed=4)
+    s.synchronize()
+    assert torch.equal(a, c)
