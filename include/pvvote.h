@@ -117,6 +117,19 @@ int64_t pvv_default_pool_capacity(const pvv_job *job);
 int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, const pvv_debug *dbg);
 
 /*
+ * ransac_voting_layer_v5 (ransac_voting_gpu.py:769-864) = v3 + a per-keypoint confidence: the refined keypoints are
+ * re-voted at the fixed threshold 0.999 (:854-856) and out_conf [b,vn] float32 = inlier count / tn (0 for skipped images).
+ */
+int pvv_v5(const pvv_job *job, float confidence, int max_iter, float *out_kp, float *out_conf, const pvv_debug *dbg);
+
+/*
+ * generate_hypothesis wrapper (ransac_voting_gpu.py:989-1040): the hypotheses and their inlier counts in the
+ * reference's layouts, out_hyp [b,hn_total,vn,2] float32 and out_counts [b,hn_total,vn] int32 (device); zeros for
+ * skipped images.  job->fg_rule = PVV_FG_BYTE.
+ */
+int pvv_hypotheses(const pvv_job *job, float *out_hyp, int32_t *out_counts, const pvv_debug *dbg);
+
+/*
  * estimate_voting_distribution_with_mean (ransac_voting_gpu.py:333-406):
  * mean [b,vn,2] float32 in, out_cov [b,vn,2,2] float32 out (device). job->hn_total = ceil(min_hyp/round_hyp)*round_hyp,
  * job->fg_rule must be PVV_FG_EQ1.

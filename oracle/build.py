@@ -2,7 +2,7 @@
 
   build_oracle()  gcc   oracle/pvv_oracle.c                    -> oracle/liborc.so
   build_ref()     nvcc  /root/reference/lib/ransac_voting_gpu_layer/src/*.{cu,cpp}
-                        (compiled where they lie, nothing copied)  -> oracle/_ref/ransac_voting.so
+                        (compiled where they lie, nothing copied)  -> oracle/_ref/ref_ransac_voting.so
 
 The second target is the reference's own pybind module `ransac_voting`
 (src/ransac_voting.cpp:102-107) cross-compiled for sm_100a with nvcc's default
@@ -26,7 +26,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SRC = "/root/reference/lib/ransac_voting_gpu_layer/src"
 REF_OUT = os.path.join(HERE, "_ref")
 ORC_SO = os.path.join(HERE, "liborc.so")
-REF_SO = os.path.join(REF_OUT, "ransac_voting.so")
+REF_SO = os.path.join(REF_OUT, "ref_ransac_voting.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 
@@ -73,7 +73,7 @@ def build_ref(force: bool = False) -> str | None:
     for p in ce.include_paths("cuda") + [sysconfig.get_paths()["include"], REF_SRC]:
         inc += ["-I", p]
     abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
-    common = ["-DTORCH_EXTENSION_NAME=ransac_voting", "-DTORCH_API_INCLUDE_EXTENSION_H",
+    common = ["-DTORCH_EXTENSION_NAME=ref_ransac_voting", "-DTORCH_API_INCLUDE_EXTENSION_H",
               f"-D_GLIBCXX_USE_CXX11_ABI={abi}", "-std=c++17"]
     o_cu = os.path.join(REF_OUT, "ransac_voting_kernel.o")
     o_cpp = os.path.join(REF_OUT, "ransac_voting.o")

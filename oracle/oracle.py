@@ -198,6 +198,46 @@ def ransac_voting_layer_v3(mask, vertex, round_hyp_num, inlier_thresh=0.99, conf
 
 
 # ----------------------------------------------------------------------------
+# ransac_voting_layer_v5  (ransac_voting_gpu.py:769-864)  and  generate_hypothesis  (:989-1040)
+# ----------------------------------------------------------------------------
+def ransac_voting_layer_v5(mask, vertex, round_hyp_num, inlier_thresh=0.999, confidence=0.99, max_iter=20,
+                           min_num=5, max_num=100, *, idxs=None, selection=None, return_debug=False):
+    """v3's body with v5's defaults, then the confidence re-vote of the refined (float32) keypoints at the fixed
+    threshold 0.999 (:854-856): conf = inlier count / tn in float32; zeros for skipped images (:786-791)."""
+    out, dbg = ransac_voting_layer_v3(mask, vertex, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num,
+                                      idxs=idxs, selection=selection, return_debug=True)
+    b, vn = out.shape[:2]
+    conf = np.zeros((b, vn), np.float32)
+    for bi in range(b):
+        if dbg[bi] is None:
+            continue
+        tn = dbg[bi]["coords"].shape[0]
+        inl = np.zeros((1, vn, tn), np.uint8)
+        voting_for_hypothesis(dbg[bi]["direct"], dbg[bi]["coords"], out[bi][None], inl, 0.999)
+        conf[bi] = inl[0].astype(np.int64).sum(1).astype(np.float32) / np.float32(tn)
+    return (out, conf, dbg) if return_debug else (out, conf)
+
+
+def generate_hypothesis_layer(mask, vertex, round_hyp_num, inlier_thresh=0.999, confidence=0.99, max_iter=20,
+                              min_num=5, max_num=30000, *, idxs=None, selection=None):
+    """The wrapper `generate_hypothesis` of ransac_voting_gpu.py:989-1040 (named *_layer here because this module's
+    `generate_hypothesis` is the kernel): (hyp [b,hn,vn,2] f32, counts [b,hn,vn] i64).  Skipped images give zeros (the
+    reference raises NameError on them, :1009)."""
+    mask, vertex = np.asarray(mask), np.asarray(vertex)
+    b, h, w, vn, _ = vertex.shape
+    hyps = np.zeros((b, round_hyp_num, vn, 2), np.float32)
+    counts = np.zeros((b, round_hyp_num, vn), np.int64)
+    for bi in range(b):
+        cp = compact(mask[bi], vertex[bi], "v3", min_num, max_num, None if selection is None else selection[bi])
+        if cp is None:
+            continue
+        coords, direct, _ = cp
+        hyps[bi] = generate_hypothesis(direct, coords, np.asarray(idxs[bi], np.int32))
+        counts[bi] = vote_counts(direct, coords, hyps[bi], inlier_thresh)
+    return hyps, counts
+
+
+# ----------------------------------------------------------------------------
 # estimate_voting_distribution_with_mean  (ransac_voting_gpu.py:333-406)
 # ----------------------------------------------------------------------------
 def estimate_voting_distribution_with_mean(mask, vertex, mean, round_hyp_num=256, min_hyp_num=4096, topk=128,

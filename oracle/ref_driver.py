@@ -1,4 +1,4 @@
-"""Drive the REFERENCE's own CUDA kernels (oracle/_ref/ransac_voting.so, built by oracle/build.py from
+"""Drive the REFERENCE's own CUDA kernels (oracle/_ref/ref_ransac_voting.so, built by oracle/build.py from
 /root/reference/lib/ransac_voting_gpu_layer/src) on the GPU box.  TEST INFRASTRUCTURE ONLY.
 
 The reference's Python wrapper cannot travel to the GPU box and does not run on torch 2.11 anyway,
@@ -17,7 +17,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "_ref", "ransac_voting.so")
+_SO = os.path.join(_HERE, "_ref", "ref_ransac_voting.so")
 _mod = None
 
 
@@ -29,7 +29,7 @@ def ext():
     """The reference's pybind module, loaded from oracle/_ref."""
     global _mod
     if _mod is None:
-        spec = importlib.util.spec_from_file_location("ransac_voting", _SO)
+        spec = importlib.util.spec_from_file_location("ref_ransac_voting", _SO)
         _mod = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(_mod)
     return _mod

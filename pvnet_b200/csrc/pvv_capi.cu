@@ -180,24 +180,57 @@ size_t pvv_workspace_bytes(const pvv_job *job)
     return make_layout(job).total_bytes;
 }
 
-int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, const pvv_debug *dbg)
+static int run_v3(const pvv_job *job, float *out_kp, float *out_conf, const pvv_debug *dbg)
 {
-    (void)confidence; (void)max_iter;  // unobservable in the reference: every round re-votes the same idxs (:553-582)
-    if (!out_kp) return PVV_ERR_INVALID;
-    if (job && job->fg_rule != PVV_FG_BYTE && job->fg_rule != PVV_FG_EQ1) return PVV_ERR_INVALID;
+    if (!out_kp || !job) return PVV_ERR_INVALID;
     int launches = 0;
     pvv_dims d;
     pvv_ws ws;
-    if (!job) return PVV_ERR_INVALID;
     stage_timer tm(dbg, (cudaStream_t)job->stream);
     const int r = run_front(job, dbg, &d, &ws, &launches, tm);
     if (r != PVV_OK) return r;
     cudaStream_t st = (cudaStream_t)job->stream;
     cudaError_t e;
-    if ((e = pvv_launch_v3_finalize(d, ws, out_kp, dbg, st, &launches))) return fail_cuda(e);
+    if ((e = pvv_launch_v3_finalize(d, ws, out_kp, out_conf, dbg, st, &launches))) return fail_cuda(e);
     tm.mark();
     tm.finish();
     if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
+    t_last_launches = launches;
+    return PVV_OK;
+}
+
+int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, const pvv_debug *dbg)
+{
+    (void)confidence; (void)max_iter;  // unobservable in the reference: every round re-votes the same idxs (:553-582)
+    return run_v3(job, out_kp, nullptr, dbg);
+}
+
+int pvv_v5(const pvv_job *job, float confidence, int max_iter, float *out_kp, float *out_conf, const pvv_debug *dbg)
+{
+    (void)confidence; (void)max_iter;  // as in v3: idxs drawn once at :805, identical rounds
+    if (!out_conf) return PVV_ERR_INVALID;
+    return run_v3(job, out_kp, out_conf, dbg);
+}
+
+int pvv_hypotheses(const pvv_job *job, float *out_hyp, int32_t *out_counts, const pvv_debug *dbg)
+{
+    if (!out_hyp || !out_counts || !job) return PVV_ERR_INVALID;
+    int launches = 0;
+    pvv_dims d;
+    pvv_ws ws;
+    stage_timer tm(nullptr, (cudaStream_t)job->stream);
+    pvv_debug local;
+    memset(&local, 0, sizeof(local));
+    if (dbg) local = *dbg;
+    local.stage_ms = nullptr;
+    local.hyp = out_hyp;   // K2 writes the reference layout [b,hn,vn,2] directly
+    const int r = run_front(job, &local, &d, &ws, &launches, tm);
+    if (r != PVV_OK) return r;
+    cudaStream_t st = (cudaStream_t)job->stream;
+    cudaError_t e;
+    if ((e = pvv_launch_export_counts(d, ws, out_counts, st, &launches))) return fail_cuda(e);
+    local.counts = nullptr;
+    if (dbg && (e = pvv_launch_debug_export(d, ws, &local, st, &launches))) return fail_cuda(e);
     t_last_launches = launches;
     return PVV_OK;
 }

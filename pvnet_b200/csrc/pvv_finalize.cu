@@ -59,15 +59,17 @@ struct v3_dbg {
     long long dbg_cap;
 };
 
-__global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws ws, float *out_kp, v3_dbg g)
+__global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws ws, float *out_kp, float *out_conf, v3_dbg g)
 {
     __shared__ double s_buf[kFinThreads / 32];
+    __shared__ float2 s_pt;
     const int img = blockIdx.y, vi = blockIdx.x;
     const int tn = ws.tn[img];
     const long long o = (long long)img * d.vn + vi;
     if (tn == 0) {  // skipped image: zeros (:537-541)
         if (threadIdx.x == 0) {
             out_kp[o * 2] = 0.f; out_kp[o * 2 + 1] = 0.f;
+            if (out_conf) out_conf[o] = 0.f;                                          // v5: pts_conf zeros (:787-789)
             if (g.win_idx) g.win_idx[o] = 0;
             if (g.win_count) g.win_count[o] = 0;
             if (g.win_pts) { g.win_pts[o * 2] = 0.f; g.win_pts[o * 2 + 1] = 0.f; }
@@ -108,6 +110,7 @@ __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws 
         }
         out_kp[o * 2] = (float)x;
         out_kp[o * 2 + 1] = (float)y;
+        s_pt = make_float2((float)x, (float)y);
         if (g.win_idx) g.win_idx[o] = best_h;
         if (g.win_count) g.win_count[o] = best_cnt;
         if (g.win_pts) { g.win_pts[o * 2] = win.x; g.win_pts[o * 2 + 1] = win.y; }
@@ -116,6 +119,19 @@ __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws 
             q[0] = s00; q[1] = s01; q[2] = s11; q[3] = b0; q[4] = b1;
         }
     }
+    if (!out_conf) return;
+    // v5 confidence: re-vote the refined keypoint at the fixed threshold 0.999, conf = count / tn      (:854-856)
+    __syncthreads();
+    const float2 pt = s_pt;
+    double c = 0.0;
+    for (int t = threadIdx.x; t < tn; t += kFinThreads) {
+        const uint32_t xy = ws.pix_xy[off + t];
+        const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + t];
+        c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16), pt.x, pt.y,
+                            0.999f) ? 1.0 : 0.0;
+    }
+    c = block_sum(c, s_buf);
+    if (threadIdx.x == 0) out_conf[o] = __fdiv_rn((float)c, (float)tn);
 }
 
 __global__ void __launch_bounds__(kFinThreads) k_cov_finalize(pvv_dims d, pvv_ws ws, const float *mean, float *out_cov)
@@ -175,15 +191,15 @@ __global__ void k_export_counts(pvv_dims d, pvv_ws ws, int32_t *counts_out)
 
 }  // namespace
 
-cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, const pvv_debug *dbg,
-                                   cudaStream_t st, int *launches)
+cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, float *out_conf,
+                                   const pvv_debug *dbg, cudaStream_t st, int *launches)
 {
     v3_dbg g = {nullptr, nullptr, nullptr, nullptr, nullptr, 0};
     if (dbg) {
         g.win_idx = dbg->win_idx; g.win_count = dbg->win_count; g.win_pts = dbg->win_pts;
         g.win_inlier = dbg->win_inlier; g.normal_eq = dbg->normal_eq; g.dbg_cap = dbg->pool_capacity;
     }
-    k_v3_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, out_kp, g);
+    k_v3_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, out_kp, out_conf, g);
     ++*launches;
     return cudaGetLastError();
 }
@@ -192,6 +208,15 @@ cudaError_t pvv_launch_cov_finalize(const pvv_dims &d, const pvv_ws &ws, const f
                                     cudaStream_t st, int *launches)
 {
     k_cov_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, mean, out_cov);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t pvv_launch_export_counts(const pvv_dims &d, const pvv_ws &ws, int32_t *counts_out, cudaStream_t st,
+                                     int *launches)
+{
+    const long long total = (long long)d.b * d.hn * d.vn;
+    k_export_counts<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d, ws, counts_out);
     ++*launches;
     return cudaGetLastError();
 }

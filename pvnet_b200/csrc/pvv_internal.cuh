@@ -46,8 +46,10 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
                                   cudaStream_t st, int *launches);
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches);
 // K4 / K5: finalisation (pvv_finalize.cu)
-cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, const pvv_debug *dbg,
-                                   cudaStream_t st, int *launches);
+cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, float *out_conf,
+                                   const pvv_debug *dbg, cudaStream_t st, int *launches);
+cudaError_t pvv_launch_export_counts(const pvv_dims &d, const pvv_ws &ws, int32_t *counts_out, cudaStream_t st,
+                                     int *launches);
 cudaError_t pvv_launch_cov_finalize(const pvv_dims &d, const pvv_ws &ws, const float *mean, float *out_cov,
                                     cudaStream_t st, int *launches);
 cudaError_t pvv_launch_debug_export(const pvv_dims &d, const pvv_ws &ws, const pvv_debug *dbg, cudaStream_t st,

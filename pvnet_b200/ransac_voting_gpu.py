@@ -21,7 +21,7 @@ import torch
 
 from . import _lib
 
-__all__ = ["ransac_voting_layer_v3", "estimate_voting_distribution_with_mean", "ransac_voting", "torch_extension", "make_idxs",
+__all__ = ["ransac_voting_layer_v3", "ransac_voting_layer_v5", "generate_hypothesis", "estimate_voting_distribution_with_mean", "ransac_voting", "torch_extension", "make_idxs",
            "make_selection", "fp32_peak_tflops", "last_launch_count"]
 
 _MASK_DT = {torch.uint8: _lib.MASK_U8, torch.bool: _lib.MASK_U8, torch.int32: _lib.MASK_I32,
@@ -103,7 +103,7 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
          image_id_base, return_debug, force_exact, pool_capacity, stage_ms=None):
     L = _lib.lib()
     b, h, w, vn, _ = vertex.shape
-    fg_rule = _lib.FG_BYTE if kind == "v3" else _lib.FG_EQ1
+    fg_rule = _lib.FG_EQ1 if kind == "cov" else _lib.FG_BYTE
     mask = _prep_mask(mask)
     if seed is None:
         seed = _fresh_seed()
@@ -113,11 +113,14 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
     if not torch.cuda.is_available():
         raise RuntimeError("pvnet_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     dev = torch.device("cuda", torch.cuda.current_device()) if host else mask.device
-    out_shape = (b, vn, 2) if kind == "v3" else (b, vn, 2, 2)
+    out_shape = (b, vn, 2, 2) if kind == "cov" else (b, vn, 2)
 
     if host:
         if return_debug:
             raise ValueError("return_debug is only available for CUDA inputs")
+        if kind not in ("v3", "cov"):
+            raise ValueError("host-buffer calls are available for ransac_voting_layer_v3 and "
+                             "estimate_voting_distribution_with_mean")
         idxs_h = None if idxs is None else idxs.to(dtype=torch.int32).reshape(b, hn_total, vn, 2).contiguous()
         sel_h = None if selection is None else selection.to(dtype=torch.float32).reshape(b, h, w).contiguous()
         job = _make_job(mask, vertex, hn_total, thresh, min_num, max_num, fg_rule, idxs_h, sel_h, seed, image_id_base,
@@ -156,8 +159,16 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
         if stage_ms is not None:
             buf = (C.c_float * 5)()
             d.stage_ms = C.cast(buf, C.c_void_p)
+        extra = None
         if kind == "v3":
             st = L.pvv_v3(C.byref(job), float(confidence), int(max_iter), out.data_ptr(), dbg_ref)
+        elif kind == "v5":
+            extra = torch.empty((b, vn), dtype=torch.float32, device=dev)
+            st = L.pvv_v5(C.byref(job), float(confidence), int(max_iter), out.data_ptr(), extra.data_ptr(), dbg_ref)
+        elif kind == "hyp":
+            out = torch.empty((b, hn_total, vn, 2), dtype=torch.float32, device=dev)
+            extra = torch.empty((b, hn_total, vn), dtype=torch.int32, device=dev)
+            st = L.pvv_hypotheses(C.byref(job), out.data_ptr(), extra.data_ptr(), dbg_ref)
         else:
             mean_d = mean.to(device=dev, dtype=torch.float32).contiguous()
             st = L.pvv_cov(C.byref(job), mean_d.data_ptr(), out.data_ptr(), dbg_ref)
@@ -165,6 +176,8 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
         ws.record_stream(torch.cuda.current_stream(dev))
         if stage_ms is not None:
             stage_ms.append(dict(zip(("compact", "hypotheses", "count", "finalize", "total"), list(buf))))
+    if extra is not None:
+        out = (out, extra)
     if return_debug:
         dbg_t["seed"] = seed
         return out, dbg_t
@@ -181,6 +194,32 @@ def ransac_voting_layer_v3(mask, vertex, round_hyp_num, inlier_thresh=0.99, conf
     result: the reference draws idxs once (:553) and re-votes the same hypotheses every round."""
     return _run("v3", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
                 selection, seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms)
+
+
+def ransac_voting_layer_v5(mask, vertex, round_hyp_num, inlier_thresh=0.999, confidence=0.99, max_iter=20, min_num=5,
+                           max_num=100, *, idxs=None, selection=None, seed=None, image_id_base=0, return_debug=False,
+                           force_exact=False, pool_capacity=None):
+    """-> (keypoints [b,vn,2], confidence [b,vn]).  Reference: ransac_voting_gpu.py:769-864 = v3 with its own defaults
+    plus a re-vote of the refined keypoints at the fixed threshold 0.999 (:854-856); confidence = inlier count / tn,
+    zeros for skipped images (:786-791)."""
+    r = _run("v5", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
+             selection, seed, image_id_base, return_debug, force_exact, pool_capacity)
+    if return_debug:
+        return r[0][0], r[0][1], r[1]
+    return r
+
+
+def generate_hypothesis(mask, vertex, round_hyp_num, inlier_thresh=0.999, confidence=0.99, max_iter=20, min_num=5,
+                        max_num=30000, *, idxs=None, selection=None, seed=None, image_id_base=0, return_debug=False,
+                        force_exact=False, pool_capacity=None):
+    """-> (hypotheses [b,hn,vn,2] float32, inlier counts [b,hn,vn] int64).  Reference: ransac_voting_gpu.py:989-1040 (what
+    tools/demo.py:127 feeds to visualize_hypothesis).  Skipped images give zeros (the reference raises NameError there:
+    `batch_win_pts` is undefined at :1009)."""
+    r = _run("hyp", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
+             selection, seed, image_id_base, return_debug, force_exact, pool_capacity)
+    if return_debug:
+        return r[0][0], r[0][1].long(), r[1]
+    return r[0], r[1].long()
 
 
 def estimate_voting_distribution_with_mean(mask, vertex, mean, round_hyp_num=256, min_hyp_num=4096, topk=128,

@@ -136,6 +136,26 @@ def run_v3(ref, mask, vertex, hn, thresh, min_num, max_num, seed):
     return out, idxs, sel, first_counts
 
 
+def run_v5(ref, mask, vertex, hn, thresh, min_num, max_num, seed):
+    """Runs the reference's ransac_voting_layer_v5 (:769-864); returns (keypoints, confidence) plus the recorded draws."""
+    _clear()
+    torch.manual_seed(seed)
+    out, conf = ref.ransac_voting_layer_v5(torch.from_numpy(mask), torch.from_numpy(vertex), hn, inlier_thresh=thresh,
+                                           min_num=min_num, max_num=max_num)
+    b, h, w, vn, _ = vertex.shape
+    idxs = np.zeros((b, hn, vn, 2), np.int32)
+    sel = np.zeros((b, h, w), np.float32)
+    it_i, it_s = iter(LOG["idxs"]), iter(LOG["selection"])
+    for bi in range(b):
+        fg = int(torch.from_numpy(mask[bi]).byte().sum())
+        if fg < min_num:
+            continue
+        if fg > max_num:
+            sel[bi] = next(it_s)
+        idxs[bi] = next(it_i)
+    return out.numpy(), conf.numpy(), idxs, sel
+
+
 def run_cov(ref, mask, vertex, mean, round_hyp, min_hyp, thresh, min_num, max_num, seed):
     _clear()
     torch.manual_seed(seed)
@@ -193,6 +213,15 @@ def main():
                         v3_idxs=idxs, v3_sel=sel, v3_counts=counts, v3_out=out,
                         cov_idxs=cidxs, cov_sel=csel, cov=cov, cov_mean=m2,
                         v3_args=np.array([64, 50, 1500]), cov_args=np.array([32, 128, 20, 1500]))
+    # ---- G4: ransac_voting_layer_v5 the way EvalWrapper(use_uncertainty) calls it (tools/train_linemod.py:122-123):
+    # 128 hypotheses, thresh 0.99, max_num=100 (every image is subsampled), min_num=5 ----
+    mask5 = mask.copy()
+    mask5[1] = 0
+    mask5[1, 10, 10:13] = 1                       # 3 px < min_num = 5: skipped image -> zeros / zero confidence
+    k5, c5, i5, s5 = run_v5(ref, mask5, vertex, 128, 0.99, 5, 100, 13)
+    np.savez_compressed(os.path.join(OUT, "v5_small_batch.npz"), mask=mask5.astype(np.uint8), idxs=i5, sel=s5, out=k5,
+                        conf=c5, args=np.array([128, 5, 100]))
+    print("v5 conf\n", c5)
     print("small batch v3 out\n", out[:, :2], "\ncov[0,0]\n", cov[0, 0], "\nfg", [(int((mask[i] != 0).sum())) for i in range(b)])
 
 

@@ -336,3 +336,52 @@ def test_torch_extension_shim_equals_ctypes_path():
         c = ext.ransac_voting_layer_v3(tm, tv, 128, 0.99, seed=4)
     s.synchronize()
     assert torch.equal(a, c)
+
+
+def test_v5_golden_and_oracle(golden_dir):
+    """ransac_voting_layer_v5 = v3 + confidence re-vote at 0.999 (ransac_voting_gpu.py:769-864)."""
+    z = np.load(os.path.join(golden_dir, "v5_small_batch.npz"))
+    sb = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    mask, vertex = z["mask"].astype(np.int64), sb["vertex"]
+    hn, min_num, max_num = (int(v) for v in z["args"])
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    out, conf, dbg = pv.ransac_voting_layer_v5(tm, tv, hn, 0.99, min_num=min_num, max_num=max_num,
+                                               idxs=torch.from_numpy(z["idxs"]), selection=torch.from_numpy(z["sel"]),
+                                               return_debug=True)
+    assert out.shape == (4, 9, 2) and conf.shape == (4, 9) and conf.dtype == torch.float32
+    np.testing.assert_allclose(out.cpu().numpy(), z["out"], rtol=RTOL, atol=0)          # reference wrapper's output
+    o_out, o_conf, o_dbg = orc.ransac_voting_layer_v5(mask, vertex, hn, 0.99, min_num=min_num, max_num=max_num,
+                                                      idxs=z["idxs"], selection=z["sel"], return_debug=True)
+    np.testing.assert_allclose(out.cpu().numpy(), o_out, rtol=RTOL, atol=0)
+    tn = dbg["tn"].cpu().numpy()
+    assert tn[1] == 0 and torch.all(conf[1] == 0) and torch.all(out[1] == 0)
+    for bi in (0, 2, 3):
+        assert np.array_equal(dbg["counts"][bi].cpu().numpy(), o_dbg[bi]["counts"])
+        # the confidence count is exact for OUR refined point: recount it with the oracle kernel
+        inl = np.zeros((1, 9, tn[bi]), np.uint8)
+        orc.voting_for_hypothesis(o_dbg[bi]["direct"], o_dbg[bi]["coords"], out[bi].cpu().numpy()[None], inl, 0.999)
+        want = inl[0].astype(np.int64).sum(1).astype(np.float32) / np.float32(tn[bi])
+        assert np.array_equal(conf[bi].cpu().numpy(), want)
+        # and within one flipped pixel of the reference wrapper's confidence (its refined point differs in the last bits)
+        assert np.all(np.abs(conf[bi].cpu().numpy() - z["conf"][bi]) * tn[bi] <= 1.0 + 1e-3)
+    # defaults are v5's own (0.999, min_num 5, max_num 100), library draws
+    k2, c2 = pv.ransac_voting_layer_v5(tm, tv, 64, seed=3)
+    assert k2.shape == (4, 9, 2) and float(c2.max()) <= 1.0 and float(c2.min()) >= 0.0
+
+
+def test_generate_hypothesis_wrapper():
+    """ransac_voting_gpu.py:989-1040 (feeds demo.visualize_hypothesis): hypotheses + counts in the reference layouts."""
+    b, vn, hn = 3, 9, 256
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=23)
+    mask[1] = 0
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    hyp, counts, dbg = pv.generate_hypothesis(tm, tv, hn, inlier_thresh=0.99, seed=8, return_debug=True)
+    assert hyp.shape == (b, hn, vn, 2) and counts.shape == (b, hn, vn) and counts.dtype == torch.int64
+    o_hyp, o_counts = orc.generate_hypothesis_layer(mask, vertex, hn, 0.99, idxs=dbg["idxs"].cpu().numpy())
+    assert np.array_equal(_bits(hyp), _bits(o_hyp))
+    assert np.array_equal(counts.cpu().numpy(), o_counts)
+    assert torch.all(hyp[1] == 0) and torch.all(counts[1] == 0)
+    # same draws as v3 with the same seed: v3's winner is the argmax of these counts
+    out, d3 = pv.ransac_voting_layer_v3(tm, tv, hn, 0.99, seed=8, min_num=5, return_debug=True)
+    assert torch.equal(d3["counts"].long(), counts)
+    assert torch.equal(d3["win_idx"][0].long(), counts[0].argmax(0))

@@ -69,3 +69,35 @@ def test_kernels_edge_cases():
     # empty pixel set
     assert orc.vote_counts(np.zeros((0, 2, 2), np.float32), np.zeros((0, 2), np.float32),
                            np.ones((3, 2, 2), np.float32), 0.9).sum() == 0
+
+
+def test_v5_small_batch(golden_dir):
+    """ransac_voting_layer_v5 as EvalWrapper(use_uncertainty) calls it (tools/train_linemod.py:122-123): every image
+    subsampled to ~100 px, one image below min_num.  Fixture from the reference's own wrapper."""
+    z = np.load(os.path.join(golden_dir, "v5_small_batch.npz"))
+    sb = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    mask, vertex = z["mask"].astype(np.int64), sb["vertex"]
+    hn, min_num, max_num = (int(v) for v in z["args"])
+    out, conf, dbg = orc.ransac_voting_layer_v5(mask, vertex, hn, 0.99, min_num=min_num, max_num=max_num, idxs=z["idxs"],
+                                                selection=z["sel"], return_debug=True)
+    assert dbg[1] is None and np.all(out[1] == 0) and np.all(conf[1] == 0)         # skipped (:786-791)
+    np.testing.assert_allclose(out, z["out"], rtol=RTOL, atol=0)
+    for bi in (0, 2, 3):
+        tn = dbg[bi]["coords"].shape[0]
+        assert 30 < tn < 140       # Bernoulli(100/fg) subsample; fg = SUM of byte values, labels 1..3 in image 3
+        # confidence = count/tn; the refined point differs from the reference's fp32 result in the last bits, so
+        # allow one pixel of the re-vote to flip
+        assert np.all(np.abs(conf[bi] - z["conf"][bi]) * tn <= 1.0 + 1e-3)
+    assert np.mean(conf == z["conf"]) > 0.9
+
+
+def test_generate_hypothesis_layer_matches_v3_internals(golden_dir):
+    z = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    mask, vertex = z["mask"].astype(np.int64), z["vertex"]
+    hn, min_num, max_num = (int(v) for v in z["v3_args"])
+    hyp, counts = orc.generate_hypothesis_layer(mask, vertex, hn, 0.99, min_num=min_num, max_num=max_num,
+                                                idxs=z["v3_idxs"], selection=z["v3_sel"])
+    assert hyp.shape == (4, hn, 9, 2) and counts.dtype == np.int64
+    for bi in (0, 2, 3):
+        assert np.array_equal(counts[bi], z["v3_counts"][bi])      # what the reference wrapper's v3 counted
+    assert np.all(hyp[1] == 0) and np.all(counts[1] == 0)
