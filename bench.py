@@ -111,6 +111,7 @@ def cpu_leg(target_s=12.0, max_s=30.0):
     sample of the workload: whole 32-image batches of configs[1] until about `target_s` seconds of CPU work."""
     from oracle import oracle as orc
 
+    orc.use_all_host_threads()
     mask, vertex, idxs, tn = _cpu_inputs(B_PER_GPU)
     orc.ransac_voting_layer_v3(mask[:2], vertex[:2], HN, THRESH, idxs=idxs[:2])  # warm-up (library load, threads)
     t0 = time.perf_counter()
@@ -139,6 +140,7 @@ def run_reference(args):
         return
     from oracle import oracle as orc
 
+    orc.use_all_host_threads()
     mask, vertex, idxs, tn = _cpu_inputs(B_PER_GPU)
     warm = max(1, args.warmup)
     t0 = time.perf_counter()

@@ -104,6 +104,14 @@ def num_threads() -> int:
     return int(lib().orc_num_threads())
 
 
+def use_all_host_threads() -> int:
+    """Size the OpenMP pool to the cores this process may run on (torchrun sets OMP_NUM_THREADS=1 for its workers)."""
+    import os
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().orc_set_num_threads(int(n))
+    return num_threads()
+
+
 # ----------------------------------------------------------------------------
 # compaction (ransac_voting_gpu.py:533-552 / :339-361)
 # ----------------------------------------------------------------------------

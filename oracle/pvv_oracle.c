@@ -44,6 +44,16 @@ int orc_num_threads(void)
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU baseline asks for the host's cores explicitly */
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* direct [tn,vn,2], coords [tn,2] (x,y), idxs [hn,vn,2] -> hyp [hn,vn,2] */
 void orc_generate_hypothesis(const float *direct, const float *coords,
                              const int32_t *idxs, int tn, int vn, int hn,

@@ -66,6 +66,27 @@ int plan_host(const pvv_job *j, host_plan *P)
     return PVV_OK;
 }
 
+// One sub-batch [i0, i1) of the job on the compute stream; device-side inputs already point at the full arrays.
+int run_sub(const pvv_job &dj, int i0, int i1, bool cov, float confidence, int max_iter, const float *mean_dev,
+            float *out_dev, int *tn_dev)
+{
+    pvv_job sj = dj;
+    sj.b = i1 - i0;
+    sj.mask = (const char *)dj.mask + (size_t)i0 * dj.mask_strides[0] * mask_elem(dj.mask_dtype);
+    sj.vertex = dj.vertex + (long long)i0 * dj.vertex_strides[0];
+    if (dj.idxs) sj.idxs = dj.idxs + (size_t)i0 * dj.hn_total * dj.vn * 2;
+    if (dj.selection) sj.selection = dj.selection + (size_t)i0 * dj.h * dj.w;
+    sj.image_id_base = dj.image_id_base + i0;
+    pvv_debug dbg;
+    memset(&dbg, 0, sizeof(dbg));
+    dbg.tn = tn_dev + i0;
+    if (cov) return pvv_cov(&sj, mean_dev + (size_t)i0 * dj.vn * 2, out_dev + (size_t)i0 * dj.vn * 4, &dbg);
+    return pvv_v3(&sj, confidence, max_iter, out_dev + (size_t)i0 * dj.vn * 2, &dbg);
+}
+
+// Host-buffer call.  With pinned inputs the batch is cut into up to 4 sub-batches: the mask of sub-batch s+1 crosses
+// PCIe on an internal copy stream while sub-batch s is compacted (its foreground vectors gathered in place over PCIe)
+// and voted on the caller's stream, so the bus and the SMs work at the same time.
 int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const float *mean_host, float *out_host,
              int64_t *h2d_bytes, int64_t *d2h_bytes)
 {
@@ -73,16 +94,23 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     int r = plan_host(j, &P);
     if (r != PVV_OK) return r;
     if (!j->workspace || j->workspace_bytes < P.total || !out_host) return PVV_ERR_WORKSPACE;
+    if (cov && !mean_host) return PVV_ERR_INVALID;
     cudaStream_t st = (cudaStream_t)j->stream;
     char *base = (char *)j->workspace;
     int64_t h2d = 0, d2h = 0;
     cudaError_t e;
     pvv_job dj = *j;
     dj.workspace_bytes = P.dev_ws;
-    const size_t mbytes = (size_t)P.mask_span * mask_elem(j->mask_dtype);
-    if ((e = cudaMemcpyAsync(base + P.o_mask, j->mask, mbytes, cudaMemcpyHostToDevice, st))) return PVV_ERR_CUDA;
     dj.mask = base + P.o_mask;
+    const size_t esz = mask_elem(j->mask_dtype);
+    const size_t mbytes = (size_t)P.mask_span * esz;
     h2d += (int64_t)mbytes;
+    void *pin_dummy = nullptr;
+    const bool mask_pinned = is_pinned(j->mask, &pin_dummy);
+    // the mask is copied per sub-batch only when images are laid out one after the other (stride[0] covers an image)
+    const bool separable = j->mask_strides[0] >= (int64_t)(j->h - 1) * j->mask_strides[1] + (int64_t)(j->w - 1) * j->mask_strides[2] + 1;
+    const int nsub = (mask_pinned && P.vertex_zero_copy && separable && j->b >= 8) ? 4 : 1;
+
     if (P.vertex_zero_copy) {
         dj.vertex = (const float *)P.vertex_dev;
     } else {
@@ -103,36 +131,61 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
         dj.selection = (const float *)(base + P.o_sel);
         h2d += (int64_t)n;
     }
-    pvv_debug dbg;
-    memset(&dbg, 0, sizeof(dbg));
-    dbg.tn = (int32_t *)(base + P.o_tn);
-    float *out_dev = (float *)(base + P.o_out);
-    size_t out_bytes;
+    const float *mean_dev = (const float *)(base + P.o_mean);
     if (cov) {
-        if (!mean_host) return PVV_ERR_INVALID;
         const size_t n = sizeof(float) * (size_t)j->b * j->vn * 2;
         if ((e = cudaMemcpyAsync(base + P.o_mean, mean_host, n, cudaMemcpyHostToDevice, st))) return PVV_ERR_CUDA;
         h2d += (int64_t)n;
-        r = pvv_cov(&dj, (const float *)(base + P.o_mean), out_dev, &dbg);
-        out_bytes = sizeof(float) * (size_t)j->b * j->vn * 4;
-    } else {
-        r = pvv_v3(&dj, confidence, max_iter, out_dev, &dbg);
-        out_bytes = sizeof(float) * (size_t)j->b * j->vn * 2;
     }
-    if (r != PVV_OK) return r;
+    float *out_dev = (float *)(base + P.o_out);
+    int *tn_dev = (int *)(base + P.o_tn);
+    const size_t out_bytes = sizeof(float) * (size_t)j->b * j->vn * (cov ? 4 : 2);
+
+    if (nsub == 1) {
+        if ((e = cudaMemcpyAsync(base + P.o_mask, j->mask, mbytes, cudaMemcpyHostToDevice, st))) return PVV_ERR_CUDA;
+        r = run_sub(dj, 0, j->b, cov, confidence, max_iter, mean_dev, out_dev, tn_dev);
+        if (r != PVV_OK) return r;
+    } else {
+        cudaStream_t cs = nullptr;
+        cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+        bool ok = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess;
+        for (int i = 0; ok && i < 5; ++i) ok = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) == cudaSuccess;
+        // the copy stream starts after whatever the caller's stream did before (the workspace may still be in use)
+        ok = ok && cudaEventRecord(ev[4], st) == cudaSuccess && cudaStreamWaitEvent(cs, ev[4], 0) == cudaSuccess;
+        r = PVV_OK;
+        for (int s = 0; ok && s < nsub; ++s) {
+            const int i0 = (int)((long long)j->b * s / nsub), i1 = (int)((long long)j->b * (s + 1) / nsub);
+            const size_t o0 = (size_t)i0 * j->mask_strides[0] * esz;
+            const size_t o1 = s + 1 == nsub ? mbytes : (size_t)i1 * j->mask_strides[0] * esz;
+            ok = cudaMemcpyAsync(base + P.o_mask + o0, (const char *)j->mask + o0, o1 - o0, cudaMemcpyHostToDevice, cs) ==
+                     cudaSuccess &&
+                 cudaEventRecord(ev[s], cs) == cudaSuccess;
+        }
+        for (int s = 0; ok && r == PVV_OK && s < nsub; ++s) {
+            const int i0 = (int)((long long)j->b * s / nsub), i1 = (int)((long long)j->b * (s + 1) / nsub);
+            ok = cudaStreamWaitEvent(st, ev[s], 0) == cudaSuccess;
+            if (ok) r = run_sub(dj, i0, i1, cov, confidence, max_iter, mean_dev, out_dev, tn_dev);
+        }
+        // destroying an event / a stream with work in flight is legal: the resources go away when that work completes,
+        // and the caller's stream already waits on every copy through the events
+        for (int i = 0; i < 5; ++i) if (ev[i]) cudaEventDestroy(ev[i]);
+        if (cs) cudaStreamDestroy(cs);
+        if (r != PVV_OK) return r;
+        if (!ok) { cudaGetLastError(); return PVV_ERR_CUDA; }
+    }
     if ((e = cudaMemcpyAsync(out_host, out_dev, out_bytes, cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
     d2h += (int64_t)out_bytes;
     if (P.vertex_zero_copy && h2d_bytes) {
         // account the foreground vectors the scatter kernel pulled over the bus: sum(tn) * vn * 8 bytes
         int *tn_host = (int *)malloc(sizeof(int) * j->b);
         if (!tn_host) return PVV_ERR_INVALID;
-        e = cudaMemcpyAsync(tn_host, dbg.tn, sizeof(int) * j->b, cudaMemcpyDeviceToHost, st);
+        e = cudaMemcpyAsync(tn_host, tn_dev, sizeof(int) * j->b, cudaMemcpyDeviceToHost, st);
         if (!e) e = cudaStreamSynchronize(st);
-        long long s = 0;
-        for (int i = 0; i < j->b; ++i) s += tn_host[i];
+        long long sum = 0;
+        for (int i = 0; i < j->b; ++i) sum += tn_host[i];
         free(tn_host);
         if (e) return PVV_ERR_CUDA;
-        h2d += s * j->vn * 8;
+        h2d += sum * j->vn * 8;
         d2h += (int64_t)sizeof(int) * j->b;
     } else {
         if ((e = cudaStreamSynchronize(st))) return PVV_ERR_CUDA;
