@@ -248,7 +248,7 @@ def run_ours(args):
         traffic, traffic_src = t["dram_bytes_per_launch"], t["source"]
     except Exception:
         pass
-    k1_bytes = mask.nbytes + tn_total * VN * 8 + tn_total * (4 + VN * 8) + mask.nbytes  # mask read twice (count, scatter)
+    k1_bytes = mask.nbytes + tn_total * VN * 8 + tn_total * (4 + VN * 8) + 2 * (mask.size // 8)  # mask once; bitmask w+r
     roofline = {"kernel": "k_count (K3 fused inlier counting)", "bound": "fp32", "achieved": achieved, "peak": peak,
                 "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
                 "bound_note": "FP32 SIMT compare/reduce (north_star: no tensor cores); HBM traffic of this kernel is ~0.6% of peak",

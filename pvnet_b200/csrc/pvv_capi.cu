@@ -45,7 +45,7 @@ long long default_cap(const pvv_job *j)
 
 struct layout {
     size_t zero_bytes, total_bytes;
-    size_t o_counters, o_img_fg, o_counts, o_flags, o_tn, o_img_off, o_chunk, o_tile_cnt, o_tile_off, o_xy, o_dir, o_hyp;
+    size_t o_counters, o_img_fg, o_counts, o_ticket, o_part, o_flags, o_tn, o_img_off, o_chunk, o_tile_cnt, o_tile_off, o_bits, o_xy, o_dir, o_hyp;
     long long cap;
     int ntiles, hn_pad;
 };
@@ -61,6 +61,7 @@ layout make_layout(const pvv_job *j)
     L.o_counters = take(16 * sizeof(unsigned));
     L.o_img_fg = take(sizeof(long long) * j->b);
     L.o_counts = take(sizeof(int) * (size_t)j->b * j->vn * L.hn_pad);
+    L.o_ticket = take(sizeof(unsigned) * (size_t)j->b * j->vn);
     L.zero_bytes = o;
     L.o_flags = take(sizeof(int) * j->b);
     L.o_tn = take(sizeof(int) * j->b);
@@ -68,9 +69,11 @@ layout make_layout(const pvv_job *j)
     L.o_chunk = take(sizeof(int) * (j->b + 1));
     L.o_tile_cnt = take(sizeof(int) * (size_t)j->b * L.ntiles);
     L.o_tile_off = take(sizeof(int) * (size_t)j->b * L.ntiles);
+    L.o_bits = take(sizeof(uint32_t) * (size_t)j->b * L.ntiles * (PVV_TILE_PX / 32));
     L.o_xy = take(sizeof(uint32_t) * (size_t)L.cap);
     L.o_dir = take(sizeof(float2) * (size_t)L.cap * j->vn);
     L.o_hyp = take(sizeof(float2) * (size_t)j->b * j->vn * L.hn_pad);
+    L.o_part = take(sizeof(double) * (size_t)j->b * j->vn * PVV_FIN_SPLIT * 5);
     L.total_bytes = o;
     return L;
 }
@@ -88,9 +91,12 @@ pvv_ws carve(const layout &L, void *base)
     ws.chunk_start = (int *)(p + L.o_chunk);
     ws.tile_cnt = (int *)(p + L.o_tile_cnt);
     ws.tile_off = (int *)(p + L.o_tile_off);
+    ws.fg_bits = (uint32_t *)(p + L.o_bits);
     ws.pix_xy = (uint32_t *)(p + L.o_xy);
     ws.pix_dir = (float2 *)(p + L.o_dir);
     ws.hyp = (float2 *)(p + L.o_hyp);
+    ws.fin_ticket = (unsigned *)(p + L.o_ticket);
+    ws.fin_part = (double *)(p + L.o_part);
     ws.idxs_used = nullptr;
     ws.cap = L.cap;
     ws.ntiles = L.ntiles;

@@ -9,9 +9,10 @@
 // The output is a pooled SoA buffer (pix_xy[cap], pix_dir[vn][cap]) in the same row-major order
 // torch.nonzero produces, so pixel index t of image i here == row t of the reference's coords/direct.
 //
-// Four launches: tile counts -> (optional) recount under subsampling -> per-image scan + batch scan by the
-// last block -> scatter.  The mask is read through its real strides and dtype; the vertex tensor is read
-// through its real strides (the network emits a permuted view), only at foreground pixels.
+// Four launches: tile counts + foreground bitmask (the only pass over the mask) -> (optional) Bernoulli selection
+// applied to the bitmask of images above max_num -> per-image scan + batch scan by the last block -> scatter from the
+// bitmask.  The mask is read ONCE through its real strides and dtype; the vertex tensor is read through its real
+// strides (the network emits a permuted view), only at foreground pixels.
 #include "pvv_internal.cuh"
 
 namespace {
@@ -57,40 +58,57 @@ __device__ __forceinline__ float sel_value(const pvv_dims &d, const float *selec
     return pvv_draw_uniform(d.seed, d.image_id_base + img, p);
 }
 
-// foreground flags of this thread's 4 consecutive pixels (bit k = pixel p0+k), plus the byte-value sum
-__device__ __forceinline__ uint32_t load_flags(const pvv_dims &d, const void *mask, int img, int p0, uint32_t *bsum)
+// ---- K1a: the ONE pass over the mask: foreground bitmask + per-tile count + per-image foreground sum ----------
+// Thread t of the CTA reads pixels t, t+256, t+512, t+768 of the tile (fully coalesced for a contiguous mask of any
+// dtype); one ballot per warp and step yields a 32-pixel word of the bitmask in pixel order.
+// DT: mask element type (compile-time: no per-element dispatch); LINEAR: rows are contiguous and adjacent, so the
+// element offset is img*stride0 + pixel (no division).
+template <int DT>
+__device__ __forceinline__ uint32_t mask_value_t(const void *mask, long long off, int fg_rule)
 {
-    const int npx = d.h * d.w;
-    uint32_t flags = 0, s = 0;
-    int y = p0 / d.w, x = p0 - y * d.w;
-#pragma unroll
-    for (int k = 0; k < kPxPerThread; ++k) {
-        if (p0 + k < npx) {
-            const uint32_t v = pvv_mask_value(mask, d.mask_dtype, img * d.ms[0] + y * d.ms[1] + x * d.ms[2], d.fg_rule);
-            s += v;
-            flags |= (v != 0u) << k;
-        }
-        if (++x == d.w) { x = 0; ++y; }
+    long long v;
+    if (DT == PVV_MASK_U8) v = ((const uint8_t *)mask)[off];
+    else if (DT == PVV_MASK_I32) v = ((const int32_t *)mask)[off];
+    else if (DT == PVV_MASK_I64) v = ((const long long *)mask)[off];
+    else {  // float: .byte() truncates toward zero, == 1 compares the float
+        const float f = ((const float *)mask)[off];
+        if (fg_rule == PVV_FG_EQ1) return f == 1.0f ? 1u : 0u;
+        v = (long long)f;
     }
-    *bsum = s;
-    return flags;
+    if (fg_rule == PVV_FG_EQ1) return v == 1 ? 1u : 0u;
+    return (uint32_t)(v & 0xFF);
 }
 
-// ---- K1a: per-tile foreground count + per-image foreground sum ------------------------------------
+template <int DT, bool LINEAR>
 __global__ void __launch_bounds__(kThreads) k_tile_count(pvv_dims d, const void *mask, pvv_ws ws)
 {
     const int img = blockIdx.y, tile = blockIdx.x;
-    uint32_t bsum;
-    const uint32_t flags = load_flags(d, mask, img, tile * PVV_TILE_PX + threadIdx.x * kPxPerThread, &bsum);
-    int n = __popc(flags);
-    int s = (int)bsum;
+    const int npx = d.h * d.w;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t *bits = ws.fg_bits + ((long long)img * ws.ntiles + tile) * (PVV_TILE_PX / 32);
+    uint32_t v[kPxPerThread];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        n += __shfl_xor_sync(0xffffffffu, n, o);
-        s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int k = 0; k < kPxPerThread; ++k) {  // all loads first: 4 independent requests in flight per thread
+        const int p = tile * PVV_TILE_PX + k * kThreads + threadIdx.x;
+        v[k] = 0;
+        if (p < npx) {
+            long long off;
+            if (LINEAR) off = img * d.ms[0] + p;
+            else { const int y = p / d.w, x = p - y * d.w; off = img * d.ms[0] + y * d.ms[1] + x * d.ms[2]; }
+            v[k] = mask_value_t<DT>(mask, off, d.fg_rule);
+        }
     }
+    int n = 0, s = 0;
+#pragma unroll
+    for (int k = 0; k < kPxPerThread; ++k) {
+        const uint32_t word = __ballot_sync(0xffffffffu, v[k] != 0u);
+        if (lane == 0) { bits[k * (kThreads / 32) + wid] = word; n += __popc(word); }
+        s += (int)v[k];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     __shared__ int s_n[kThreads / 32], s_s[kThreads / 32];
-    if ((threadIdx.x & 31) == 0) { s_n[threadIdx.x >> 5] = n; s_s[threadIdx.x >> 5] = s; }
+    if (lane == 0) { s_n[wid] = n; s_s[wid] = s; }
     __syncthreads();
     if (threadIdx.x == 0) {
         int tn = 0, ts = 0;
@@ -101,32 +119,36 @@ __global__ void __launch_bounds__(kThreads) k_tile_count(pvv_dims d, const void 
     }
 }
 
-// ---- K1a': recount tiles of images that get subsampled ---------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_tile_recount(pvv_dims d, const void *mask, const float *selection,
-                                                           pvv_ws ws)
+template <int DT>
+static void launch_tile_count(const pvv_dims &d, const void *mask, const pvv_ws &ws, dim3 grid, cudaStream_t st)
 {
-    const int img = blockIdx.y, tile = blockIdx.x;
+    const bool linear = d.ms[2] == 1 && d.ms[1] == d.w;
+    if (linear) k_tile_count<DT, true><<<grid, kThreads, 0, st>>>(d, mask, ws);
+    else k_tile_count<DT, false><<<grid, kThreads, 0, st>>>(d, mask, ws);
+}
+
+// ---- K1a': images above max_num: apply the Bernoulli selection to the bitmask, recount their tiles ------------
+// One warp per tile (lane = one 32-pixel word); a CTA whose image is not subsampled exits at once.
+__global__ void __launch_bounds__(kThreads) k_tile_recount(pvv_dims d, const float *selection, pvv_ws ws)
+{
+    const int img = blockIdx.y;
     const long long fg = ws.img_fg[img];
     if (fg <= d.max_num || fg < d.min_num) return;
+    const int tile = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (tile >= ws.ntiles) return;
     const float prob = pvv_subsample_prob(d.max_num, fg);
-    const int p0 = tile * PVV_TILE_PX + threadIdx.x * kPxPerThread;
-    uint32_t bsum;
-    uint32_t flags = load_flags(d, mask, img, p0, &bsum);
-    int n = 0;
-#pragma unroll
-    for (int k = 0; k < kPxPerThread; ++k)
-        if ((flags >> k) & 1u) n += sel_value(d, selection, img, (uint32_t)(p0 + k)) < prob;
+    uint32_t *bits = ws.fg_bits + ((long long)img * ws.ntiles + tile) * (PVV_TILE_PX / 32);
+    uint32_t word = bits[lane], keep = 0u;
+    while (word) {
+        const int bit = __ffs(word) - 1;
+        word &= word - 1;
+        if (sel_value(d, selection, img, (uint32_t)(tile * PVV_TILE_PX + lane * 32 + bit)) < prob) keep |= 1u << bit;
+    }
+    bits[lane] = keep;
+    int n = __popc(keep);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-    __shared__ int s_n[kThreads / 32];
-    if ((threadIdx.x & 31) == 0) s_n[threadIdx.x >> 5] = n;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int tn = 0;
-#pragma unroll
-        for (int i = 0; i < kThreads / 32; ++i) tn += s_n[i];
-        ws.tile_cnt[img * ws.ntiles + tile] = tn;
-    }
+    if (lane == 0) ws.tile_cnt[img * ws.ntiles + tile] = n;
 }
 
 // ---- K1c: per-image exclusive scan of tile counts; the last block scans the batch ------------------
@@ -188,49 +210,57 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
     if (threadIdx.x == 0) ws.chunk_start[d.b] = chunk;
 }
 
-// ---- K1d: scatter ----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const void *mask, const float *vertex,
-                                                      const float *selection, pvv_ws ws)
+// ---- K1d: scatter (reads the bitmask, not the mask) ------------------------------------------------
+constexpr int kTilesPerCta = 4;  // empty tiles (most of an image) cost one load, not one CTA
+
+__global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *vertex, pvv_ws ws)
 {
-    const int img = blockIdx.y, tile = blockIdx.x;
+    const int img = blockIdx.y;
     const int tn = ws.tn[img];
     if (tn == 0) return;
-    const int cnt = ws.tile_cnt[img * ws.ntiles + tile];
-    if (cnt == 0) return;
-    const int iflags = ws.img_flags[img];
-    const int p0 = tile * PVV_TILE_PX + threadIdx.x * kPxPerThread;
-    uint32_t bsum;
-    uint32_t flags = load_flags(d, mask, img, p0, &bsum);
-    if (iflags & PVV_IMG_SUBSAMPLED) {
-        const float prob = pvv_subsample_prob(d.max_num, ws.img_fg[img]);
+    __shared__ uint32_t s_xy[PVV_TILE_PX];
+    __shared__ long long s_off[PVV_TILE_PX];
+    for (int tile = blockIdx.x * kTilesPerCta; tile < min(ws.ntiles, (blockIdx.x + 1) * kTilesPerCta); ++tile) {
+        const int cnt = ws.tile_cnt[img * ws.ntiles + tile];
+        if (cnt == 0) continue;  // CTA-uniform
+        // this thread's 4 consecutive pixels of the tile: one nibble of the bitmask
+        const uint32_t *bits = ws.fg_bits + ((long long)img * ws.ntiles + tile) * (PVV_TILE_PX / 32);
+        const int q0 = threadIdx.x * kPxPerThread;
+        const uint32_t flags = (bits[q0 >> 5] >> (q0 & 31)) & 0xFu;
+        const int p0 = tile * PVV_TILE_PX + q0;
+        int total;
+        int rank = block_excl_scan(__popc(flags), &total);  // total == cnt: the bitmask is what was counted
+        if (flags) {
+            int y = p0 / d.w, x = p0 - y * d.w;
 #pragma unroll
-        for (int k = 0; k < kPxPerThread; ++k)
-            if (((flags >> k) & 1u) && !(sel_value(d, selection, img, (uint32_t)(p0 + k)) < prob)) flags &= ~(1u << k);
-    }
-    __shared__ int s_list[PVV_TILE_PX];
-    int total;
-    int rank = block_excl_scan(__popc(flags), &total);
-#pragma unroll
-    for (int k = 0; k < kPxPerThread; ++k)
-        if ((flags >> k) & 1u) s_list[rank++] = p0 + k;
-    __syncthreads();
-    // total == cnt by construction (same deterministic predicate as the count pass)
-    const long long base = ws.img_off[img] + ws.tile_off[img * ws.ntiles + tile];
-    for (int j = threadIdx.x; j < total; j += kThreads) {
-        const int p = s_list[j];
-        const int y = p / d.w, x = p - y * d.w;
-        ws.pix_xy[base + j] = (uint32_t)x | ((uint32_t)y << 16);
-    }
-    const int work = total * d.vn;
-    for (int e = threadIdx.x; e < work; e += kThreads) {
-        const int vi = e / total, j = e - vi * total;
-        const int p = s_list[j];
-        const int y = p / d.w, x = p - y * d.w;
-        const long long vo = img * d.vs[0] + y * d.vs[1] + x * d.vs[2] + vi * d.vs[3];
-        float2 v;
-        v.x = __ldg(vertex + vo);
-        v.y = __ldg(vertex + vo + d.vs[4]);
-        ws.pix_dir[(long long)vi * ws.cap + base + j] = v;
+            for (int k = 0; k < kPxPerThread; ++k) {
+                if ((flags >> k) & 1u) {
+                    s_xy[rank] = (uint32_t)x | ((uint32_t)y << 16);
+                    s_off[rank] = img * d.vs[0] + y * d.vs[1] + x * d.vs[2];
+                    ++rank;
+                }
+                if (++x == d.w) { x = 0; ++y; }
+            }
+        }
+        __syncthreads();
+        const long long base = ws.img_off[img] + ws.tile_off[img * ws.ntiles + tile];
+        // consecutive threads take consecutive pixels (coalesced along x inside a keypoint plane); every thread walks the
+        // keypoints of its pixel
+        for (int j = threadIdx.x; j < total; j += kThreads) {
+            ws.pix_xy[base + j] = s_xy[j];
+            const float *src = vertex + s_off[j];
+            float2 *dst = ws.pix_dir + base + j;
+            // 3 keypoints (6 loads) in flight per thread: measured best -- 18 in flight is 1.7x slower (the planes of one
+            // image are 1.2 MB apart: too many open DRAM pages / TLB entries per warp)
+#pragma unroll 3
+            for (int vi = 0; vi < d.vn; ++vi) {
+                float2 v;
+                v.x = __ldg(src + vi * d.vs[3]);
+                v.y = __ldg(src + vi * d.vs[3] + d.vs[4]);
+                dst[(long long)vi * ws.cap] = v;
+            }
+        }
+        __syncthreads();  // s_xy / s_off are reused by the next tile
     }
 }
 
@@ -240,14 +270,20 @@ cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float 
                                const pvv_ws &ws, cudaStream_t st, int *launches)
 {
     const dim3 grid(ws.ntiles, d.b);
-    k_tile_count<<<grid, kThreads, 0, st>>>(d, mask, ws);
+    switch (d.mask_dtype) {
+        case PVV_MASK_U8: launch_tile_count<PVV_MASK_U8>(d, mask, ws, grid, st); break;
+        case PVV_MASK_I32: launch_tile_count<PVV_MASK_I32>(d, mask, ws, grid, st); break;
+        case PVV_MASK_I64: launch_tile_count<PVV_MASK_I64>(d, mask, ws, grid, st); break;
+        default: launch_tile_count<PVV_MASK_F32>(d, mask, ws, grid, st); break;
+    }
     ++*launches;
     if ((long long)d.max_num < (long long)d.h * d.w * (d.fg_rule == PVV_FG_BYTE ? 255 : 1)) {
-        k_tile_recount<<<grid, kThreads, 0, st>>>(d, mask, selection, ws);
+        const dim3 rgrid((ws.ntiles + kThreads / 32 - 1) / (kThreads / 32), d.b);
+        k_tile_recount<<<rgrid, kThreads, 0, st>>>(d, selection, ws);
         ++*launches;
     }
     k_scan<<<d.b, kThreads, 0, st>>>(d, ws);
-    k_scatter<<<grid, kThreads, 0, st>>>(d, mask, vertex, selection, ws);
+    k_scatter<<<dim3((ws.ntiles + kTilesPerCta - 1) / kTilesPerCta, d.b), kThreads, 0, st>>>(d, vertex, ws);
     *launches += 2;
     return cudaGetLastError();
 }

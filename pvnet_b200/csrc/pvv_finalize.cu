@@ -59,15 +59,19 @@ struct v3_dbg {
     long long dbg_cap;
 };
 
+// grid (vn, b, PVV_FIN_SPLIT): the pixels of one (image, keypoint) are shared by PVV_FIN_SPLIT CTAs; each writes its
+// partial normal equations to its own slot and the last one to arrive adds the slots in a fixed order (deterministic,
+// unlike float atomics) and solves.
 __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws ws, float *out_kp, float *out_conf, v3_dbg g)
 {
     __shared__ double s_buf[kFinThreads / 32];
     __shared__ float2 s_pt;
-    const int img = blockIdx.y, vi = blockIdx.x;
+    __shared__ bool s_last;
+    const int img = blockIdx.y, vi = blockIdx.x, part = blockIdx.z;
     const int tn = ws.tn[img];
     const long long o = (long long)img * d.vn + vi;
     if (tn == 0) {  // skipped image: zeros (:537-541)
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0 && part == 0) {
             out_kp[o * 2] = 0.f; out_kp[o * 2 + 1] = 0.f;
             if (out_conf) out_conf[o] = 0.f;                                          // v5: pts_conf zeros (:787-789)
             if (g.win_idx) g.win_idx[o] = 0;
@@ -85,7 +89,7 @@ __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws 
 
     const long long off = ws.img_off[img];
     double s00 = 0, s01 = 0, s11 = 0, b0 = 0, b1 = 0;
-    for (int t = threadIdx.x; t < tn; t += kFinThreads) {
+    for (int t = part * kFinThreads + threadIdx.x; t < tn; t += kFinThreads * PVV_FIN_SPLIT) {
         const uint32_t xy = ws.pix_xy[off + t];
         const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + t];
         const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
@@ -102,6 +106,21 @@ __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws 
     s00 = block_sum(s00, s_buf); s01 = block_sum(s01, s_buf); s11 = block_sum(s11, s_buf);
     b0 = block_sum(b0, s_buf); b1 = block_sum(b1, s_buf);
     if (threadIdx.x == 0) {
+        double *slot = ws.fin_part + (o * PVV_FIN_SPLIT + part) * 5;
+        slot[0] = s00; slot[1] = s01; slot[2] = s11; slot[3] = b0; slot[4] = b1;
+        __threadfence();
+        s_last = atomicAdd(&ws.fin_ticket[o], 1u) == PVV_FIN_SPLIT - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s00 = s01 = s11 = b0 = b1 = 0.0;
+        const volatile double *slots = ws.fin_part + o * PVV_FIN_SPLIT * 5;
+        for (int p = 0; p < PVV_FIN_SPLIT; ++p) {  // fixed order: bit-reproducible sums
+            s00 += slots[p * 5 + 0]; s01 += slots[p * 5 + 1]; s11 += slots[p * 5 + 2];
+            b0 += slots[p * 5 + 3]; b1 += slots[p * 5 + 4];
+        }
         const double det = s00 * s11 - s01 * s01;
         double x = b0, y = b1;  // b_inv's identity fallback (:516-517), applied per keypoint
         if (det != 0.0 && isfinite(det)) {
@@ -199,7 +218,7 @@ cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *o
         g.win_idx = dbg->win_idx; g.win_count = dbg->win_count; g.win_pts = dbg->win_pts;
         g.win_inlier = dbg->win_inlier; g.normal_eq = dbg->normal_eq; g.dbg_cap = dbg->pool_capacity;
     }
-    k_v3_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, out_kp, out_conf, g);
+    k_v3_finalize<<<dim3(d.vn, d.b, PVV_FIN_SPLIT), kFinThreads, 0, st>>>(d, ws, out_kp, out_conf, g);
     ++*launches;
     return cudaGetLastError();
 }

@@ -8,6 +8,7 @@ struct pvv_ws {
     unsigned int *counters;       // [16] see PVV_CTR_*
     long long *img_fg;            // [b]  v3: sum of byte values; eq1: number of ==1 pixels   (K1a, atomics)
     int *counts;                  // [b][vn][hn]  inlier counts (K3, atomics)
+    unsigned int *fin_ticket;     // [b][vn]      arrival counter of the K4 pixel-range splits
     // --- written before read ---
     int *img_flags;               // [b]  PVV_IMG_*
     int *tn;                      // [b]  compacted pixels per image (0 when skipped)
@@ -15,9 +16,12 @@ struct pvv_ws {
     int *chunk_start;             // [b+1] first voting chunk of each image; [b] = total
     int *tile_cnt;                // [b][ntiles] foreground pixels per compaction tile
     int *tile_off;                // [b][ntiles] exclusive prefix of tile_cnt within the image
+    uint32_t *fg_bits;            // [b][ntiles][32] foreground bitmask (bit i of word w = pixel 32w+i of the tile), after
+                                  //                 subsampling: the mask itself is read exactly once
     uint32_t *pix_xy;             // [cap]      x | y<<16
     float2 *pix_dir;              // [vn][cap]  raw direction vectors (SoA over keypoints)
     float2 *hyp;                  // [b][vn][hn] hypotheses
+    double *fin_part;             // [b][vn][PVV_FIN_SPLIT][5] partial normal equations of the K4 splits
     int32_t *idxs_used;           // optional debug [b][hn][vn][2]
     long long cap;
     int ntiles;

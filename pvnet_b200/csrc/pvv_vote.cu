@@ -66,7 +66,7 @@ struct band_consts {
 };
 
 constexpr int K3_GROUP = 8;    // pixels per band-check group in the hot loop (four packed pixel pairs)
-constexpr int K3_QCAP = 1024;  // deferred (thread, pixel group) entries per work item; overflow is resolved in line
+constexpr int K3_QCAP = 512;   // deferred (thread, pixel group) entries per work item; overflow is resolved in line
 constexpr int K3_PAIRS = PVV_CHUNK_PX / 2;
 
 // packed FP32x2 helpers: Blackwell issues one FFMA2 for two IEEE fp32 FMAs (half the issue slots of two FFMAs)
@@ -225,8 +225,8 @@ __device__ __forceinline__ void cp_async8(void *smem, const void *gmem)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <int H, int THREADS>
-__global__ void __launch_bounds__(THREADS) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
+template <int H, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
 {
     static_assert(THREADS <= 256 && H <= 8 && PVV_CHUNK_PX / K3_GROUP <= 32, "entry packing");
     __shared__ __align__(16) float sP[12 * K3_PAIRS];
@@ -458,13 +458,13 @@ static bool pvv_band_for(float t, band_consts *bc)
     return true;
 }
 
-template <int H, int THREADS>
+template <int H, int THREADS, int MINB>
 static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st)
 {
     int per_sm = 8;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS>, THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS, MINB>, THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    k_count<H, THREADS><<<sms * per_sm, THREADS, 0, st>>>(d, ws, bc);
+    k_count<H, THREADS, MINB><<<sms * per_sm, THREADS, 0, st>>>(d, ws, bc);
     return cudaGetLastError();
 }
 
@@ -486,12 +486,12 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         k_count_exact<4, 128><<<sms * (per_sm < 1 ? 1 : per_sm), 128, 0, st>>>(d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 1) e = launch_count_t<4, 64>(d, ws, bc, sms, st);
-    else if (variant == 2) e = launch_count_t<4, 32>(d, ws, bc, sms, st);
-    else if (variant == 3) e = launch_count_t<2, 256>(d, ws, bc, sms, st);
-    else if (variant == 4) e = launch_count_t<8, 64>(d, ws, bc, sms, st);
-    else if (variant == 5) e = launch_count_t<2, 128>(d, ws, bc, sms, st);
-    else e = launch_count_t<4, 128>(d, ws, bc, sms, st);
+    else if (variant == 1) e = launch_count_t<4, 64, 14>(d, ws, bc, sms, st);
+    else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
+    else if (variant == 3) e = launch_count_t<4, 128, 5>(d, ws, bc, sms, st);
+    else if (variant == 4) e = launch_count_t<4, 128, 7>(d, ws, bc, sms, st);
+    else if (variant == 5) e = launch_count_t<4, 128, 8>(d, ws, bc, sms, st);
+    else e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);  // 80 registers, no spills, 6 CTAs per SM: measured best
     ++*launches;
     return e;
 }

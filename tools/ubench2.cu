@@ -11,7 +11,9 @@ __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm
 
 constexpr int PX = 256;
 // MODE 0: packed half-plane loop (as k_count); 1: scalar half-plane loop; 2: packed, FFMA2 only (no classification);
-// 3: packed, min + sign count only (no band tracking)
+// 3: packed, min + sign count only (no band tracking); 4: band by FSETP chain instead of FMNMX3;
+// 5: sign count by PRMT (sign-replicated bytes) + IDP.4A instead of 2 LEA.HI; 6: as 0 with the FMNMX on the integer pipe
+// (VIMNMX on the float bits is NOT equivalent for negative values -- timing probe only)
 template <int H, int THREADS, int MODE>
 __global__ void __launch_bounds__(THREADS) k_loop(const float *consts, int reps, int *out)
 {
@@ -47,7 +49,16 @@ __global__ void __launch_bounds__(THREADS) k_loop(const float *consts, int reps,
                         unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
                         unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
                     }
-                    if (MODE == 2) {
+                    if (MODE == 4) {
+                        const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
+                        neg[k] += (int)(__float_as_uint(m0) >> 31) + (int)(__float_as_uint(m1) >> 31);
+                        if (!(fabsf(m0) > T[k]) || !(fabsf(m1) > T[k])) mabs[k] = 0.f;
+                    } else if (MODE == 5) {
+                        const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
+                        const unsigned sb = __byte_perm(__float_as_uint(m0), __float_as_uint(m1), 0xFFBB);
+                        neg[k] = __dp4a((int)sb, 0x00010001, neg[k]);
+                        mabs[k] = fminf(fminf(mabs[k], fabsf(m0)), fabsf(m1));
+                    } else if (MODE == 2) {
                         neg[k] += __float_as_int(ep0) ^ __float_as_int(em1);  // cheap sink: 1 LOP3 + ... per 2 tests
                         hx[k] += ep1 * 0.f + em0 * 0.f;                        // keep all four live (2 FFMA)
                     } else {
@@ -119,5 +130,11 @@ int main()
     run<2, 128, 0>("packed full", 12, dc, out);
     run<4, 64, 0>("packed full", 16, dc, out);
     run<4, 32, 0>("packed full", 32, dc, out);
+    run<4, 128, 4>("packed, FSETP band", 8, dc, out);
+    run<4, 128, 5>("packed, PRMT+IDP4A count", 8, dc, out);
+    run<4, 128, 0>("packed full", 5, dc, out);
+    run<4, 128, 0>("packed full", 6, dc, out);
+    run<4, 128, 0>("packed full", 10, dc, out);
+    run<4, 128, 0>("packed full", 12, dc, out);
     return 0;
 }
