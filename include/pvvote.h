@@ -130,6 +130,13 @@ int pvv_v5(const pvv_job *job, float confidence, int max_iter, float *out_kp, fl
 int pvv_hypotheses(const pvv_job *job, float *out_hyp, int32_t *out_counts, const pvv_debug *dbg);
 
 /*
+ * ransac_motion_voting (ransac_voting_gpu.py:966-987): out_kp [b,vn,2] float32 = mean over the foreground pixels of
+ * (vertex + pixel coordinate); zeros for images without foreground.  Uses job->mask / vertex / strides / b,h,w,vn only
+ * (fg rule PVV_FG_BYTE, no minimum, no subsampling); job->hn_total must be >= 1 and is otherwise ignored.
+ */
+int pvv_motion(const pvv_job *job, float *out_kp);
+
+/*
  * estimate_voting_distribution_with_mean (ransac_voting_gpu.py:333-406):
  * mean [b,vn,2] float32 in, out_cov [b,vn,2,2] float32 out (device). job->hn_total = ceil(min_hyp/round_hyp)*round_hyp,
  * job->fg_rule must be PVV_FG_EQ1.

@@ -245,6 +245,22 @@ def generate_hypothesis_layer(mask, vertex, round_hyp_num, inlier_thresh=0.999, 
     return hyps, counts
 
 
+def ransac_motion_voting(mask, vertex):
+    """ransac_voting_gpu.py:966-987: per image the mean over foreground pixels of (vertex + coords); zeros if none."""
+    mask, vertex = np.asarray(mask), np.asarray(vertex)
+    b, h, w, vn, _ = vertex.shape
+    out = np.zeros((b, vn, 2), np.float32)
+    for bi in range(b):
+        cur = np.asarray(mask[bi]).astype(np.int64).astype(np.uint8)
+        ys, xs = np.nonzero(cur)
+        if len(xs) < 1:
+            continue
+        coords = np.stack([xs, ys], 1).astype(np.float32)
+        cur_vert = (vertex[bi][ys, xs] + coords[:, None, :]).astype(np.float32)   # fp32 terms as torch forms them
+        out[bi] = cur_vert.astype(np.float64).mean(0).astype(np.float32)
+    return out
+
+
 # ----------------------------------------------------------------------------
 # estimate_voting_distribution_with_mean  (ransac_voting_gpu.py:333-406)
 # ----------------------------------------------------------------------------

@@ -241,6 +241,30 @@ int pvv_hypotheses(const pvv_job *job, float *out_hyp, int32_t *out_counts, cons
     return PVV_OK;
 }
 
+int pvv_motion(const pvv_job *job, float *out_kp)
+{
+    if (!out_kp || !job) return PVV_ERR_INVALID;
+    pvv_job j = *job;
+    j.fg_rule = PVV_FG_BYTE;
+    j.min_num = 1;                 // an image without foreground is "skipped": zeros
+    j.max_num = 0x7fffffff;        // no subsampling
+    j.idxs = nullptr; j.selection = nullptr;
+    const int v = validate(&j);
+    if (v != PVV_OK) return v;
+    const layout L = make_layout(&j);
+    if (j.workspace_bytes < L.total_bytes || ((uintptr_t)j.workspace & 255)) return PVV_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)j.stream;
+    pvv_ws ws = carve(L, j.workspace);
+    const pvv_dims d = make_dims(&j);
+    int launches = 0;
+    cudaError_t e = cudaMemsetAsync(j.workspace, 0, L.zero_bytes, st);
+    if (e) return fail_cuda(e);
+    if ((e = pvv_launch_compact(d, j.mask, j.vertex, nullptr, ws, st, &launches))) return fail_cuda(e);
+    if ((e = pvv_launch_motion_mean(d, ws, out_kp, st, &launches))) return fail_cuda(e);
+    t_last_launches = launches;
+    return PVV_OK;
+}
+
 int pvv_cov(const pvv_job *job, const float *mean, float *out_cov, const pvv_debug *dbg)
 {
     if (!mean || !out_cov) return PVV_ERR_INVALID;

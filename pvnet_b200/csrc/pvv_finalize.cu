@@ -195,6 +195,29 @@ __global__ void __launch_bounds__(kFinThreads) k_cov_finalize(pvv_dims d, pvv_ws
     }
 }
 
+// ransac_motion_voting (:966-987): mean over the foreground pixels of (vertex + coordinate), fp64 accumulation of the
+// fp32 terms torch forms (cur_vert[cur_mask] + coords, :983)
+__global__ void __launch_bounds__(kFinThreads) k_motion_mean(pvv_dims d, pvv_ws ws, float *out_kp)
+{
+    __shared__ double s_buf[kFinThreads / 32];
+    const int img = blockIdx.y, vi = blockIdx.x;
+    const int tn = ws.tn[img];
+    const long long o = (long long)img * d.vn + vi, off = ws.img_off[img];
+    double sx = 0, sy = 0;
+    for (int t = threadIdx.x; t < tn; t += kFinThreads) {
+        const uint32_t xy = ws.pix_xy[off + t];
+        const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + t];
+        sx += (double)__fadd_rn(dir.x, (float)(xy & 0xffffu));
+        sy += (double)__fadd_rn(dir.y, (float)(xy >> 16));
+    }
+    sx = block_sum(sx, s_buf);
+    sy = block_sum(sy, s_buf);
+    if (threadIdx.x == 0) {
+        out_kp[o * 2] = tn > 0 ? (float)(sx / tn) : 0.f;      // no foreground: zeros (:978-980)
+        out_kp[o * 2 + 1] = tn > 0 ? (float)(sy / tn) : 0.f;
+    }
+}
+
 // counts [b][vn][hn_pad] -> reference layout [b][hn][vn]
 __global__ void k_export_counts(pvv_dims d, pvv_ws ws, int32_t *counts_out)
 {
@@ -219,6 +242,13 @@ cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *o
         g.win_inlier = dbg->win_inlier; g.normal_eq = dbg->normal_eq; g.dbg_cap = dbg->pool_capacity;
     }
     k_v3_finalize<<<dim3(d.vn, d.b, PVV_FIN_SPLIT), kFinThreads, 0, st>>>(d, ws, out_kp, out_conf, g);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t pvv_launch_motion_mean(const pvv_dims &d, const pvv_ws &ws, float *out_kp, cudaStream_t st, int *launches)
+{
+    k_motion_mean<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, out_kp);
     ++*launches;
     return cudaGetLastError();
 }

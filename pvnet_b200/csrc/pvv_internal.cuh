@@ -54,6 +54,7 @@ cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *o
                                    const pvv_debug *dbg, cudaStream_t st, int *launches);
 cudaError_t pvv_launch_export_counts(const pvv_dims &d, const pvv_ws &ws, int32_t *counts_out, cudaStream_t st,
                                      int *launches);
+cudaError_t pvv_launch_motion_mean(const pvv_dims &d, const pvv_ws &ws, float *out_kp, cudaStream_t st, int *launches);
 cudaError_t pvv_launch_cov_finalize(const pvv_dims &d, const pvv_ws &ws, const float *mean, float *out_cov,
                                     cudaStream_t st, int *launches);
 cudaError_t pvv_launch_debug_export(const pvv_dims &d, const pvv_ws &ws, const pvv_debug *dbg, cudaStream_t st,

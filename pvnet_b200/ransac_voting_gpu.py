@@ -21,7 +21,7 @@ import torch
 
 from . import _lib
 
-__all__ = ["ransac_voting_layer_v3", "ransac_voting_layer_v5", "generate_hypothesis", "estimate_voting_distribution_with_mean", "ransac_voting", "torch_extension", "make_idxs",
+__all__ = ["ransac_voting_layer_v3", "ransac_voting_layer_v5", "generate_hypothesis", "ransac_motion_voting", "estimate_voting_distribution_with_mean", "ransac_voting", "torch_extension", "make_idxs",
            "make_selection", "fp32_peak_tflops", "last_launch_count"]
 
 _MASK_DT = {torch.uint8: _lib.MASK_U8, torch.bool: _lib.MASK_U8, torch.int32: _lib.MASK_I32,
@@ -220,6 +220,26 @@ def generate_hypothesis(mask, vertex, round_hyp_num, inlier_thresh=0.999, confid
     if return_debug:
         return r[0][0], r[0][1].long(), r[1]
     return r[0], r[1].long()
+
+
+def ransac_motion_voting(mask, vertex):
+    """-> [b,vn,2]: mean over the foreground pixels of (vertex + pixel coordinate); zeros without foreground.
+    Reference: ransac_voting_gpu.py:966-987 (MotionEvalWrapper, tools/train_linemod.py:127-133)."""
+    if not torch.cuda.is_available() or not mask.is_cuda or not vertex.is_cuda:
+        raise RuntimeError("ransac_motion_voting needs CUDA tensors (sm_100a); there is no CPU fallback")
+    L = _lib.lib()
+    b, h, w, vn, _ = vertex.shape
+    mask = _prep_mask(mask)
+    dev = mask.device
+    with torch.cuda.device(dev):
+        job = _make_job(mask, vertex, 1, 0.99, 1, 2 ** 31 - 1, _lib.FG_BYTE, None, None, 0, 0, b * h * w)
+        nbytes = L.pvv_workspace_bytes(C.byref(job))
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        job.workspace, job.workspace_bytes, job.stream = ws.data_ptr(), nbytes, _stream_ptr(dev)
+        out = torch.empty((b, vn, 2), dtype=torch.float32, device=dev)
+        _lib.check(L.pvv_motion(C.byref(job), out.data_ptr()), "pvv_motion")
+        ws.record_stream(torch.cuda.current_stream(dev))
+    return out
 
 
 def estimate_voting_distribution_with_mean(mask, vertex, mean, round_hyp_num=256, min_hyp_num=4096, topk=128,

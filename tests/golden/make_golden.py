@@ -222,6 +222,15 @@ def main():
     np.savez_compressed(os.path.join(OUT, "v5_small_batch.npz"), mask=mask5.astype(np.uint8), idxs=i5, sel=s5, out=k5,
                         conf=c5, args=np.array([128, 5, 100]))
     print("v5 conf\n", c5)
+    # ---- G5: ransac_motion_voting (:966-987) on the same batch (image 1 of mask5 has 3 fg px, an empty one is added) ----
+    mask6 = mask5.copy()
+    mask6[1] = 0
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")      # uint8 mask indexing (:983) is deprecated in torch 2.x but still a mask
+        mv = ref.ransac_motion_voting(torch.from_numpy(mask6), torch.from_numpy(vertex)).numpy()
+    np.savez_compressed(os.path.join(OUT, "motion_small_batch.npz"), mask=mask6.astype(np.uint8), out=mv)
+    print("motion voting\n", mv[:, :2])
     print("small batch v3 out\n", out[:, :2], "\ncov[0,0]\n", cov[0, 0], "\nfg", [(int((mask[i] != 0).sum())) for i in range(b)])
 
 

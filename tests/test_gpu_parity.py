@@ -385,3 +385,21 @@ def test_generate_hypothesis_wrapper():
     out, d3 = pv.ransac_voting_layer_v3(tm, tv, hn, 0.99, seed=8, min_num=5, return_debug=True)
     assert torch.equal(d3["counts"].long(), counts)
     assert torch.equal(d3["win_idx"][0].long(), counts[0].argmax(0))
+
+
+def test_motion_voting(golden_dir):
+    """ransac_motion_voting = masked mean of (vertex + coordinate) per image and keypoint."""
+    z = np.load(os.path.join(golden_dir, "motion_small_batch.npz"))
+    sb = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    mask, vertex = z["mask"].astype(np.int64), sb["vertex"]
+    out = pv.ransac_motion_voting(torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV))
+    assert out.shape == (4, 9, 2) and torch.all(out[1] == 0)
+    np.testing.assert_allclose(out.cpu().numpy(), z["out"], rtol=RTOL, atol=0)               # reference wrapper
+    np.testing.assert_allclose(out.cpu().numpy(), orc.ransac_motion_voting(mask, vertex), rtol=1e-6, atol=0)
+    # full-size, network layout, every pixel foreground in one image (no subsampling on this path)
+    m2, v2, _ = synth.make_batch(2, vn=9, frac=0.3, sigma=0.05, seed=3)
+    m2[1] = 1
+    o2 = pv.ransac_motion_voting(torch.from_numpy(m2).to(DEV), synth.as_net_output(v2, device=DEV))
+    np.testing.assert_allclose(o2.cpu().numpy(), orc.ransac_motion_voting(m2, v2), rtol=1e-5, atol=0)
+    with pytest.raises(RuntimeError):
+        pv.ransac_motion_voting(torch.from_numpy(mask), torch.from_numpy(vertex))              # CPU tensors: no fallback

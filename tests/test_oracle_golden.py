@@ -101,3 +101,12 @@ def test_generate_hypothesis_layer_matches_v3_internals(golden_dir):
     for bi in (0, 2, 3):
         assert np.array_equal(counts[bi], z["v3_counts"][bi])      # what the reference wrapper's v3 counted
     assert np.all(hyp[1] == 0) and np.all(counts[1] == 0)
+
+
+def test_motion_voting_small_batch(golden_dir):
+    """ransac_motion_voting (ransac_voting_gpu.py:966-987), fixture from the reference's own wrapper."""
+    z = np.load(os.path.join(golden_dir, "motion_small_batch.npz"))
+    sb = np.load(os.path.join(golden_dir, "small_batch.npz"))
+    out = orc.ransac_motion_voting(z["mask"].astype(np.int64), sb["vertex"])
+    assert np.all(out[1] == 0)                                           # no foreground: zeros (:978-980)
+    np.testing.assert_allclose(out, z["out"], rtol=RTOL, atol=0)
