@@ -45,7 +45,7 @@ long long default_cap(const pvv_job *j)
 
 struct layout {
     size_t zero_bytes, total_bytes;
-    size_t o_counters, o_img_fg, o_counts, o_ticket, o_part, o_flags, o_tn, o_img_off, o_chunk, o_tile_cnt, o_tile_off, o_bits, o_xy, o_dir, o_hyp;
+    size_t o_counters, o_img_fg, o_counts, o_ticket, o_part, o_flags, o_tn, o_img_off, o_chunk, o_ctab, o_tile_cnt, o_tile_off, o_bits, o_xy, o_dir, o_hyp;
     long long cap;
     int ntiles, hn_pad;
 };
@@ -67,6 +67,7 @@ layout make_layout(const pvv_job *j)
     L.o_tn = take(sizeof(int) * j->b);
     L.o_img_off = take(sizeof(long long) * j->b);
     L.o_chunk = take(sizeof(int) * (j->b + 1));
+    L.o_ctab = take(sizeof(int4) * ((size_t)L.cap / PVV_CHUNK_PX + (size_t)j->b + 1));
     L.o_tile_cnt = take(sizeof(int) * (size_t)j->b * L.ntiles);
     L.o_tile_off = take(sizeof(int) * (size_t)j->b * L.ntiles);
     L.o_bits = take(sizeof(uint32_t) * (size_t)j->b * L.ntiles * (PVV_TILE_PX / 32));
@@ -89,6 +90,7 @@ pvv_ws carve(const layout &L, void *base)
     ws.tn = (int *)(p + L.o_tn);
     ws.img_off = (long long *)(p + L.o_img_off);
     ws.chunk_start = (int *)(p + L.o_chunk);
+    ws.chunk_tab = (int4 *)(p + L.o_ctab);
     ws.tile_cnt = (int *)(p + L.o_tile_cnt);
     ws.tile_off = (int *)(p + L.o_tile_off);
     ws.fg_bits = (uint32_t *)(p + L.o_bits);

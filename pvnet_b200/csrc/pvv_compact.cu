@@ -208,6 +208,13 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
         chunk += total_c;
     }
     if (threadIdx.x == 0) ws.chunk_start[d.b] = chunk;
+    __syncthreads();
+    // voting-chunk table: K3 turns a work item into (image, pixel range) with one load instead of a search
+    for (int i = threadIdx.x; i < d.b; i += kThreads) {
+        const int n = ws.tn[i], cs = ws.chunk_start[i];
+        for (int p0 = 0, c = 0; p0 < n; p0 += PVV_CHUNK_PX, ++c)
+            *reinterpret_cast<int3 *>(&ws.chunk_tab[cs + c]) = make_int3(i, p0, min(PVV_CHUNK_PX, n - p0));
+    }
 }
 
 // ---- K1d: scatter (reads the bitmask, not the mask) ------------------------------------------------
@@ -243,11 +250,17 @@ __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *v
             }
         }
         __syncthreads();
-        const long long base = ws.img_off[img] + ws.tile_off[img * ws.ntiles + tile];
+        const int toff = ws.tile_off[img * ws.ntiles + tile];
+        const long long base = ws.img_off[img] + toff;
+        const int cs = ws.chunk_start[img];
         // consecutive threads take consecutive pixels (coalesced along x inside a keypoint plane); every thread walks the
         // keypoints of its pixel
         for (int j = threadIdx.x; j < total; j += kThreads) {
             ws.pix_xy[base + j] = s_xy[j];
+            {   // the middle pixel of a voting chunk is the origin of that chunk's local frame in K3
+                const int t = toff + j, c = t / PVV_CHUNK_PX;
+                if (t - c * PVV_CHUNK_PX == (min(PVV_CHUNK_PX, tn - c * PVV_CHUNK_PX) >> 1)) ws.chunk_tab[cs + c].w = (int)s_xy[j];
+            }
             const float *src = vertex + s_off[j];
             float2 *dst = ws.pix_dir + base + j;
             // 3 keypoints (6 loads) in flight per thread: measured best -- 18 in flight is 1.7x slower (the planes of one

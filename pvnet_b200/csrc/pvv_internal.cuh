@@ -14,6 +14,8 @@ struct pvv_ws {
     int *tn;                      // [b]  compacted pixels per image (0 when skipped)
     long long *img_off;           // [b]  offset of the image's pixels in the pool
     int *chunk_start;             // [b+1] first voting chunk of each image; [b] = total
+    int4 *chunk_tab;              // [cap/256 + b] per voting chunk: {image, first pixel, pixels, x|y<<16 of the middle pixel}
+                                  //               (.x .y .z by K1c, .w by K1d): K3 decodes a work item with one load
     int *tile_cnt;                // [b][ntiles] foreground pixels per compaction tile
     int *tile_off;                // [b][ntiles] exclusive prefix of tile_cnt within the image
     uint32_t *fg_bits;            // [b][ntiles][32] foreground bitmask (bit i of word w = pixel 32w+i of the tile), after

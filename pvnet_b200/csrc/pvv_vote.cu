@@ -63,11 +63,23 @@ struct band_consts {
     float tau;        // t / sqrt(1 - t^2)
     float krel;       // half-width of the band per unit of max |coordinate| (covers tau's uncertainty + rounding)
     float abs_floor;  // catches ||d|| < 1e-6 (reference skips those)
+    int ablate;       // experiments only (tools/k3_ablate.py builds with -DPVV_K3_ABLATE): phases to leave out
 };
+#ifndef K3_HOTVAR
+#define K3_HOTVAR 0
+#endif
+#ifdef PVV_K3_ABLATE
+#define K3_ABL(bit) (bc.ablate & (bit))
+#else
+#define K3_ABL(bit) 0
+#endif
 
 constexpr int K3_GROUP = 16;   // pixels per band-check group in the hot loop (eight packed pixel pairs): measured best of 8/16
 constexpr int K3_QCAP = 512;   // deferred (thread, pixel group) entries per work item; overflow is resolved in line
-constexpr int K3_PAIRS = PVV_CHUNK_PX / 2;
+constexpr int K3_GSTRIDE = 3 * (K3_GROUP / 2) + 1;  // 16-byte units per pixel group in shared memory: the pad spreads the
+                                                    // groups over the banks for the per-entry reads of phase A
+constexpr int K3_SP_FLOATS = 4 * K3_GSTRIDE * (PVV_CHUNK_PX / K3_GROUP);
+constexpr int K3_SUB = 2;      // phase A: lanes per flagged (hypothesis, group) entry
 
 // packed FP32x2 helpers: Blackwell issues one FFMA2 for two IEEE fp32 FMAs (half the issue slots of two FFMAs)
 typedef unsigned long long f32x2;
@@ -88,6 +100,25 @@ __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
     return d;
 }
 
+// Sign bits of two floats as two 16-bit lanes of one word: lane = 0xFFFF (-1 mod 2^16) when the value is negative, else 0.
+// One PRMT in its sign-replicate mode (selector nibble 8|byte: the byte's msb copied to all 8 bits).  Words are summed
+// as plain 32-bit integers (IADD3 takes two of them per instruction); the carries between the lanes are undone by
+// sign_lanes_total as long as each lane saw fewer than 65536 negatives.
+__device__ __forceinline__ int sign_lanes(float x, float y)
+{
+    int d;
+    asm("prmt.b32 %0, %1, %2, 0xFFBB;" : "=r"(d) : "r"(__float_as_int(x)), "r"(__float_as_int(y)));
+    return d;
+}
+__device__ __forceinline__ int sign_lanes_total(int acc)
+{
+    // acc = k0 * 0xFFFF + k1 * 0xFFFF0000 (mod 2^32), k0 / k1 = negatives seen by the low / high lane
+    const uint32_t w = (uint32_t)acc;
+    const uint32_t k0 = (0u - w) & 0xffffu;
+    const uint32_t k1 = (0u - ((w - k0 * 0xffffu) >> 16)) & 0xffffu;
+    return (int)(k0 + k1);
+}
+
 // Per-pixel constants of the filter, in the chunk-local frame (origin = middle pixel of the chunk).  With d = h - pixel,
 // n^ the unit direction, a = d . n^ and c = d x n^, the reference's test cos > t is the cone a > tau |c|, i.e. the
 // intersection of two half-planes through the pixel:
@@ -99,14 +130,14 @@ struct px_consts { float px, py, pz, qx, qy, qz; };
 
 __device__ __forceinline__ px_consts k3_load_px(const float *sP, int j)
 {
-    const float *q = sP + (j >> 1) * 12 + (j & 1);
+    const float *q = sP + (j >> 1) * 12 + (j / K3_GROUP) * 4 + (j & 1);
     px_consts c;
     c.px = q[0]; c.py = q[2]; c.pz = q[4]; c.qx = q[6]; c.qy = q[8]; c.qz = q[10];
     return c;
 }
 __device__ __forceinline__ void k3_store_px(float *sP, int j, const px_consts &c)
 {
-    float *q = sP + (j >> 1) * 12 + (j & 1);
+    float *q = sP + (j >> 1) * 12 + (j / K3_GROUP) * 4 + (j & 1);
     q[0] = c.px; q[2] = c.py; q[4] = c.pz; q[6] = c.qx; q[8] = c.qy; q[10] = c.qz;
 }
 
@@ -143,20 +174,14 @@ __device__ __forceinline__ k3_item k3_decode_item(const pvv_dims &d, const pvv_w
     k3_item it;
     const int ci = item / d.vn;
     it.vi = item - ci * d.vn;
-    int lo = 0, hi = d.b;
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (ws.chunk_start[mid] <= ci) lo = mid; else hi = mid;
-    }
-    it.img = lo;
-    const int tn = ws.tn[lo];
-    it.off = ws.img_off[lo];
-    it.p0 = (ci - ws.chunk_start[lo]) * PVV_CHUNK_PX;
-    it.n = min(PVV_CHUNK_PX, tn - it.p0);
+    const int4 e = __ldg(&ws.chunk_tab[ci]);  // {image, first pixel, pixels, x|y<<16 of the middle pixel}, written by K1
+    it.img = e.x;
+    it.p0 = e.y;
+    it.n = e.z;
     // frame origin = the chunk's middle pixel: halves the extent P of the chunk around it, and with it the band
-    const uint32_t xy0 = ws.pix_xy[it.off + it.p0 + (it.n >> 1)];
-    it.ox = (int)(xy0 & 0xffffu);
-    it.oy = (int)(xy0 >> 16);
+    it.ox = (int)((uint32_t)e.w & 0xffffu);
+    it.oy = (int)((uint32_t)e.w >> 16);
+    it.off = __ldg(&ws.img_off[e.x]);
     return it;
 }
 
@@ -230,7 +255,7 @@ template <int H, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
 {
     static_assert(THREADS <= 256 && H <= 8 && PVV_CHUNK_PX / K3_GROUP <= 32, "entry packing");
-    __shared__ __align__(16) float sP[12 * K3_PAIRS];
+    __shared__ __align__(16) float sP[K3_SP_FLOATS];
     __shared__ __align__(8) float2 sDir[2][PVV_CHUNK_PX];  // raw pixels, double-buffered (current / prefetched item)
     __shared__ uint32_t sXY[2][PVV_CHUNK_PX];
     __shared__ float4 sH[H * THREADS];  // this pass's hypotheses in the chunk-local frame: {hx, hy, T, -}
@@ -251,6 +276,14 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
         cp_async_commit();
     };
 
+#ifdef PVV_K3_ABLATE
+    {   // experiment: stagger the CTAs of one SM by (ablate >> 8) x 100 ns each, to break their lock-step
+        const unsigned long long ns = 100ull * (unsigned)(bc.ablate >> 8) * (blockIdx.x / 148);
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        do { __nanosleep(100); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1)); } while (t1 - t0 < ns);
+    }
+#endif
     if (tid == 0) {
         s_id[0] = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u);
         s_P[0] = 0; s_P[1] = 0; s_qn = 0; s_q2n = 0;
@@ -272,9 +305,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 
         // ---- derived constants in the chunk-local frame ----
         const int npad = (n + K3_GROUP - 1) / K3_GROUP * K3_GROUP;
+        int ext = 0;  // this thread's largest |offset| from the frame origin
         for (int j = tid; j < npad; j += THREADS) {
             px_consts c = never;
-            if (j < n) {
+            if (j < n && !K3_ABL(4)) {
                 const uint32_t xy = rXY[j];
                 const float2 dir = rDir[j];
                 const float n1 = pvv_norm1(dir.x, dir.y);
@@ -289,11 +323,13 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                     c.qy = (float)(ny - tau * nx);
                     c.pz = (float)(-((double)ix * c.px + (double)iy * c.py));
                     c.qz = (float)(-((double)ix * c.qx + (double)iy * c.qy));
-                    atomicMax(&s_P[buf], abs(ix) + abs(iy));
+                    ext = max(ext, abs(ix) + abs(iy));
                 }
             }
             k3_store_px(sP, j, c);
         }
+        ext = __reduce_max_sync(0xffffffffu, ext);
+        if ((tid & 31) == 0 && ext) atomicMax(&s_P[buf], ext);
         // ---- prefetch the next item's raw pixels and the id of the one after it ----
         k3_item nit = it;
         if (next < total_items) {
@@ -308,7 +344,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
         __syncthreads();  // constants and s_P complete
         const float P = (float)s_P[buf];
         const long long row = ((long long)it.img * d.vn + it.vi) * ws.hn_pad;
-        const int ngroups = npad / K3_GROUP;
+        const int ngroups = K3_ABL(2) ? 0 : npad / K3_GROUP;
 
         // exact decision for one in-band test, correcting the provisional count (sign bit of m clear = counted)
         auto resolve = [&](int hbase, int t, int k, int j, float m) {
@@ -346,22 +382,40 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                 // only sets a bit in a per-thread mask.
                 uint32_t bit = 1u;
                 const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(sP);
-                for (int g = 0; g < ngroups; ++g, pp += 3 * (K3_GROUP / 2), bit <<= 1) {
+                for (int g = 0; g < ngroups; ++g, pp += K3_GSTRIDE, bit <<= 1) {
                     float mabs[H];
 #pragma unroll
                     for (int k = 0; k < H; ++k) mabs[k] = __int_as_float(0x7f800000);
 #pragma unroll
-                    for (int u = 0; u < K3_GROUP / 2; ++u) {
-                        const ulonglong2 v0 = pp[3 * u], v1 = pp[3 * u + 1], v2 = pp[3 * u + 2];
+                    for (int u = 0; u < K3_GROUP / 2; u += 2) {  // two pixel pairs per step
+                        const ulonglong2 a0 = pp[3 * u], a1 = pp[3 * u + 1], a2 = pp[3 * u + 2];
+                        const ulonglong2 b0 = pp[3 * u + 3], b1 = pp[3 * u + 4], b2 = pp[3 * u + 5];
 #pragma unroll
                         for (int k = 0; k < H; ++k) {
                             const f32x2 hxx = pk(hx[k], hx[k]), hyy = pk(hy[k], hy[k]);  // FFMA2 broadcast operands
-                            float ep0, ep1, em0, em1;
-                            unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
-                            unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
+                            float ep0, ep1, em0, em1, ep2, ep3, em2, em3;
+                            unpk(ffma2(hxx, a0.x, ffma2(hyy, a0.y, a1.x)), ep0, ep1);
+                            unpk(ffma2(hxx, a1.y, ffma2(hyy, a2.x, a2.y)), em0, em1);
+                            unpk(ffma2(hxx, b0.x, ffma2(hyy, b0.y, b1.x)), ep2, ep3);
+                            unpk(ffma2(hxx, b1.y, ffma2(hyy, b2.x, b2.y)), em2, em3);
                             const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
-                            neg[k] += (int)(__float_as_uint(m0) >> 31) + (int)(__float_as_uint(m1) >> 31);
+                            const float m2 = fminf(ep2, em2), m3 = fminf(ep3, em3);
+                            // sign bits of four tests in 3 instructions (2 PRMT + IADD3) instead of 4 LEA.HI: see sign_lanes
+#if K3_HOTVAR == 0
+                            neg[k] += sign_lanes(m0, m1) + sign_lanes(m2, m3);
                             mabs[k] = fminf(fminf(mabs[k], fabsf(m0)), fabsf(m1));
+                            mabs[k] = fminf(fminf(mabs[k], fabsf(m2)), fabsf(m3));
+#else  // experiments (tools/k3_ablate.py): marginal cost of the loop's parts; counts are wrong
+                            if (K3_HOTVAR == 1) neg[k] += (int)(__float_as_uint(m0) >> 31) + (int)(__float_as_uint(m1) >> 31) +
+                                                          (int)(__float_as_uint(m2) >> 31) + (int)(__float_as_uint(m3) >> 31);
+                            if (K3_HOTVAR == 2 || K3_HOTVAR == 5) neg[k] += sign_lanes(m0, m1) + sign_lanes(m2, m3);
+                            if (K3_HOTVAR == 3 || K3_HOTVAR == 4) neg[k] ^= __float_as_int(m0) ^ __float_as_int(m1) ^ __float_as_int(m2) ^ __float_as_int(m3);
+                            if (K3_HOTVAR == 1 || K3_HOTVAR == 3) {
+                                mabs[k] = fminf(fminf(mabs[k], fabsf(m0)), fabsf(m1));
+                                mabs[k] = fminf(fminf(mabs[k], fabsf(m2)), fabsf(m3));
+                            }
+                            if (K3_HOTVAR == 5) mabs[k] = fminf(mabs[k], fminf(fminf(fabsf(m0), fabsf(m1)), fminf(fabsf(m2), fabsf(m3))));
+#endif
                         }
                     }
 #pragma unroll
@@ -371,13 +425,13 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
                     const int h = hbase + k * THREADS + tid;
-                    const int cnt = npad - neg[k];  // padded and never-inlier pixels have m < 0
-                    if (h < d.hn && cnt) atomicAdd(&ws.counts[row + h], cnt);
+                    const int cnt = npad - sign_lanes_total(neg[k]);  // padded and never-inlier pixels have m < 0
+                    if (h < d.hn && cnt && !K3_ABL(8)) atomicAdd(&ws.counts[row + h], cnt);
                 }
                 // queue this thread's flagged (slot, group) pairs for the dense passes below
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
-                    uint32_t dm = hbase + k * THREADS + tid < d.hn ? dmask[k] : 0u;
+                    uint32_t dm = hbase + k * THREADS + tid < d.hn && !K3_ABL(1) ? dmask[k] : 0u;
                     while (dm) {
                         const int grp = __ffs(dm) - 1;
                         dm &= dm - 1;
@@ -395,19 +449,34 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                 }
             }
             __syncthreads();
-            // phase A: one (pixel, hypothesis) band re-evaluation per thread and step, spread over the whole CTA
-            const int qtot = min(s_qn, K3_QCAP) * K3_GROUP;
+            // phase A: K3_SUB lanes per flagged (hypothesis, group) entry re-evaluate its pixels with the hot loop's own
+            // packed FMA chains (bit-identical m) and queue the tests truly inside the band
+            const int qtot = min(s_qn, K3_QCAP) * K3_SUB;
             for (int idx = tid; idx < qtot; idx += THREADS) {
-                const uint32_t ent = s_q[idx / K3_GROUP];
-                const int t = (int)(ent & 0xffu), k = (int)((ent >> 8) & 0xffu);
-                const int j = (int)(ent >> 16) * K3_GROUP + idx % K3_GROUP;
-                if (j >= n) continue;
+                const uint32_t ent = s_q[idx / K3_SUB];
+                const int t = (int)(ent & 0xffu), k = (int)((ent >> 8) & 0xffu), grp = (int)(ent >> 16);
+                constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
+                const int u0 = (idx % K3_SUB) * PAIRS;
                 const float4 hl = sH[k * THREADS + t];
-                const float m = k3_m(hl.x, hl.y, k3_load_px(sP, j));
-                if (fabsf(m) > hl.z) continue;
-                const int q = atomicAdd(&s_q2n, 1);
-                if (q < K3_QCAP) s_q2[q] = ((uint32_t)j << 16) | ((uint32_t)k << 8) | (uint32_t)t;
-                else resolve(hbase, t, k, j, m);
+                const f32x2 hxx = pk(hl.x, hl.x), hyy = pk(hl.y, hl.y);
+                const ulonglong2 *pg = reinterpret_cast<const ulonglong2 *>(sP) + grp * K3_GSTRIDE + 3 * u0;
+                uint32_t inband = 0u;
+#pragma unroll
+                for (int u = 0; u < PAIRS; ++u) {
+                    const ulonglong2 v0 = pg[3 * u], v1 = pg[3 * u + 1], v2 = pg[3 * u + 2];
+                    float ep0, ep1, em0, em1;
+                    unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
+                    unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
+                    if (!(fabsf(fminf(ep0, em0)) > hl.z)) inband |= 1u << (2 * u);
+                    if (!(fabsf(fminf(ep1, em1)) > hl.z)) inband |= 2u << (2 * u);
+                }
+                while (inband) {  // padded pixels have m = -1e30 and never get here
+                    const int j = grp * K3_GROUP + 2 * u0 + __ffs(inband) - 1;
+                    inband &= inband - 1;
+                    const int q = atomicAdd(&s_q2n, 1);
+                    if (q < K3_QCAP) s_q2[q] = ((uint32_t)j << 16) | ((uint32_t)k << 8) | (uint32_t)t;
+                    else resolve(hbase, t, k, j, k3_m(hl.x, hl.y, k3_load_px(sP, j)));
+                }
             }
             __syncthreads();
             if (tid == 0) s_qn = 0;  // every thread has read it; the next pushes come after another barrier
@@ -456,6 +525,10 @@ static bool pvv_band_for(float t, band_consts *bc)
     bc->tau = (float)tau;
     bc->krel = (float)((erel + kabs) * (1.0 + 4.0 * u));
     bc->abs_floor = (float)(4e-6 * (1.0 + tau));
+    bc->ablate = 0;
+#ifdef PVV_K3_ABLATE
+    if (const char *e = getenv("PVV_K3_ABLATE")) bc->ablate = atoi(e);
+#endif
     return true;
 }
 
@@ -487,12 +560,13 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         k_count_exact<4, 128><<<sms * (per_sm < 1 ? 1 : per_sm), 128, 0, st>>>(d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 1) e = launch_count_t<4, 64, 14>(d, ws, bc, sms, st);
+    else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
-    else if (variant == 3) e = launch_count_t<4, 128, 5>(d, ws, bc, sms, st);
+    else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);
+    else if (variant == 6) e = launch_count_t<4, 128, 4>(d, ws, bc, sms, st);
     else if (variant == 4) e = launch_count_t<4, 128, 7>(d, ws, bc, sms, st);
     else if (variant == 5) e = launch_count_t<4, 128, 8>(d, ws, bc, sms, st);
-    else e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);  // 80 registers, no spills, 6 CTAs per SM: measured best
+    else e = launch_count_t<4, 128, 5>(d, ws, bc, sms, st);  // 96 registers, no spills, 5 CTAs per SM: measured best (6 CTAs spill)
     ++*launches;
     return e;
 }
