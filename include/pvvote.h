@@ -38,7 +38,15 @@ typedef enum pvv_status {
 } pvv_status;
 
 /* mask element types accepted (the reference takes whatever `.byte()` / `== 1` accept) */
-enum { PVV_MASK_U8 = 0, PVV_MASK_I32 = 1, PVV_MASK_I64 = 2, PVV_MASK_F32 = 3 };
+enum {
+    PVV_MASK_U8 = 0, PVV_MASK_I32 = 1, PVV_MASK_I64 = 2, PVV_MASK_F32 = 3,
+    /* `mask` is the segmentation head's output seg_pred [b,C,h,w] float32; the label of a pixel is
+     * torch.argmax(seg_pred, 1) (first maximal class, a NaN counts as maximal) computed on the fly by the compaction
+     * pass, so the int64 mask of EvalWrapper.forward (tools/demo.py:46-55, tools/train_linemod.py:254) is never
+     * written.  mask_strides = strides of (b,h,w); the class stride and count are seg_class_stride / seg_classes.
+     * Device-buffer entry points only. */
+    PVV_MASK_LOGITS_F32 = 4
+};
 
 /* which foreground rule to apply */
 enum {
@@ -53,7 +61,8 @@ enum {
 
 /*
  * One voting job over a batch.  Layouts are the reference's:
- *   mask    [b,h,w]      any PVV_MASK_* type, strides in ELEMENTS (mask_strides[3])
+ *   mask    [b,h,w]      any PVV_MASK_* type, strides in ELEMENTS (mask_strides[3]); or seg_pred logits [b,C,h,w]
+ *           with PVV_MASK_LOGITS_F32
  *   vertex  [b,h,w,vn,2] float32, strides in ELEMENTS (vertex_strides[5]); the network emits this as a
  *           permuted view of [b,2+2vn,h,w] (tools/train_linemod.py:118-120) -- it is consumed in place.
  * Random draws are either injected (parity runs) or produced by the library's counter-based generator
@@ -80,6 +89,8 @@ typedef struct pvv_job {
     void *workspace;
     size_t workspace_bytes;
     void *stream;
+    int32_t seg_classes;      /* PVV_MASK_LOGITS_F32 only: C */
+    int64_t seg_class_stride; /* PVV_MASK_LOGITS_F32 only: stride of the class dimension, in elements */
 } pvv_job;
 
 /* Optional device-side introspection buffers (any may be NULL); used by the parity tests. */
@@ -172,6 +183,19 @@ int pvv_voting_for_hypothesis(const float *direct, const float *coords, const fl
 /* fused form of voting_for_hypothesis + torch.sum(inliers, 2): counts int32 [hn,vn], never materialises the matrix */
 int pvv_vote_counts(const float *direct, const float *coords, const float *hyp, int tn, int vn, int hn,
                     float inlier_thresh, int32_t *counts, void *stream);
+
+/*
+ * The vanishing-point twins of the two primitives (src/ransac_voting.cpp:64-98 -> ransac_voting_kernel.cu:170-351),
+ * so that the replacement module exports all four functions of the reference's pybind module (:102-107).
+ * hyp is [hn,vn,3] f32: homogeneous intersection (x,y,z) of the two pixel lines, sign-flipped / zeroed as the
+ * reference does (:219-223); the vote is |cos| > thresh between the direction and hyp.xy - coords*hyp.z with both
+ * component products non-negative (:285-300).
+ */
+int pvv_generate_hypothesis_vanishing_point(const float *direct, const float *coords, const int32_t *idxs, int tn,
+                                            int vn, int hn, float *hyp, void *stream);
+int pvv_voting_for_hypothesis_vanishing_point(const float *direct, const float *coords, const float *hyp,
+                                              uint8_t *inliers, int tn, int vn, int hn, float inlier_thresh,
+                                              void *stream);
 
 /* The library's draw streams, materialised (for feeding the oracle / the reference wrapper the same draws). */
 int pvv_make_idxs(uint64_t seed, int64_t image_id_base, int b, int hn_total, int vn, const int32_t *tn /*device [b]*/,

@@ -55,6 +55,8 @@ def lib():
         L.orc_voting_for_hypothesis.argtypes = [_f32p, _f32p, _f32p, _u8p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float]
         L.orc_vote_counts.argtypes = [_f32p, _f32p, _f32p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float, _i64p]
         L.orc_inlier_test.argtypes = [ctypes.c_float] * 7
+        L.orc_generate_hypothesis_vanishing_point.argtypes = [_f32p, _f32p, _i32p, ctypes.c_int, ctypes.c_int, ctypes.c_int, _f32p]
+        L.orc_voting_for_hypothesis_vanishing_point.argtypes = [_f32p, _f32p, _f32p, _u8p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float]
         L.orc_inlier_test.restype = ctypes.c_int
         L.orc_num_threads.restype = ctypes.c_int
         _LIB = L
@@ -79,6 +81,27 @@ def generate_hypothesis(direct, coords, idxs):
     hyp = np.empty((hn, vn, 2), np.float32)
     lib().orc_generate_hypothesis(_p(direct, _f32p), _p(coords, _f32p), _p(idxs, _i32p), tn, vn, hn, _p(hyp, _f32p))
     return hyp
+
+
+def generate_hypothesis_vanishing_point(direct, coords, idxs):
+    """ransac_voting_kernel.cu:170-227: homogeneous hypotheses [hn,vn,3]."""
+    direct, coords, idxs = _c(direct, np.float32), _c(coords, np.float32), _c(idxs, np.int32)
+    tn, vn, _ = direct.shape
+    hn = idxs.shape[0]
+    hyp = np.empty((hn, vn, 3), np.float32)
+    lib().orc_generate_hypothesis_vanishing_point(_p(direct, _f32p), _p(coords, _f32p), _p(idxs, _i32p), tn, vn, hn,
+                                                  _p(hyp, _f32p))
+    return hyp
+
+
+def voting_for_hypothesis_vanishing_point(direct, coords, hyp, inliers, thresh):
+    """ransac_voting_kernel.cu:258-301, in place on `inliers` (uint8 [hn,vn,tn], pre-zeroed)."""
+    direct, coords, hyp = _c(direct, np.float32), _c(coords, np.float32), _c(hyp, np.float32)
+    assert inliers.dtype == np.uint8 and inliers.flags.c_contiguous and hyp.shape[-1] == 3
+    tn, vn, _ = direct.shape
+    hn = hyp.shape[0]
+    lib().orc_voting_for_hypothesis_vanishing_point(_p(direct, _f32p), _p(coords, _f32p), _p(hyp, _f32p),
+                                                    _p(inliers, _u8p), tn, vn, hn, float(thresh))
 
 
 def voting_for_hypothesis(direct, coords, hyp, inliers, thresh):

@@ -153,3 +153,56 @@ void orc_vote_counts(const float *direct, const float *coords,
         }
     }
 }
+
+/* ---- vanishing-point twins: lib/ransac_voting_gpu_layer/src/ransac_voting_kernel.cu:170-227 and :258-301 ----
+ * Rounding sequence as compiled by the reference build (nvcc defaults, fma contraction on; read off the sm_100a
+ * SASS of oracle/_ref/ransac_voting_kernel.o): products that feed a subtraction are rounded, the subtraction is the
+ * fma; num of the cosine is the plain sum of the two rounded products that are also val_x / val_y. */
+void orc_generate_hypothesis_vanishing_point(const float *direct, const float *coords, const int32_t *idxs, int tn,
+                                             int vn, int hn, float *hyp /* [hn,vn,3] */)
+{
+    (void)tn;
+    for (int hi = 0; hi < hn; ++hi) {
+        for (int vi = 0; vi < vn; ++vi) {
+            const int t0 = idxs[(hi * vn + vi) * 2], t1 = idxs[(hi * vn + vi) * 2 + 1];
+            const float dx0 = direct[((size_t)t0 * vn + vi) * 2], dy0 = direct[((size_t)t0 * vn + vi) * 2 + 1];
+            const float dx1 = direct[((size_t)t1 * vn + vi) * 2], dy1 = direct[((size_t)t1 * vn + vi) * 2 + 1];
+            const float cx0 = coords[(size_t)t0 * 2], cy0 = coords[(size_t)t0 * 2 + 1];
+            const float cx1 = coords[(size_t)t1 * 2], cy1 = coords[(size_t)t1 * 2 + 1];
+            const float lz1 = fmaf(dx1, cy1, -(dy1 * cx1));
+            const float lz0 = fmaf(dx0, cy0, -(dy0 * cx0));
+            float z = fmaf(dx0, dy1, -(dy0 * dx1));
+            float x = fmaf(dx1, lz0, -(dx0 * lz1));
+            float y = fmaf(dy1, lz0, -(dy0 * lz1));
+            const float vx0 = dx0 * fmaf(-cx0, z, x), vx1 = dx1 * fmaf(-cx1, z, x);
+            const float vy0 = dy0 * fmaf(-cy0, z, y), vy1 = dy1 * fmaf(-cy1, z, y);
+            if (vx0 < 0 && vx1 < 0 && vy0 < 0 && vy1 < 0) { x = -x; y = -y; z = -z; }
+            if (vx0 * vx1 < 0 || vy0 * vy1 < 0) { x = 0.f; y = 0.f; z = 0.f; }
+            float *o = hyp + ((size_t)hi * vn + vi) * 3;
+            o[0] = x; o[1] = y; o[2] = z;
+        }
+    }
+}
+
+void orc_voting_for_hypothesis_vanishing_point(const float *direct, const float *coords, const float *hyp,
+                                               uint8_t *inliers, int tn, int vn, int hn, float thresh)
+{
+#pragma omp parallel for schedule(static)
+    for (int hi = 0; hi < hn; ++hi) {
+        for (int vi = 0; vi < vn; ++vi) {
+            const float *h = hyp + ((size_t)hi * vn + vi) * 3;
+            uint8_t *row = inliers + ((size_t)hi * vn + vi) * tn;
+            for (int ti = 0; ti < tn; ++ti) {
+                const float dx = direct[((size_t)ti * vn + vi) * 2], dy = direct[((size_t)ti * vn + vi) * 2 + 1];
+                const float fx = fmaf(-coords[(size_t)ti * 2], h[2], h[0]);
+                const float fy = fmaf(-coords[(size_t)ti * 2 + 1], h[2], h[1]);
+                const float n1 = sqrtf(fmaf(dx, dx, dy * dy));
+                const float n2 = sqrtf(fmaf(fx, fx, fy * fy));
+                if ((double)n1 < 1e-6 || (double)n2 < 1e-6) continue;
+                const float vx = dx * fx, vy = dy * fy;
+                if (vx < 0 || vy < 0) continue;
+                if (fabsf((vx + vy) / (n2 * n1)) > thresh) row[ti] = 1;
+            }
+        }
+    }
+}

@@ -8,7 +8,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpvvote.so")
 
 PVV_OK = 0
-MASK_U8, MASK_I32, MASK_I64, MASK_F32 = 0, 1, 2, 3
+MASK_U8, MASK_I32, MASK_I64, MASK_F32, MASK_LOGITS_F32 = 0, 1, 2, 3, 4
 FG_BYTE, FG_EQ1 = 0, 1
 FLAG_POOL_OVERFLOW = 1
 STATUS_NAMES = {0: "PVV_OK", -1: "PVV_ERR_INVALID", -2: "PVV_ERR_WORKSPACE", -3: "PVV_ERR_CUDA",
@@ -23,7 +23,7 @@ class Job(C.Structure):
         ("inlier_thresh", C.c_float), ("min_num", C.c_int32), ("max_num", C.c_int32),
         ("idxs", C.c_void_p), ("selection", C.c_void_p), ("seed", C.c_uint64), ("image_id_base", C.c_int64),
         ("pool_capacity", C.c_int64), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
-        ("stream", C.c_void_p),
+        ("stream", C.c_void_p), ("seg_classes", C.c_int32), ("seg_class_stride", C.c_int64),
     ]
 
 
@@ -41,6 +41,7 @@ class Debug(C.Structure):
 SYMBOLS = [
     "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_v5", "pvv_hypotheses", "pvv_motion", "pvv_cov", "pvv_workspace_bytes_host",
     "pvv_v3_host", "pvv_cov_host", "pvv_generate_hypothesis", "pvv_voting_for_hypothesis", "pvv_vote_counts",
+    "pvv_generate_hypothesis_vanishing_point", "pvv_voting_for_hypothesis_vanishing_point",
     "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_probe_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
     "pvv_version",
 ]
@@ -73,6 +74,8 @@ def lib():
     L.pvv_cov_host.argtypes = [P(Job), V, V, P(C.c_int64), P(C.c_int64)]
     L.pvv_generate_hypothesis.argtypes = [V, V, V, I, I, I, V, V]
     L.pvv_voting_for_hypothesis.argtypes = [V, V, V, V, I, I, I, F, V]
+    L.pvv_generate_hypothesis_vanishing_point.argtypes = [V, V, V, I, I, I, V, V]
+    L.pvv_voting_for_hypothesis_vanishing_point.argtypes = [V, V, V, V, I, I, I, F, V]
     L.pvv_vote_counts.argtypes = [V, V, V, I, I, I, F, V, V]
     L.pvv_make_idxs.argtypes = [C.c_uint64, C.c_int64, I, I, I, V, V, V]
     L.pvv_make_selection.argtypes = [C.c_uint64, C.c_int64, I, I, I, V, V]

@@ -22,7 +22,8 @@ int validate(const pvv_job *j)
 {
     if (!j || !j->mask || !j->vertex || !j->workspace) return PVV_ERR_INVALID;
     if (j->b <= 0 || j->h <= 0 || j->w <= 0 || j->vn <= 0 || j->hn_total <= 0) return PVV_ERR_INVALID;
-    if (j->mask_dtype < PVV_MASK_U8 || j->mask_dtype > PVV_MASK_F32) return PVV_ERR_INVALID;
+    if (j->mask_dtype < PVV_MASK_U8 || j->mask_dtype > PVV_MASK_LOGITS_F32) return PVV_ERR_INVALID;
+    if (j->mask_dtype == PVV_MASK_LOGITS_F32 && j->seg_classes < 1) return PVV_ERR_INVALID;
     if (j->fg_rule != PVV_FG_BYTE && j->fg_rule != PVV_FG_EQ1) return PVV_ERR_INVALID;
     if (!(j->inlier_thresh == j->inlier_thresh)) return PVV_ERR_INVALID;
     if (j->vn > PVV_MAX_VN || j->h > 65535 || j->w > 65535 || (long long)j->h * j->w > (1LL << 23) || j->b > 65535)
@@ -115,6 +116,7 @@ pvv_dims make_dims(const pvv_job *j)
     d.thresh = j->inlier_thresh;
     d.seed = j->seed; d.image_id_base = j->image_id_base;
     for (int i = 0; i < 3; ++i) d.ms[i] = j->mask_strides[i];
+    d.seg_c = j->seg_classes; d.seg_cs = j->seg_class_stride;
     for (int i = 0; i < 5; ++i) d.vs[i] = j->vertex_strides[i];
     return d;
 }

@@ -64,10 +64,21 @@ __device__ __forceinline__ float sel_value(const pvv_dims &d, const float *selec
 // DT: mask element type (compile-time: no per-element dispatch); LINEAR: rows are contiguous and adjacent, so the
 // element offset is img*stride0 + pixel (no division).
 template <int DT>
-__device__ __forceinline__ uint32_t mask_value_t(const void *mask, long long off, int fg_rule)
+__device__ __forceinline__ uint32_t mask_value_t(const pvv_dims &d, const void *mask, long long off, int fg_rule)
 {
     long long v;
-    if (DT == PVV_MASK_U8) v = ((const uint8_t *)mask)[off];
+    if (DT == PVV_MASK_LOGITS_F32) {
+        // torch.argmax(seg_pred, 1) fused into the pass: first maximal class, a NaN counts as maximal (ATen's rule)
+        const float *p = (const float *)mask + off;
+        float best = p[0];
+        int bi = 0;
+        for (int c = 1; c < d.seg_c; ++c) {
+            const float x = p[c * d.seg_cs];
+            if (x > best || (x != x && best == best)) { best = x; bi = c; }
+        }
+        v = bi;
+    }
+    else if (DT == PVV_MASK_U8) v = ((const uint8_t *)mask)[off];
     else if (DT == PVV_MASK_I32) v = ((const int32_t *)mask)[off];
     else if (DT == PVV_MASK_I64) v = ((const long long *)mask)[off];
     else {  // float: .byte() truncates toward zero, == 1 compares the float
@@ -95,7 +106,7 @@ __global__ void __launch_bounds__(kThreads) k_tile_count(pvv_dims d, const void 
             long long off;
             if (LINEAR) off = img * d.ms[0] + p;
             else { const int y = p / d.w, x = p - y * d.w; off = img * d.ms[0] + y * d.ms[1] + x * d.ms[2]; }
-            v[k] = mask_value_t<DT>(mask, off, d.fg_rule);
+            v[k] = mask_value_t<DT>(d, mask, off, d.fg_rule);
         }
     }
     int n = 0, s = 0;
@@ -287,6 +298,7 @@ cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float 
         case PVV_MASK_U8: launch_tile_count<PVV_MASK_U8>(d, mask, ws, grid, st); break;
         case PVV_MASK_I32: launch_tile_count<PVV_MASK_I32>(d, mask, ws, grid, st); break;
         case PVV_MASK_I64: launch_tile_count<PVV_MASK_I64>(d, mask, ws, grid, st); break;
+        case PVV_MASK_LOGITS_F32: launch_tile_count<PVV_MASK_LOGITS_F32>(d, mask, ws, grid, st); break;
         default: launch_tile_count<PVV_MASK_F32>(d, mask, ws, grid, st); break;
     }
     ++*launches;

@@ -95,6 +95,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     if (r != PVV_OK) return r;
     if (!j->workspace || j->workspace_bytes < P.total || !out_host) return PVV_ERR_WORKSPACE;
     if (cov && !mean_host) return PVV_ERR_INVALID;
+    if (j->mask_dtype == PVV_MASK_LOGITS_F32) return PVV_ERR_UNSUPPORTED;  // logits live on the device, next to the network
     cudaStream_t st = (cudaStream_t)j->stream;
     char *base = (char *)j->workspace;
     int64_t h2d = 0, d2h = 0;

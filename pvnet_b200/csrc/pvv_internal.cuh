@@ -41,6 +41,8 @@ struct pvv_dims {
     unsigned long long seed;
     long long image_id_base;
     long long ms[3];   // mask strides (elements)
+    int seg_c;         // PVV_MASK_LOGITS_F32: classes and class stride
+    long long seg_cs;
     long long vs[5];   // vertex strides (elements)
 };
 

@@ -47,15 +47,25 @@ pvv_job make_job(const at::Tensor &mask, const at::Tensor &vertex, int64_t hn_to
 {
     CHECK_CUDA(mask);
     CHECK_CUDA(vertex);
-    TORCH_CHECK(vertex.dim() == 5 && vertex.size(4) == 2 && mask.dim() == 3, "expected mask [b,h,w], vertex [b,h,w,vn,2]");
+    const bool logits = mask.dim() == 4;  // seg_pred [b,C,h,w]: argmax fused into the compaction pass
+    TORCH_CHECK(vertex.dim() == 5 && vertex.size(4) == 2 && (mask.dim() == 3 || logits),
+                "expected mask [b,h,w] (or seg_pred [b,C,h,w]), vertex [b,h,w,vn,2]");
     TORCH_CHECK(vertex.scalar_type() == at::kFloat, "vertex must be float32");
-    TORCH_CHECK(mask.size(0) == vertex.size(0) && mask.size(1) == vertex.size(1) && mask.size(2) == vertex.size(2),
+    TORCH_CHECK(mask.size(0) == vertex.size(0) && mask.size(-2) == vertex.size(1) && mask.size(-1) == vertex.size(2),
                 "mask and vertex disagree on [b,h,w]");
     pvv_job j = {};
     j.mask = mask.data_ptr();
-    j.mask_dtype = mask_dtype(mask);
     j.fg_rule = fg_rule;
-    for (int i = 0; i < 3; ++i) j.mask_strides[i] = mask.stride(i);
+    if (logits) {
+        TORCH_CHECK(mask.scalar_type() == at::kFloat, "seg_pred must be float32");
+        j.mask_dtype = PVV_MASK_LOGITS_F32;
+        j.mask_strides[0] = mask.stride(0); j.mask_strides[1] = mask.stride(2); j.mask_strides[2] = mask.stride(3);
+        j.seg_classes = (int32_t)mask.size(1);
+        j.seg_class_stride = mask.stride(1);
+    } else {
+        j.mask_dtype = mask_dtype(mask);
+        for (int i = 0; i < 3; ++i) j.mask_strides[i] = mask.stride(i);
+    }
     j.vertex = vertex.data_ptr<float>();
     for (int i = 0; i < 5; ++i) j.vertex_strides[i] = vertex.stride(i);
     j.b = (int32_t)vertex.size(0); j.h = (int32_t)vertex.size(1); j.w = (int32_t)vertex.size(2);
@@ -117,6 +127,41 @@ void voting_for_hypothesis(at::Tensor direct, at::Tensor coords, at::Tensor hypo
                  "pvv_voting_for_hypothesis");
 }
 
+// reference: at::Tensor generate_hypothesis_vanishing_point(direct, coords, idxs)       ransac_voting.cpp:64-75
+at::Tensor generate_hypothesis_vanishing_point(at::Tensor direct, at::Tensor coords, at::Tensor idxs)
+{
+    CHECK_INPUT(direct);
+    CHECK_INPUT(coords);
+    CHECK_INPUT(idxs);
+    TORCH_CHECK(direct.scalar_type() == at::kFloat && coords.scalar_type() == at::kFloat && idxs.scalar_type() == at::kInt,
+                "direct/coords float32, idxs int32");
+    const c10::cuda::CUDAGuard guard(direct.device());
+    const int tn = (int)direct.size(0), vn = (int)direct.size(1), hn = (int)idxs.size(0);
+    auto hyp = at::empty({hn, vn, 3}, direct.options());
+    check_status(pvv_generate_hypothesis_vanishing_point(direct.data_ptr<float>(), coords.data_ptr<float>(),
+                                                         idxs.data_ptr<int32_t>(), tn, vn, hn, hyp.data_ptr<float>(),
+                                                         cur_stream(direct)),
+                 "pvv_generate_hypothesis_vanishing_point");
+    return hyp;
+}
+
+// reference: void voting_for_hypothesis_vanishing_point(direct, coords, hypo_pts, inliers, thresh)   ransac_voting.cpp:85-98
+void voting_for_hypothesis_vanishing_point(at::Tensor direct, at::Tensor coords, at::Tensor hypo_pts, at::Tensor inliers,
+                                           float inlier_thresh)
+{
+    CHECK_INPUT(direct);
+    CHECK_INPUT(coords);
+    CHECK_INPUT(hypo_pts);
+    CHECK_INPUT(inliers);
+    TORCH_CHECK(inliers.scalar_type() == at::kByte, "inliers must be uint8");
+    const c10::cuda::CUDAGuard guard(direct.device());
+    const int tn = (int)direct.size(0), vn = (int)direct.size(1), hn = (int)hypo_pts.size(0);
+    check_status(pvv_voting_for_hypothesis_vanishing_point(direct.data_ptr<float>(), coords.data_ptr<float>(),
+                                                           hypo_pts.data_ptr<float>(), inliers.data_ptr<uint8_t>(), tn, vn,
+                                                           hn, inlier_thresh, cur_stream(direct)),
+                 "pvv_voting_for_hypothesis_vanishing_point");
+}
+
 // ransac_voting_gpu.py:520-604 as one call
 at::Tensor ransac_voting_layer_v3(at::Tensor mask, at::Tensor vertex, int64_t round_hyp_num, double inlier_thresh,
                                   double confidence, int64_t max_iter, int64_t min_num, int64_t max_num,
@@ -160,6 +205,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
     m.def("generate_hypothesis", &generate_hypothesis, "generate hypothesis");
     m.def("voting_for_hypothesis", &voting_for_hypothesis, "voting for hypothesis");
+    m.def("generate_hypothesis_vanishing_point", &generate_hypothesis_vanishing_point, "generate hypothesis vanishing point");
+    m.def("voting_for_hypothesis_vanishing_point", &voting_for_hypothesis_vanishing_point,
+          "voting for hypothesis vanishing point");
     m.def("ransac_voting_layer_v3", &ransac_voting_layer_v3, "fused v3", py::arg("mask"), py::arg("vertex"),
           py::arg("round_hyp_num"), py::arg("inlier_thresh") = 0.99, py::arg("confidence") = 0.99, py::arg("max_iter") = 100,
           py::arg("min_num") = 100, py::arg("max_num") = 30000, py::arg("idxs") = py::none(),

@@ -38,6 +38,8 @@ def _fresh_seed():
 
 
 def _prep_mask(mask):
+    if mask.dim() == 4:  # seg_pred logits [b,C,h,w]: torch.argmax(seg_pred, 1) is fused into the compaction pass
+        return mask if mask.dtype == torch.float32 else mask.to(torch.float32)
     if mask.dtype not in _MASK_DT:
         mask = mask.to(torch.float32) if mask.dtype.is_floating_point else mask.to(torch.int32)
     return mask
@@ -46,13 +48,22 @@ def _prep_mask(mask):
 def _make_job(mask, vertex, hn_total, thresh, min_num, max_num, fg_rule, idxs, selection, seed, image_id_base,
               pool_capacity):
     b, h, w, vn, two = vertex.shape
-    if two != 2 or tuple(mask.shape) != (b, h, w):
-        raise ValueError(f"expected mask [b,h,w] and vertex [b,h,w,vn,2], got {tuple(mask.shape)} / {tuple(vertex.shape)}")
+    logits = mask.dim() == 4
+    if two != 2 or (mask.shape[0], mask.shape[-2], mask.shape[-1]) != (b, h, w) or mask.dim() not in (3, 4):
+        raise ValueError(f"expected mask [b,h,w] (or seg_pred [b,C,h,w]) and vertex [b,h,w,vn,2], got "
+                         f"{tuple(mask.shape)} / {tuple(vertex.shape)}")
     if vertex.dtype != torch.float32:
         raise TypeError("vertex must be float32")
     j = _lib.Job()
-    j.mask, j.mask_dtype, j.fg_rule = mask.data_ptr(), _MASK_DT[mask.dtype], fg_rule
-    j.mask_strides = (C.c_int64 * 3)(*mask.stride())
+    j.mask, j.fg_rule = mask.data_ptr(), fg_rule
+    if logits:
+        j.mask_dtype = _lib.MASK_LOGITS_F32
+        sb, sc, sh, sw = mask.stride()
+        j.mask_strides = (C.c_int64 * 3)(sb, sh, sw)
+        j.seg_classes, j.seg_class_stride = mask.shape[1], sc
+    else:
+        j.mask_dtype = _MASK_DT[mask.dtype]
+        j.mask_strides = (C.c_int64 * 3)(*mask.stride())
     j.vertex = vertex.data_ptr()
     j.vertex_strides = (C.c_int64 * 5)(*vertex.stride())
     j.b, j.h, j.w, j.vn, j.hn_total = b, h, w, vn, int(hn_total)
@@ -295,6 +306,32 @@ class _RansacVoting:
                                                       inliers.data_ptr(), tn, vn, hn, float(inlier_thresh),
                                                       _stream_ptr(direct.device))
         _lib.check(st, "pvv_voting_for_hypothesis")
+
+    @staticmethod
+    def generate_hypothesis_vanishing_point(direct, coords, idxs):
+        """src/ransac_voting.cpp:64-75: homogeneous hypotheses [hn,vn,3]."""
+        _chk(direct, "direct", torch.float32); _chk(coords, "coords", torch.float32); _chk(idxs, "idxs", torch.int32)
+        tn, vn, _ = direct.shape
+        hn = idxs.shape[0]
+        hyp = torch.empty((hn, vn, 3), dtype=torch.float32, device=direct.device)
+        with torch.cuda.device(direct.device):
+            st = _lib.lib().pvv_generate_hypothesis_vanishing_point(direct.data_ptr(), coords.data_ptr(), idxs.data_ptr(),
+                                                                    tn, vn, hn, hyp.data_ptr(), _stream_ptr(direct.device))
+        _lib.check(st, "pvv_generate_hypothesis_vanishing_point")
+        return hyp
+
+    @staticmethod
+    def voting_for_hypothesis_vanishing_point(direct, coords, hypo_pts, inliers, inlier_thresh):
+        """src/ransac_voting.cpp:85-98: in place on inliers [hn,vn,tn] u8."""
+        _chk(direct, "direct", torch.float32); _chk(coords, "coords", torch.float32)
+        _chk(hypo_pts, "hypo_pts", torch.float32); _chk(inliers, "inliers", torch.uint8)
+        tn, vn, _ = direct.shape
+        hn = hypo_pts.shape[0]
+        with torch.cuda.device(direct.device):
+            st = _lib.lib().pvv_voting_for_hypothesis_vanishing_point(direct.data_ptr(), coords.data_ptr(),
+                                                                      hypo_pts.data_ptr(), inliers.data_ptr(), tn, vn, hn,
+                                                                      float(inlier_thresh), _stream_ptr(direct.device))
+        _lib.check(st, "pvv_voting_for_hypothesis_vanishing_point")
 
     @staticmethod
     def vote_counts(direct, coords, hypo_pts, inlier_thresh):

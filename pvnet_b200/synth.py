@@ -107,3 +107,14 @@ def philox_note():
     """The index / selection streams are produced by the product's own
     counter-based generator (pvv_make_idxs / pvv_make_selection in include/pvvote.h)
     and *materialised* for the oracle -- see pvnet_b200.ransac_voting_gpu.make_idxs."""
+
+
+def vanishing_point_field(rng, tn, vn, noise=0.0):
+    """Pixels and unit directions pointing at homogeneous points V[vi] = (X, Y, Z); Z = 0 is a point at infinity."""
+    coords = np.stack([rng.integers(200, 440, tn), rng.integers(100, 380, tn)], 1).astype(np.float32)
+    V = np.stack([rng.uniform(-2000, 2000, vn), rng.uniform(-2000, 2000, vn), rng.choice([1.0, 2.5, 0.0], vn)], 1)
+    V[0, 2], V[1, 2] = 0.0, 1.0
+    diff = V[None, :, :2] - coords[:, None, :] * V[None, :, 2:3]
+    ang = np.arctan2(diff[..., 1], diff[..., 0]) + rng.normal(0, noise, diff.shape[:2]) if noise else None
+    direct = np.stack([np.cos(ang), np.sin(ang)], -1) if noise else diff / np.linalg.norm(diff, axis=-1, keepdims=True)
+    return coords, direct.astype(np.float32), V

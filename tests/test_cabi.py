@@ -203,3 +203,29 @@ def test_integration_stub_reexports_the_path():
     assert m.ransac_voting_layer_v3 is pv.ransac_voting_layer_v3
     assert m.estimate_voting_distribution_with_mean is pv.estimate_voting_distribution_with_mean
     assert hasattr(m.ransac_voting, "generate_hypothesis") and hasattr(m.ransac_voting, "voting_for_hypothesis")
+
+
+def test_logits_job_and_eval_wrapper_surface(built_lib):
+    """SURVEY 8(f) N3 boundary: seg_pred [b,C,h,w] is marshalled as PVV_MASK_LOGITS_F32 with the (b,h,w) strides and the
+    class stride split out; EvalWrapper.forward has the reference's signature (tools/train_linemod.py:117)."""
+    import inspect
+    from pvnet_b200 import _lib
+    from pvnet_b200 import ransac_voting_gpu as pv
+    from pvnet_b200.eval_wrapper import EvalWrapper
+    seg = torch.zeros((2, 3, 8, 16)).permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)   # NHWC strides
+    vertex = torch.zeros((2, 8, 16, 4, 2))
+    j = pv._make_job(pv._prep_mask(seg), vertex, 16, 0.99, 10, 100, _lib.FG_BYTE, None, None, 0, 0, 0)
+    assert j.mask_dtype == _lib.MASK_LOGITS_F32 == 4 and j.seg_classes == 3 and j.seg_class_stride == 1
+    assert list(j.mask_strides) == [8 * 16 * 3, 16 * 3, 3]
+    L = _lib.lib()
+    assert L.pvv_workspace_bytes(C.byref(j)) > 0
+    buf = (C.c_char * 4096)()
+    j.workspace, j.workspace_bytes = C.addressof(buf), 4096
+    out = (C.c_float * 64)()
+    j.seg_classes = 0
+    assert L.pvv_v3(C.byref(j), 0.99, 100, out, None) == -1            # logits need a class count
+    with pytest.raises(ValueError, match="seg_pred"):
+        pv._make_job(torch.zeros((2, 3, 8, 15)), vertex, 16, 0.99, 10, 100, _lib.FG_BYTE, None, None, 0, 0, 0)
+    sig = inspect.signature(EvalWrapper.forward)
+    assert [(n, p.default) for n, p in list(sig.parameters.items())[1:]] == [
+        ("seg_pred", inspect._empty), ("vertex_pred", inspect._empty), ("use_argmax", True), ("use_uncertainty", False)]

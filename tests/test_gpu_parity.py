@@ -403,3 +403,97 @@ def test_motion_voting(golden_dir):
     np.testing.assert_allclose(o2.cpu().numpy(), orc.ransac_motion_voting(m2, v2), rtol=1e-5, atol=0)
     with pytest.raises(RuntimeError):
         pv.ransac_motion_voting(torch.from_numpy(mask), torch.from_numpy(vertex))              # CPU tensors: no fallback
+
+
+def _seg_from_labels(labels, classes, rng, nan_frac=0.0):
+    """Logits [b,C,h,w] whose argmax is `labels`, with ties (equal maxima: the first class wins) and, optionally, NaNs
+    (the first NaN wins, ATen's rule) planted so that the fused argmax has to restate torch.argmax exactly."""
+    b, h, w = labels.shape
+    seg = rng.normal(0, 1, (b, classes, h, w)).astype(np.float32)
+    top = seg.max(1) + 1.0
+    np.put_along_axis(seg, labels[:, None], top[:, None], 1)
+    tie = rng.random((b, h, w)) < 0.05                       # a later class equal to the maximum must not win
+    later = np.minimum(labels + 1, classes - 1)
+    cur = np.take_along_axis(seg, later[:, None], 1)[:, 0]
+    np.put_along_axis(seg, later[:, None], np.where(tie, top, cur)[:, None], 1)
+    if nan_frac:
+        nanm = rng.random((b, classes, h, w)) < nan_frac
+        seg[nanm] = np.nan
+    return seg
+
+
+@pytest.mark.parametrize("classes,nan_frac,channels_last", [(2, 0.0, False), (2, 0.001, True), (5, 0.0005, False)])
+def test_logits_argmax_fused_equals_mask_path(classes, nan_frac, channels_last):
+    """seg_pred logits consumed directly (argmax fused into the compaction pass) == the reference's
+    `mask = torch.argmax(seg_pred, 1)` followed by the layer (tools/demo.py:46-55), bit for bit."""
+    rng = np.random.default_rng(77 + classes)
+    mask, vertex, _ = synth.make_batch(3, vn=9, frac=0.04, sigma=0.05, seed=31, h=240, w=320)
+    labels = (mask != 0).astype(np.int64) * rng.integers(1, classes, mask.shape)   # labels 1..C-1 on the foreground
+    labels[1] = 0 if classes == 2 else labels[1]                                    # an empty image (skipped)
+    seg = torch.from_numpy(_seg_from_labels(labels, classes, rng, nan_frac)).to(DEV)
+    if channels_last:
+        seg = seg.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)              # same values, NHWC strides
+    tmask = torch.argmax(seg, 1)                                                    # the reference's producer
+    if not nan_frac:
+        assert torch.equal(tmask.cpu(), torch.from_numpy(labels))
+    tv = synth.as_net_output(vertex, device=DEV)
+    kw = dict(seed=5, min_num=50, max_num=2500, return_debug=True)
+    a, da = pv.ransac_voting_layer_v3(tmask, tv, 128, 0.99, **kw)
+    f, df = pv.ransac_voting_layer_v3(seg, tv, 128, 0.99, **kw)
+    assert torch.equal(da["tn"], df["tn"]) and int(da["tn"].sum()) > 0
+    for k in ("pix_xy", "counts", "win_idx", "hyp"):
+        n = int(da["tn"].sum()) if k == "pix_xy" else None
+        assert torch.equal(da[k][:n], df[k][:n]), k
+    assert torch.equal(a, f)
+    # the distribution path uses the `== 1` rule on the same labels
+    _, ca = pv.estimate_voting_distribution_with_mean(tmask, tv, a, 32, 128, seed=6, min_num=20, max_num=2500)
+    _, cf = pv.estimate_voting_distribution_with_mean(seg, tv, a, 32, 128, seed=6, min_num=20, max_num=2500)
+    assert torch.equal(ca, cf)
+    # host buffers are not a producer-side case
+    with pytest.raises(RuntimeError, match="PVV_ERR_UNSUPPORTED"):
+        pv.ransac_voting_layer_v3(seg.cpu().pin_memory(), synth.as_net_output(vertex, pin=True), 128, 0.99)
+
+
+def test_eval_wrapper_equals_reference_composition():
+    """pvnet_b200.eval_wrapper.EvalWrapper == EvalWrapper.forward of tools/demo.py:46-55 (argmax, permute/view, v3(512, 0.99))
+    and of tools/train_linemod.py:116-125 (use_uncertainty -> v5), fed the network's raw outputs."""
+    from pvnet_b200.eval_wrapper import EvalWrapper
+    rng = np.random.default_rng(3)
+    mask, vertex, _ = synth.make_batch(2, vn=9, frac=0.03, sigma=0.03, seed=11, h=240, w=320)
+    seg = torch.from_numpy(_seg_from_labels((mask != 0).astype(np.int64), 2, rng)).to(DEV)
+    vnet = synth.as_net_output(vertex, device=DEV)                       # [b,h,w,vn,2] view of the NCHW output
+    vertex_pred = vnet.reshape(2, 240, 320, 18).permute(0, 3, 1, 2)      # back to what the network returns: [b,2vn,h,w]
+    w = EvalWrapper(512, 0.99, seed=9)
+    got = w(seg, vertex_pred)
+    want = pv.ransac_voting_layer_v3(torch.argmax(seg, 1), vnet, 512, inlier_thresh=0.99, seed=9)
+    assert torch.equal(got, want)
+    kp5, conf5 = w(seg, vertex_pred, use_uncertainty=True)
+    kp5w, conf5w = pv.ransac_voting_layer_v5(torch.argmax(seg, 1), vnet, 512, inlier_thresh=0.99, seed=9)
+    assert torch.equal(kp5, kp5w) and torch.equal(conf5, conf5w)
+    got_mask = w(torch.argmax(seg, 1), vertex_pred, use_argmax=False)    # the reference's other branch: seg_pred is a mask
+    assert torch.equal(got_mask, want)
+
+
+def test_vanishing_point_primitives_vs_oracle_and_reference_kernels():
+    """the two vanishing-point primitives (ransac_voting_kernel.cu:170-351) behind the C ABI, bit for bit
+    against the C oracle and, when oracle/_ref is present, the reference's own kernels -- through the ctypes object and
+    through the torch shim that replaces the pybind module."""
+    rng = np.random.default_rng(21)
+    tn, vn, hn = 2500, 8, 80
+    coords, direct, _ = synth.vanishing_point_field(rng, tn, vn, noise=0.03)
+    direct[5] = 0.0                                                       # a zero direction: norm1 < 1e-6 -> never votes
+    idxs = rng.integers(0, tn, (hn, vn, 2)).astype(np.int32)
+    idxs[0] = idxs[0][:, :1]                                              # identical pair
+    td, tc, ti = (torch.from_numpy(a).to(DEV) for a in (direct, coords, idxs))
+    o_hyp = orc.generate_hypothesis_vanishing_point(direct, coords, idxs)
+    impls = [pv.ransac_voting, pv.torch_extension()] + ([ref_driver.ext()] if ref_driver.available() else [])
+    for m in impls:
+        hyp = m.generate_hypothesis_vanishing_point(td, tc, ti)
+        assert hyp.shape == (hn, vn, 3) and np.array_equal(_bits(hyp), _bits(o_hyp)), m
+        for thresh in (0.99, 0.999):
+            inl = torch.zeros((hn, vn, tn), dtype=torch.uint8, device=DEV)
+            m.voting_for_hypothesis_vanishing_point(td, tc, hyp, inl, thresh)
+            o_inl = np.zeros((hn, vn, tn), np.uint8)
+            orc.voting_for_hypothesis_vanishing_point(direct, coords, o_hyp, o_inl, thresh)
+            assert np.array_equal(inl.cpu().numpy(), o_inl), (m, thresh)
+            assert 0 < o_inl.sum() < o_inl.size and not o_inl[:, :, 5].any()

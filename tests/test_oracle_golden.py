@@ -110,3 +110,36 @@ def test_motion_voting_small_batch(golden_dir):
     out = orc.ransac_motion_voting(z["mask"].astype(np.int64), sb["vertex"])
     assert np.all(out[1] == 0)                                           # no foreground: zeros (:978-980)
     np.testing.assert_allclose(out, z["out"], rtol=RTOL, atol=0)
+
+
+def test_vanishing_point_primitives_known_answer():
+    """The reference's own (commented) acceptance check for this path, ransac_voting_gpu.py:1091-1094: a voted vanishing
+    point is a positive multiple of the true homogeneous point (ratio >= 0, equal across the three components).  On an
+    exact field every non-degenerate hypothesis must satisfy it, and every pixel must vote for it."""
+    rng = np.random.default_rng(8)
+    tn, vn, hn = 400, 6, 64
+    coords, direct, V = synth.vanishing_point_field(rng, tn, vn)
+    idxs = rng.integers(0, tn, (hn, vn, 2)).astype(np.int32)
+    hyp = orc.generate_hypothesis_vanishing_point(direct, coords, idxs)
+    assert hyp.shape == (hn, vn, 3)
+    ok = 0
+    for hi in range(hn):
+        for vi in range(vn):
+            h = hyp[hi, vi].astype(np.float64)
+            if np.abs(h).max() < 1e-4:
+                continue                                   # zeroed (rays judged non-intersecting) or the same pixel twice:
+                                                           # the reference has no degenerate-pair guard here, only noise
+            big = np.abs(V[vi]) > 1e-9
+            ratio = h[big] / V[vi][big]
+            assert np.all(ratio > 0) and np.ptp(ratio) <= 2e-3 * ratio.mean(), (hi, vi, h, V[vi])
+            assert np.all(np.abs(h[~big]) <= 2e-3 * np.abs(h).max())
+            ok += 1
+    assert ok > 0.5 * hn * vn
+    # every pixel votes for the true point (scaled like a hypothesis), none for its negation
+    true_h = np.broadcast_to((V * 37.0).astype(np.float32), (1, vn, 3)).copy()
+    inl = np.zeros((1, vn, tn), np.uint8)
+    orc.voting_for_hypothesis_vanishing_point(direct, coords, true_h, inl, 0.999)
+    assert inl.all()
+    inl[:] = 0
+    orc.voting_for_hypothesis_vanishing_point(direct, coords, -true_h, inl, 0.999)
+    assert not inl.any()
