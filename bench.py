@@ -165,7 +165,7 @@ def run_reference(args):
             "cpu_baseline": cpu,
             "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "hyp_pixel_tests_per_s": tests / dt, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def run_ours(args):
@@ -302,13 +302,30 @@ def run_ours(args):
                 "hyp_pixel_tests_per_s": world * tests_per_step * args.steps / (ms * 1e-3),
                 "stage_ms": st, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def _emit(line):
+    """The ONE JSON line of the contract goes to the process's real stdout; everything else a library may print there
+    (NCCL's version banner under NCCL_DEBUG=VERSION, for one) was redirected to stderr by _quiet_stdout()."""
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
+def _quiet_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+_REAL_STDOUT = sys.stdout
+
 if __name__ == "__main__":
     a = parse()
+    _quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
