@@ -497,3 +497,87 @@ def test_vanishing_point_primitives_vs_oracle_and_reference_kernels():
             orc.voting_for_hypothesis_vanishing_point(direct, coords, o_hyp, o_inl, thresh)
             assert np.array_equal(inl.cpu().numpy(), o_inl), (m, thresh)
             assert 0 < o_inl.sum() < o_inl.size and not o_inl[:, :, 5].any()
+
+
+@pytest.mark.parametrize("h,w,vn,hn,frac,max_num", [
+    (37, 53, 1, 5, 0.5, 30000),        # smaller than one compaction tile, one keypoint, hn below one warp and not a multiple of 4
+    (250, 333, 17, 130, 0.06, 30000),  # ragged tiles, 17 keypoints, hn between the CTA shapes
+    (96, 128, 3, 1030, 0.3, 30000),    # three hypothesis passes, the last one partial
+    (64, 64, 2, 64, 1.0, 700),         # every pixel foreground, subsampled (fg > max_num)
+])
+def test_ragged_shapes_vs_oracle(h, w, vn, hn, frac, max_num):
+    """Edge shapes: counts / argmax / compaction bit-exact against the oracle, filter == exact-only kernel."""
+    b = 3
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=min(frac, 0.6), sigma=0.08, seed=h + w, h=h, w=w)
+    if frac >= 1.0:
+        mask[:] = 1
+        rng = np.random.default_rng(4)
+        ang = rng.uniform(0, 2 * np.pi, (b, h, w, vn))
+        vertex = np.stack([np.cos(ang), np.sin(ang)], -1).astype(np.float32)
+    mask[b - 1] = 0
+    mask[b - 1, 0, :7] = 1                                  # fewer than min_num pixels: skipped image, zeros out
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    kw = dict(seed=3, min_num=10, max_num=max_num, return_debug=True)
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, 0.99, **kw)
+    out_x, dbg_x = pv.ransac_voting_layer_v3(tm, tv, hn, 0.99, force_exact=True, **kw)
+    assert torch.equal(dbg["counts"], dbg_x["counts"]) and torch.equal(out, out_x)
+    sel = pv.make_selection(3, b, h, w, torch.device(DEV)).cpu().numpy() if max_num < h * w else None
+    _check_v3_against_oracle(mask, vertex, hn, 0.99, 10, max_num, dbg["idxs"].cpu().numpy(), sel, out, dbg)
+    assert int(dbg["tn"][b - 1]) == 0 and not out[b - 1].any()
+
+
+def test_cuda_graph_capture_and_replay():
+    """The device entry points neither synchronise nor allocate outside the caller's allocator, so a call can be
+    captured into a CUDA graph and replayed on new data in the same buffers."""
+    mask, vertex, _ = synth.make_batch(4, vn=9, frac=0.03, sigma=0.05, seed=50, h=240, w=320)
+    mask2, vertex2, _ = synth.make_batch(4, vn=9, frac=0.05, sigma=0.02, seed=60, h=240, w=320)
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    eager1 = pv.ransac_voting_layer_v3(tm, tv, 256, 0.99, seed=8)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        pv.ransac_voting_layer_v3(tm, tv, 256, 0.99, seed=8)          # warm-up on the capture stream
+        with torch.cuda.graph(g, stream=side):
+            captured = pv.ransac_voting_layer_v3(tm, tv, 256, 0.99, seed=8)
+    torch.cuda.current_stream().wait_stream(side)
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(captured, eager1)
+    tm.copy_(torch.from_numpy(mask2))
+    tv.copy_(torch.from_numpy(vertex2).to(DEV))
+    g.replay()
+    torch.cuda.synchronize()
+    eager2 = pv.ransac_voting_layer_v3(tm, tv, 256, 0.99, seed=8)
+    assert torch.equal(captured, eager2) and not torch.equal(eager1, eager2)
+
+
+def test_concurrent_threads_and_streams():
+    """Re-entrancy (DataParallel calls the layer from one thread per GPU, tools/train_linemod.py:222-223):
+    four host threads, each on its own stream, give the serial results."""
+    import threading
+    jobs = []
+    for i in range(4):
+        mask, vertex, _ = synth.make_batch(2, vn=9, frac=0.02 + 0.01 * i, sigma=0.05, seed=200 + i, h=240, w=320)
+        jobs.append((torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)))
+    serial = [pv.ransac_voting_layer_v3(m, v, 128, 0.99, seed=40 + i) for i, (m, v) in enumerate(jobs)]
+    torch.cuda.synchronize()
+    got, errs = [None] * 4, []
+
+    def work(i):
+        try:
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                for _ in range(5):
+                    got[i] = pv.ransac_voting_layer_v3(jobs[i][0], jobs[i][1], 128, 0.99, seed=40 + i)
+            s.synchronize()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    for i in range(4):
+        assert torch.equal(got[i], serial[i])
