@@ -197,6 +197,26 @@ int pvv_voting_for_hypothesis_vanishing_point(const float *direct, const float *
                                               uint8_t *inliers, int tn, int vn, int hn, float inlier_thresh,
                                               void *stream);
 
+/*
+ * Batched uncertainty-driven PnP -- the consumer of pvv_cov.  Replaces, per image,
+ *   Evaluator.evaluate_uncertainty   lib/utils/evaluation_utils.py:164-183      (covariance -> 2x2 weights)
+ *   uncertainty_pnp                  lib/utils/extend_utils/extend_utils.py:63-114 (start pose + cffi call)
+ *   the Ceres problem                lib/utils/extend_utils/src/uncertainty_pnp.cpp:61-92
+ * i.e. pose = argmin over (R,t) of sum_i || W_i (proj(K, R X_i + t) - x_i) ||^2.  All pointers are device pointers.
+ *   pts2d           [b,vn,2]    keypoints (pvv_v3 / pvv_v5 output)
+ *   weights_or_cov  mode 0: covariances [b,vn,2,2] (pvv_cov output): W_i = inv(sqrtm(cov_i)), zero weight when
+ *                           cov_i[0,0] < 1e-6 or cov_i has a NaN (evaluation_utils.py:171-173)
+ *                   mode 1: weights [b,vn,3] = wxx,wxy,wyy, what uncertainty_pnp() itself takes
+ *   f64_inputs      0: pts2d / weights_or_cov are float32, 1: float64
+ *   pts3d           [vn,3] float64 (+ pts3d_image_stride elements per image; 0 = one object for the whole batch)
+ *   camera          [3,3] float64 row-major intrinsics (+ camera_image_stride; 0 = shared)
+ *   out_pose        [b,3,4] float64 = [R|t], as uncertainty_pnp returns it
+ *   out_info        optional [b,3] float64: final cost, LM iterations, status (0 converged, 1 iteration cap, 2 no start)
+ */
+int pvv_uncertainty_pnp(const void *pts2d, const void *weights_or_cov, int mode, int f64_inputs, const double *pts3d,
+                        int64_t pts3d_image_stride, const double *camera, int64_t camera_image_stride, int b, int vn,
+                        double *out_pose, double *out_info, void *stream);
+
 /* The library's draw streams, materialised (for feeding the oracle / the reference wrapper the same draws). */
 int pvv_make_idxs(uint64_t seed, int64_t image_id_base, int b, int hn_total, int vn, const int32_t *tn /*device [b]*/,
                   int32_t *idxs /*device [b,hn_total,vn,2]*/, void *stream);

@@ -8,7 +8,9 @@
 #define PVV_MAX_VN 64
 #define PVV_TILE_PX 1024   // pixels per compaction tile (K1)
 #define PVV_CHUNK_PX 256   // pixels per voting work item (K3)
+#ifndef PVV_FIN_SPLIT
 #define PVV_FIN_SPLIT 4     // CTAs sharing the pixels of one (image, keypoint) in K4
+#endif
 
 // ---------------------------------------------------------------------------------------------------
 // Reference arithmetic (bit-exact restatement of what nvcc 12.9 emits for the reference kernels on

@@ -93,6 +93,7 @@ __device__ __forceinline__ uint32_t mask_value_t(const pvv_dims &d, const void *
 template <int DT, bool LINEAR>
 __global__ void __launch_bounds__(kThreads) k_tile_count(pvv_dims d, const void *mask, pvv_ws ws)
 {
+    pvv_pdl_enter();  // first kernel of the chain (plain launch after the memset): the wait is a no-op, the trigger is not
     const int img = blockIdx.y, tile = blockIdx.x;
     const int npx = d.h * d.w;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -142,6 +143,7 @@ static void launch_tile_count(const pvv_dims &d, const void *mask, const pvv_ws 
 // One warp per tile (lane = one 32-pixel word); a CTA whose image is not subsampled exits at once.
 __global__ void __launch_bounds__(kThreads) k_tile_recount(pvv_dims d, const float *selection, pvv_ws ws)
 {
+    pvv_pdl_enter();
     const int img = blockIdx.y;
     const long long fg = ws.img_fg[img];
     if (fg <= d.max_num || fg < d.min_num) return;
@@ -165,6 +167,7 @@ __global__ void __launch_bounds__(kThreads) k_tile_recount(pvv_dims d, const flo
 // ---- K1c: per-image exclusive scan of tile counts; the last block scans the batch ------------------
 __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
 {
+    pvv_pdl_enter();
     const int img = blockIdx.x;
     const long long fg = ws.img_fg[img];
     int flags = 0;
@@ -230,9 +233,12 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
 
 // ---- K1d: scatter (reads the bitmask, not the mask) ------------------------------------------------
 constexpr int kTilesPerCta = 4;  // empty tiles (most of an image) cost one load, not one CTA
+constexpr int kKpPerCta = 3;     // blockIdx.z = a group of keypoints: the gather is latency-bound, so the keypoint planes of
+                                 // a tile go to different CTAs (the cheap ranking is repeated, the loads are spread)
 
 __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *vertex, pvv_ws ws)
 {
+    pvv_pdl_enter();
     const int img = blockIdx.y;
     const int tn = ws.tn[img];
     if (tn == 0) return;
@@ -266,9 +272,11 @@ __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *v
         const int cs = ws.chunk_start[img];
         // consecutive threads take consecutive pixels (coalesced along x inside a keypoint plane); every thread walks the
         // keypoints of its pixel
+        const int vi0 = blockIdx.z * kKpPerCta, vi1 = min(d.vn, vi0 + kKpPerCta);
         for (int j = threadIdx.x; j < total; j += kThreads) {
-            ws.pix_xy[base + j] = s_xy[j];
-            {   // the middle pixel of a voting chunk is the origin of that chunk's local frame in K3
+            if (blockIdx.z == 0) {
+                ws.pix_xy[base + j] = s_xy[j];
+                // the middle pixel of a voting chunk is the origin of that chunk's local frame in K3
                 const int t = toff + j, c = t / PVV_CHUNK_PX;
                 if (t - c * PVV_CHUNK_PX == (min(PVV_CHUNK_PX, tn - c * PVV_CHUNK_PX) >> 1)) ws.chunk_tab[cs + c].w = (int)s_xy[j];
             }
@@ -277,7 +285,7 @@ __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *v
             // 3 keypoints (6 loads) in flight per thread: measured best -- 18 in flight is 1.7x slower (the planes of one
             // image are 1.2 MB apart: too many open DRAM pages / TLB entries per warp)
 #pragma unroll 3
-            for (int vi = 0; vi < d.vn; ++vi) {
+            for (int vi = vi0; vi < vi1; ++vi) {
                 float2 v;
                 v.x = __ldg(src + vi * d.vs[3]);
                 v.y = __ldg(src + vi * d.vs[3] + d.vs[4]);
@@ -304,11 +312,12 @@ cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float 
     ++*launches;
     if ((long long)d.max_num < (long long)d.h * d.w * (d.fg_rule == PVV_FG_BYTE ? 255 : 1)) {
         const dim3 rgrid((ws.ntiles + kThreads / 32 - 1) / (kThreads / 32), d.b);
-        k_tile_recount<<<rgrid, kThreads, 0, st>>>(d, selection, ws);
+        pvv_launch_pdl(k_tile_recount, rgrid, dim3(kThreads), st, d, selection, ws);
         ++*launches;
     }
-    k_scan<<<d.b, kThreads, 0, st>>>(d, ws);
-    k_scatter<<<dim3((ws.ntiles + kTilesPerCta - 1) / kTilesPerCta, d.b), kThreads, 0, st>>>(d, vertex, ws);
+    pvv_launch_pdl(k_scan, dim3(d.b), dim3(kThreads), st, d, ws);
+    pvv_launch_pdl(k_scatter, dim3((ws.ntiles + kTilesPerCta - 1) / kTilesPerCta, d.b, (d.vn + kKpPerCta - 1) / kKpPerCta),
+                   dim3(kThreads), st, d, vertex, ws);
     *launches += 2;
     return cudaGetLastError();
 }

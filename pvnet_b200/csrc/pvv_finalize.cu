@@ -11,7 +11,10 @@
 
 namespace {
 
-constexpr int kFinThreads = 256;
+#ifndef PVV_FIN_THREADS
+#define PVV_FIN_THREADS 256
+#endif
+constexpr int kFinThreads = PVV_FIN_THREADS;
 
 __device__ __forceinline__ double block_sum(double v, double *s_buf)
 {
@@ -24,6 +27,27 @@ __device__ __forceinline__ double block_sum(double v, double *s_buf)
 #pragma unroll
     for (int i = 0; i < kFinThreads / 32; ++i) t += s_buf[i];
     return t;
+}
+
+// five sums at once (the normal equations): one pair of barriers instead of five
+__device__ __forceinline__ void block_sum5(double (&v)[5], double *s_buf5 /* [5 * kFinThreads / 32] */)
+{
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0)
+#pragma unroll
+        for (int i = 0; i < 5; ++i) s_buf5[i * (kFinThreads / 32) + (threadIdx.x >> 5)] = v[i];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < kFinThreads / 32; ++w) t += s_buf5[i * (kFinThreads / 32) + w];
+        v[i] = t;
+    }
 }
 
 // max count with lowest-index tie rule (torch.max(dim) returns the first maximal index)
@@ -65,6 +89,8 @@ struct v3_dbg {
 __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws ws, float *out_kp, float *out_conf, v3_dbg g)
 {
     __shared__ double s_buf[kFinThreads / 32];
+    __shared__ double s_buf5[5 * kFinThreads / 32];
+    pvv_pdl_enter();
     __shared__ float2 s_pt;
     __shared__ bool s_last;
     const int img = blockIdx.y, vi = blockIdx.x, part = blockIdx.z;
@@ -88,23 +114,35 @@ __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws 
     const float2 win = best_cnt > 0 ? ws.hyp[row + best_h] : make_float2(0.f, 0.f);
 
     const long long off = ws.img_off[img];
-    double s00 = 0, s01 = 0, s11 = 0, b0 = 0, b1 = 0;
-    for (int t = part * kFinThreads + threadIdx.x; t < tn; t += kFinThreads * PVV_FIN_SPLIT) {
-        const uint32_t xy = ws.pix_xy[off + t];
-        const float2 dir = ws.pix_dir[(long long)vi * ws.cap + off + t];
-        const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
-        const bool inl = pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), cx, cy, win.x, win.y, d.thresh);
-        if (g.win_inlier) g.win_inlier[(long long)vi * g.dbg_cap + off + t] = inl ? 1 : 0;
-        if (inl) {
-            const float nx = dir.y, ny = -dir.x;                                 // :586-587
-            const float bb = __fadd_rn(__fmul_rn(nx, cx), __fmul_rn(ny, cy));    // :596 (fp32 products, 2-term sum)
-            s00 += (double)nx * nx; s01 += (double)nx * ny; s11 += (double)ny * ny;
-            b0 += (double)__fmul_rn(nx, bb);                                     // :598
-            b1 += (double)__fmul_rn(ny, bb);
+    double acc[5] = {0, 0, 0, 0, 0};  // ATA00, ATA01, ATA11, ATb0, ATb1
+    const float2 *pdir = ws.pix_dir + (long long)vi * ws.cap + off;
+    constexpr int STEP = kFinThreads * PVV_FIN_SPLIT;
+    for (int t0 = part * kFinThreads + threadIdx.x; t0 < tn; t0 += 2 * STEP) {
+        // two pixels per step, loads first: the loop is a chain of L2 round trips otherwise
+        const int t1 = t0 + STEP;
+        const bool has1 = t1 < tn;
+        const uint32_t xy0 = ws.pix_xy[off + t0], xy1 = has1 ? ws.pix_xy[off + t1] : 0u;
+        const float2 dir0 = pdir[t0], dir1 = has1 ? pdir[t1] : make_float2(0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            if (u == 1 && !has1) break;
+            const int t = u ? t1 : t0;
+            const uint32_t xy = u ? xy1 : xy0;
+            const float2 dir = u ? dir1 : dir0;
+            const float cx = (float)(xy & 0xffffu), cy = (float)(xy >> 16);
+            const bool inl = pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), cx, cy, win.x, win.y, d.thresh);
+            if (g.win_inlier) g.win_inlier[(long long)vi * g.dbg_cap + off + t] = inl ? 1 : 0;
+            if (inl) {
+                const float nx = dir.y, ny = -dir.x;                                 // :586-587
+                const float bb = __fadd_rn(__fmul_rn(nx, cx), __fmul_rn(ny, cy));    // :596 (fp32 products, 2-term sum)
+                acc[0] += (double)nx * nx; acc[1] += (double)nx * ny; acc[2] += (double)ny * ny;
+                acc[3] += (double)__fmul_rn(nx, bb);                                 // :598
+                acc[4] += (double)__fmul_rn(ny, bb);
+            }
         }
     }
-    s00 = block_sum(s00, s_buf); s01 = block_sum(s01, s_buf); s11 = block_sum(s11, s_buf);
-    b0 = block_sum(b0, s_buf); b1 = block_sum(b1, s_buf);
+    block_sum5(acc, s_buf5);
+    double s00 = acc[0], s01 = acc[1], s11 = acc[2], b0 = acc[3], b1 = acc[4];
     if (threadIdx.x == 0) {
         double *slot = ws.fin_part + (o * PVV_FIN_SPLIT + part) * 5;
         slot[0] = s00; slot[1] = s01; slot[2] = s11; slot[3] = b0; slot[4] = b1;
@@ -156,6 +194,7 @@ __global__ void __launch_bounds__(kFinThreads) k_v3_finalize(pvv_dims d, pvv_ws 
 __global__ void __launch_bounds__(kFinThreads) k_cov_finalize(pvv_dims d, pvv_ws ws, const float *mean, float *out_cov)
 {
     __shared__ double s_buf[kFinThreads / 32];
+    pvv_pdl_enter();
     const int img = blockIdx.y, vi = blockIdx.x;
     const int tn = ws.tn[img];
     const long long o = (long long)img * d.vn + vi;
@@ -200,6 +239,7 @@ __global__ void __launch_bounds__(kFinThreads) k_cov_finalize(pvv_dims d, pvv_ws
 __global__ void __launch_bounds__(kFinThreads) k_motion_mean(pvv_dims d, pvv_ws ws, float *out_kp)
 {
     __shared__ double s_buf[kFinThreads / 32];
+    pvv_pdl_enter();
     const int img = blockIdx.y, vi = blockIdx.x;
     const int tn = ws.tn[img];
     const long long o = (long long)img * d.vn + vi, off = ws.img_off[img];
@@ -221,6 +261,7 @@ __global__ void __launch_bounds__(kFinThreads) k_motion_mean(pvv_dims d, pvv_ws 
 // counts [b][vn][hn_pad] -> reference layout [b][hn][vn]
 __global__ void k_export_counts(pvv_dims d, pvv_ws ws, int32_t *counts_out)
 {
+    pvv_pdl_enter();
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long total = (long long)d.b * d.hn * d.vn;
     if (e >= total) return;
@@ -241,14 +282,14 @@ cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *o
         g.win_idx = dbg->win_idx; g.win_count = dbg->win_count; g.win_pts = dbg->win_pts;
         g.win_inlier = dbg->win_inlier; g.normal_eq = dbg->normal_eq; g.dbg_cap = dbg->pool_capacity;
     }
-    k_v3_finalize<<<dim3(d.vn, d.b, PVV_FIN_SPLIT), kFinThreads, 0, st>>>(d, ws, out_kp, out_conf, g);
+    pvv_launch_pdl(k_v3_finalize, dim3(d.vn, d.b, PVV_FIN_SPLIT), dim3(kFinThreads), st, d, ws, out_kp, out_conf, g);
     ++*launches;
     return cudaGetLastError();
 }
 
 cudaError_t pvv_launch_motion_mean(const pvv_dims &d, const pvv_ws &ws, float *out_kp, cudaStream_t st, int *launches)
 {
-    k_motion_mean<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, out_kp);
+    pvv_launch_pdl(k_motion_mean, dim3(d.vn, d.b), dim3(kFinThreads), st, d, ws, out_kp);
     ++*launches;
     return cudaGetLastError();
 }
@@ -256,7 +297,7 @@ cudaError_t pvv_launch_motion_mean(const pvv_dims &d, const pvv_ws &ws, float *o
 cudaError_t pvv_launch_cov_finalize(const pvv_dims &d, const pvv_ws &ws, const float *mean, float *out_cov,
                                     cudaStream_t st, int *launches)
 {
-    k_cov_finalize<<<dim3(d.vn, d.b), kFinThreads, 0, st>>>(d, ws, mean, out_cov);
+    pvv_launch_pdl(k_cov_finalize, dim3(d.vn, d.b), dim3(kFinThreads), st, d, ws, mean, out_cov);
     ++*launches;
     return cudaGetLastError();
 }
@@ -265,7 +306,7 @@ cudaError_t pvv_launch_export_counts(const pvv_dims &d, const pvv_ws &ws, int32_
                                      int *launches)
 {
     const long long total = (long long)d.b * d.hn * d.vn;
-    k_export_counts<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d, ws, counts_out);
+    pvv_launch_pdl(k_export_counts, dim3((unsigned)((total + 255) / 256)), dim3(256), st, d, ws, counts_out);
     ++*launches;
     return cudaGetLastError();
 }
@@ -283,7 +324,7 @@ cudaError_t pvv_launch_debug_export(const pvv_dims &d, const pvv_ws &ws, const p
     if (!e && dbg->amb_count) e = cudaMemcpyAsync(dbg->amb_count, &ws.counters[PVV_CTR_AMB_LO], sizeof(uint64_t), cudaMemcpyDeviceToDevice, st);
     if (!e && dbg->counts) {
         const long long total = (long long)d.b * d.hn * d.vn;
-        k_export_counts<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d, ws, dbg->counts);
+        pvv_launch_pdl(k_export_counts, dim3((unsigned)((total + 255) / 256)), dim3(256), st, d, ws, dbg->counts);
         ++*launches;
         e = cudaGetLastError();
     }

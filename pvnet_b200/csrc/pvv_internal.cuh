@@ -46,6 +46,36 @@ struct pvv_dims {
     long long vs[5];   // vertex strides (elements)
 };
 
+// Programmatic dependent launch (PDL): the kernels of one call form a chain on the caller's stream; each is launched with
+// programmatic stream serialisation, so its launch and CTA scheduling overlap the tail of its predecessor instead of
+// following the predecessor's completion by a launch latency.  Contract inside the library: EVERY kernel launched
+// through pvv_launch_pdl executes pvv_pdl_enter() as its first statement in every thread -- it waits until the
+// predecessor grid has completed and its writes are visible (which, by induction, covers all earlier grids of the
+// chain), then lets the next kernel of the chain start launching.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pvv_pdl_enter()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t pvv_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+
 // K1: compaction (pvv_compact.cu)
 cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float *vertex, const float *selection,
                                const pvv_ws &ws, cudaStream_t st, int *launches);

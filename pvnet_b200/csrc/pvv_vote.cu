@@ -26,6 +26,7 @@ namespace {
 // ---- K2 -------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out)
 {
+    pvv_pdl_enter();
     const int img = blockIdx.y;
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= d.vn * d.hn) return;
@@ -192,6 +193,7 @@ __global__ void __launch_bounds__(THREADS) k_count_exact(pvv_dims d, pvv_ws ws)
     __shared__ float2 sDir[PVV_CHUNK_PX];
     __shared__ uint32_t sXY[PVV_CHUNK_PX];
     __shared__ int s_item;
+    pvv_pdl_enter();
     const int tid = threadIdx.x;
     const int total_items = ws.chunk_start[d.b] * d.vn;
     while (true) {
@@ -263,6 +265,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
     __shared__ uint32_t s_q2[K3_QCAP];  // phase B: (pixel << 16) | (k << 8) | thread
     __shared__ int s_id[2], s_P[2], s_qn, s_q2n;
 
+    pvv_pdl_enter();
     const int tid = threadIdx.x;
     const int total_items = ws.chunk_start[d.b] * d.vn;
     unsigned long long amb_local = 0;
@@ -501,7 +504,7 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
                                   cudaStream_t st, int *launches)
 {
     const dim3 grid((d.vn * d.hn + 255) / 256, d.b);
-    k_hypotheses<<<grid, 256, 0, st>>>(d, idxs, ws, hyp_out);
+    pvv_launch_pdl(k_hypotheses, grid, dim3(256), st, d, idxs, ws, hyp_out);
     ++*launches;
     return cudaGetLastError();
 }
@@ -538,7 +541,7 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
     int per_sm = 8;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS, MINB>, THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    k_count<H, THREADS, MINB><<<sms * per_sm, THREADS, 0, st>>>(d, ws, bc);
+    pvv_launch_pdl(k_count<H, THREADS, MINB>, dim3(sms * per_sm), dim3(THREADS), st, d, ws, bc);
     return cudaGetLastError();
 }
 
@@ -557,7 +560,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     if (!fast) {
         int per_sm = 8;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count_exact<4, 128>, 128, 0);
-        k_count_exact<4, 128><<<sms * (per_sm < 1 ? 1 : per_sm), 128, 0, st>>>(d, ws);
+        pvv_launch_pdl(k_count_exact<4, 128>, dim3(sms * (per_sm < 1 ? 1 : per_sm)), dim3(128), st, d, ws);
         e = cudaGetLastError();
     }
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);

@@ -581,3 +581,70 @@ def test_concurrent_threads_and_streams():
     assert not errs, errs
     for i in range(4):
         assert torch.equal(got[i], serial[i])
+
+
+def test_uncertainty_pnp_vs_oracle():
+    """batched uncertainty PnP on the GPU against the CPU restatement of extend_utils.py:63-114 +
+    uncertainty_pnp.cpp:61-92 (OpenCV P3P start + LM on the same weighted residuals).  Both run to convergence, so the
+    poses must agree to solver precision: tolerance 1e-6 absolute on R and on t (metres), written here."""
+    from oracle import pnp_oracle as po
+    from pvnet_b200 import uncertainty_pnp as up
+    from tests_support import pnp_case
+    rng = np.random.default_rng(2024)
+    b, pn = 24, 9
+    cases = [pnp_case(rng, pn, noise=(0.0 if i < 4 else 1.5)) for i in range(b)]
+    K, X = cases[0][0], cases[0][1]
+    x = np.stack([c[3] for c in cases]).astype(np.float32)
+    cov = np.stack([c[4] for c in cases])
+    cov[5, 2] = np.nan
+    cov[6, 7, 0, 0] = 1e-7
+    # shared object and camera, covariances converted on the device (evaluate_uncertainty's path)
+    Xs = np.stack([c[1] for c in cases])
+    poses, info = up.uncertainty_pnp_batch(torch.from_numpy(x).to(DEV), torch.from_numpy(cov).to(DEV), Xs, K, return_info=True)
+    poses, info = poses.cpu().numpy(), info.cpu().numpy()
+    assert np.all(info[:, 2] == 0), info                                      # converged everywhere
+    for i in range(b):
+        want = po.evaluate_uncertainty_pose(x[i], cov[i], Xs[i], K)
+        np.testing.assert_allclose(poses[i], want, atol=1e-6, err_msg=f"image {i}")
+        if i < 4:
+            np.testing.assert_allclose(poses[i], cases[i][2], atol=2e-5)     # exact projections (rounded to fp32): the pose itself
+        R = poses[i][:, :3]
+        np.testing.assert_allclose(R @ R.T, np.eye(3), atol=1e-12)
+        assert np.linalg.det(R) > 0.999999
+    # the reference's per-image numpy signature with explicit weights, float64 inputs
+    w = po.weights_from_covariance(cov[9])
+    got = up.uncertainty_pnp(x[9].astype(np.float64), w, Xs[9], K)
+    np.testing.assert_allclose(got, po.uncertainty_pnp(x[9].astype(np.float64), w, Xs[9], K), atol=1e-6)
+
+
+def test_voting_to_pose_pipeline():
+    """mask + vertex field -> v3 keypoints -> covariances -> uncertainty PnP, all on the device: the recovered pose
+    reprojects the object's keypoints onto the voted ones."""
+    from pvnet_b200 import uncertainty_pnp as up
+    from tests_support import pnp_case
+    rng = np.random.default_rng(5)
+    b, vn, h, w = 3, 9, 480, 640
+    K, X, Rt, x, _ = pnp_case(rng, vn)
+    masks = np.zeros((b, h, w), np.int64)
+    verts = np.zeros((b, h, w, vn, 2), np.float32)
+    kps = np.zeros((b, vn, 2))
+    for i in range(b):
+        r = np.random.default_rng(100 + i)
+        masks[i] = synth.blob_mask(r, 0.03, h, w)
+        kps[i] = x + r.normal(0, 0.3, x.shape)
+        verts[i] = synth.unit_field(masks[i], kps[i], 0.03, r)
+    tm, tv = torch.from_numpy(masks).to(DEV), synth.as_net_output(verts, device=DEV)
+    kp = pv.ransac_voting_layer_v3(tm, tv, 512, 0.99, seed=1)
+    _, cov = pv.estimate_voting_distribution_with_mean(tm, tv, kp, seed=2)
+    poses = up.evaluate_uncertainty_pose(kp, cov, X, K).cpu().numpy()
+    from oracle import pnp_oracle as po
+    kp_h, cov_h = kp.cpu().numpy(), cov.cpu().numpy()
+    assert np.isfinite(cov_h).all() and (cov_h[:, :, 0, 0] > 1e-6).all()
+    for i in range(b):
+        want = po.evaluate_uncertainty_pose(kp_h[i], cov_h[i], X, K)     # the reference's host-side step on the same inputs
+        np.testing.assert_allclose(poses[i], want, atol=1e-6)
+        P = X @ poses[i][:, :3].T + poses[i][:, 3]
+        proj = np.stack([K[0, 0] * P[:, 0] / P[:, 2] + K[0, 2], K[1, 1] * P[:, 1] / P[:, 2] + K[1, 2]], 1)
+        # keypoints far from the object are voted with less certainty and weigh less: the median reprojection is tight
+        assert np.median(np.abs(proj - kp_h[i])) < 8.0
+        assert np.abs(poses[i][:, 3] - Rt[:, 3]).max() < 0.1

@@ -7,6 +7,7 @@ import pytest
 
 from oracle import oracle as orc
 from pvnet_b200 import synth
+from tests_support import pnp_case
 
 RTOL = 1e-4  # BASELINE.json north_star: keypoints/means/covariances within 1e-4 relative
 
@@ -143,3 +144,32 @@ def test_vanishing_point_primitives_known_answer():
     inl[:] = 0
     orc.voting_for_hypothesis_vanishing_point(direct, coords, -true_h, inl, 0.999)
     assert not inl.any()
+
+
+def test_uncertainty_pnp_oracle_known_answers():
+    """N2 oracle (oracle/pnp_oracle.py restates extend_utils.py:63-114 + uncertainty_pnp.cpp:61-92).  The reference has no
+    fixture for it; pin the restatement by known answers: (i) the weights are inverse matrix square roots, (ii) exact
+    projections of a known pose are recovered, (iii) at the returned pose the gradient of the weighted cost vanishes."""
+    from oracle import pnp_oracle as po
+    rng = np.random.default_rng(12)
+    for trial in range(4):
+        K, X, Rt_true, x, cov = pnp_case(rng)
+        cov[2] = np.nan
+        cov[5, 0, 0] = 1e-7                                             # both get zero weight (evaluation_utils.py:171-173)
+        w = po.weights_from_covariance(cov)
+        assert not w[2].any() and not w[5].any()
+        for vi in (0, 1, 3):
+            W = np.array([[w[vi, 0], w[vi, 1]], [w[vi, 1], w[vi, 2]]], np.float64)
+            np.testing.assert_allclose(W @ W @ cov[vi].astype(np.float64), np.eye(2), atol=2e-5)
+        Rt = po.uncertainty_pnp(x, w, X, K)
+        np.testing.assert_allclose(Rt, Rt_true, atol=1e-9)
+        xn = x + rng.normal(0, 2.0, x.shape)
+        Rt, info = po.uncertainty_pnp(xn, w, X, K, return_info=True)
+        import cv2
+        rt = np.concatenate([cv2.Rodrigues(Rt[:, :3])[0].reshape(-1), Rt[:, 3]])
+        f0 = po.residuals(rt, xn, X, w.astype(np.float64), K)
+        assert abs(f0 @ f0 - info["cost"]) <= 1e-9 * info["cost"] and info["cost"] > 1.0
+        g = np.array([(np.sum(po.residuals(rt + e, xn, X, w.astype(np.float64), K) ** 2) -
+                       np.sum(po.residuals(rt - e, xn, X, w.astype(np.float64), K) ** 2)) / 2e-6
+                      for e in 1e-6 * np.eye(6)])
+        assert np.abs(g).max() < 1e-3 * info["cost"], g                 # stationary point of the weighted cost
