@@ -589,10 +589,9 @@ def test_uncertainty_pnp_vs_oracle():
     poses must agree to solver precision: tolerance 1e-6 absolute on R and on t (metres), written here."""
     from oracle import pnp_oracle as po
     from pvnet_b200 import uncertainty_pnp as up
-    from tests_support import pnp_case
     rng = np.random.default_rng(2024)
     b, pn = 24, 9
-    cases = [pnp_case(rng, pn, noise=(0.0 if i < 4 else 1.5)) for i in range(b)]
+    cases = [synth.pnp_case(rng, pn, noise=(0.0 if i < 4 else 1.5)) for i in range(b)]
     K, X = cases[0][0], cases[0][1]
     x = np.stack([c[3] for c in cases]).astype(np.float32)
     cov = np.stack([c[4] for c in cases])
@@ -621,10 +620,9 @@ def test_voting_to_pose_pipeline():
     """mask + vertex field -> v3 keypoints -> covariances -> uncertainty PnP, all on the device: the recovered pose
     reprojects the object's keypoints onto the voted ones."""
     from pvnet_b200 import uncertainty_pnp as up
-    from tests_support import pnp_case
     rng = np.random.default_rng(5)
     b, vn, h, w = 3, 9, 480, 640
-    K, X, Rt, x, _ = pnp_case(rng, vn)
+    K, X, Rt, x, _ = synth.pnp_case(rng, vn)
     masks = np.zeros((b, h, w), np.int64)
     verts = np.zeros((b, h, w, vn, 2), np.float32)
     kps = np.zeros((b, vn, 2))

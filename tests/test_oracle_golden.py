@@ -7,7 +7,6 @@ import pytest
 
 from oracle import oracle as orc
 from pvnet_b200 import synth
-from tests_support import pnp_case
 
 RTOL = 1e-4  # BASELINE.json north_star: keypoints/means/covariances within 1e-4 relative
 
@@ -153,7 +152,7 @@ def test_uncertainty_pnp_oracle_known_answers():
     from oracle import pnp_oracle as po
     rng = np.random.default_rng(12)
     for trial in range(4):
-        K, X, Rt_true, x, cov = pnp_case(rng)
+        K, X, Rt_true, x, cov = synth.pnp_case(rng)
         cov[2] = np.nan
         cov[5, 0, 0] = 1e-7                                             # both get zero weight (evaluation_utils.py:171-173)
         w = po.weights_from_covariance(cov)
