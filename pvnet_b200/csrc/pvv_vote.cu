@@ -75,12 +75,18 @@ struct band_consts {
 #define K3_ABL(bit) 0
 #endif
 
-constexpr int K3_GROUP = 16;   // pixels per band-check group in the hot loop (eight packed pixel pairs): measured best of 8/16
+#ifndef K3_GROUP_PX
+#define K3_GROUP_PX 16
+#endif
+#ifndef K3_SUB_LANES
+#define K3_SUB_LANES 2
+#endif
+constexpr int K3_GROUP = K3_GROUP_PX;   // pixels per band-check group in the hot loop (eight packed pixel pairs): measured best of 8/16
 constexpr int K3_QCAP = 512;   // deferred (thread, pixel group) entries per work item; overflow is resolved in line
 constexpr int K3_GSTRIDE = 3 * (K3_GROUP / 2) + 1;  // 16-byte units per pixel group in shared memory: the pad spreads the
                                                     // groups over the banks for the per-entry reads of phase A
 constexpr int K3_SP_FLOATS = 4 * K3_GSTRIDE * (PVV_CHUNK_PX / K3_GROUP);
-constexpr int K3_SUB = 2;      // phase A: lanes per flagged (hypothesis, group) entry
+constexpr int K3_SUB = K3_SUB_LANES;      // phase A: lanes per flagged (hypothesis, group) entry
 
 // packed FP32x2 helpers: Blackwell issues one FFMA2 for two IEEE fp32 FMAs (half the issue slots of two FFMAs)
 typedef unsigned long long f32x2;
