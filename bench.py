@@ -255,6 +255,12 @@ def run_ours(args):
                 "peak_source": "FFMA probe kernel run in this process (pvv_fp32_peak_tflops); MEASURED_PEAKS.json has no FP32 figure",
                 "flop_per_test": FLOP_PER_TEST, "tests_per_launch": tests_per_step, "kernel_ms": st["count"],
                 "tests_per_s": tests_per_step / (st["count"] * 1e-3),
+                # issue-slot utilisation next to the FLOP fraction.  4.9 warp instructions per warp-test is the
+                # SASS count of the shipped hot loop (profiles/r01_k_count_ncu_summary.txt); 4 schedulers per SM, 1 issue/clk
+                "warp_instr_per_test": 4.9,
+                "issue_slot_utilisation": (tests_per_step / (st["count"] * 1e-3) / 32.0 * 4.9 /
+                                           (torch.cuda.get_device_properties(dev).multi_processor_count * 4 *
+                                            (clocks.get("sm_mhz") or 1965) * 1e6)),
                 "k1_compaction": {"bound": "hbm", "achieved": k1_bytes / (st["compact"] * 1e-3) / 1e9, "peak": hbm_peak,
                                   "unit": "GB/s", "frac": k1_bytes / (st["compact"] * 1e-3) / 1e9 / hbm_peak,
                                   "kernel_ms": st["compact"], "bytes": k1_bytes,

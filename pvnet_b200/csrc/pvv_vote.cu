@@ -176,15 +176,25 @@ __device__ __forceinline__ float k3_m(float hx, float hy, const px_consts &c)
 // work item -> (image, keypoint, pixel range)
 struct k3_item { int img, vi, p0, n, ox, oy; long long off; };
 
-__device__ __forceinline__ k3_item k3_decode_item(const pvv_dims &d, const pvv_ws &ws, int item)
+// `split` (1, 2 or 4) cuts every chunk into that many pixel ranges, each its own work item: small jobs (few chunks per
+// CTA of the persistent grid) balance better; the per-item set-up is amortised over fewer pixels, so large jobs use 1.
+__device__ __forceinline__ int k3_split_for(int chunks_times_vn, int grid_ctas)
+{
+    return chunks_times_vn >= 6 * grid_ctas ? 1 : chunks_times_vn >= 3 * grid_ctas ? 2 : 4;
+}
+
+__device__ __forceinline__ k3_item k3_decode_item(const pvv_dims &d, const pvv_ws &ws, int item, int split = 1)
 {
     k3_item it;
+    const int sub = item % split;
+    item /= split;
     const int ci = item / d.vn;
     it.vi = item - ci * d.vn;
     const int4 e = __ldg(&ws.chunk_tab[ci]);  // {image, first pixel, pixels, x|y<<16 of the middle pixel}, written by K1
+    const int span = PVV_CHUNK_PX / split;
     it.img = e.x;
-    it.p0 = e.y;
-    it.n = e.z;
+    it.p0 = e.y + sub * span;
+    it.n = max(0, min(span, e.z - sub * span));  // 0: the chunk ends before this range (an empty item)
     // frame origin = the chunk's middle pixel: halves the extent P of the chunk around it, and with it the band
     it.ox = (int)((uint32_t)e.w & 0xffffu);
     it.oy = (int)((uint32_t)e.w >> 16);
@@ -273,7 +283,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 
     pvv_pdl_enter();
     const int tid = threadIdx.x;
-    const int total_items = ws.chunk_start[d.b] * d.vn;
+    const int split = k3_split_for(ws.chunk_start[d.b] * d.vn, (int)gridDim.x);
+    const int total_items = ws.chunk_start[d.b] * d.vn * split;
     unsigned long long amb_local = 0;
     const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};  // m = -1e30: never an inlier, never in the band
 
@@ -300,7 +311,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
     __syncthreads();
     int item = s_id[0];
     if (item >= total_items) return;
-    k3_item it = k3_decode_item(d, ws, item);
+    k3_item it = k3_decode_item(d, ws, item, split);
     prefetch(it, 0);
     if (tid == 0) s_id[1] = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u);
 
@@ -342,7 +353,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
         // ---- prefetch the next item's raw pixels and the id of the one after it ----
         k3_item nit = it;
         if (next < total_items) {
-            nit = k3_decode_item(d, ws, next);
+            nit = k3_decode_item(d, ws, next, split);
             prefetch(nit, buf ^ 1);
         }
         if (tid == 0) {
