@@ -5,18 +5,20 @@
 //              (ransac_voting_gpu.py:563-567 / :371-374): the [hn,vn,tn] uint8 matrix is never materialised.
 //
 // K3 design (DESIGN.md "K3"):
-//   * persistent CTAs pull (256-pixel chunk, keypoint) items from a dynamic work queue; the raw pixels of the next
-//     item are prefetched with cp.async into a second shared-memory buffer while the current item is voted on;
+//   * persistent CTAs pull (256-pixel chunk, keypoint) items from a dynamic work queue (chunks are cut in 2 or 4 when the
+//     job is small); an item is decoded with one load from the chunk table K1 wrote; the raw pixels of the next item are
+//     prefetched with cp.async into a second shared-memory buffer while the current item is voted on;
 //   * per pixel, 6 derived floats turn the reference's cosine test into two half-plane tests through the pixel
 //     (cone a > tau|c|, tau = t/sqrt(1-t^2)):  e+- = hx*p + hy*q + r,  m = min(e+, e-),  inlier <=> m > 0.
-//     Pixels are stored as PAIRS so that one packed FFMA2 evaluates a term for two pixels: 2 FFMA2 + FMNMX + LEA.HI
-//     (+ half an FMNMX3 for the band) per test; every thread keeps 4 hypotheses and their counters in registers, so
-//     the inner loop has no atomics, no shuffles, no branches and no global traffic;
+//     Pixels are stored as PAIRS so that one packed FFMA2 evaluates a term for two pixels; per test the loop issues
+//     2 FFMA2 + FMNMX + 1/2 PRMT + 1/4 IADD3 (sign counting in 16-bit lanes) + 1/2 FMNMX3 (band tracker); every thread
+//     keeps 4 hypotheses and their counters in registers, so the inner loop has no atomics, no shuffles, no branches and
+//     no global traffic;
 //   * the filter is guard-banded: a test with |m| <= T (T bounds the filter's rounding plus the uncertainty of the
 //     reference's own fp32 quotient) only sets a bit in a per-thread mask; after the loop the flagged (hypothesis,
-//     8-pixel group) pairs are re-evaluated densely by the whole CTA and the tests truly inside the band get the
-//     reference's exact rounding sequence (pvv_exact_test).  Counts are bit-identical to the reference kernel's
-//     (error analysis in DESIGN.md "Guard band").
+//     16-pixel group) pairs are re-evaluated by the CTA (phase A, the loop's own packed FMA chains) and the tests truly
+//     inside the band get the reference's exact rounding sequence (phase B, pvv_exact_test).  Counts are bit-identical
+//     to the reference kernel's (error analysis in DESIGN.md "Guard band").
 #include <stdlib.h>
 
 #include "pvv_internal.cuh"
