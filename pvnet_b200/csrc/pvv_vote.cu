@@ -182,7 +182,9 @@ struct k3_item { int img, vi, p0, n, ox, oy; long long off; };
 // CTA of the persistent grid) balance better; the per-item set-up is amortised over fewer pixels, so large jobs use 1.
 __device__ __forceinline__ int k3_split_for(int chunks_times_vn, int grid_ctas)
 {
-    return chunks_times_vn >= 6 * grid_ctas ? 1 : chunks_times_vn >= 3 * grid_ctas ? 2 : 4;
+    // measured (profiles/r01_sweep.md): worth it only below ~2.5 items per CTA; the per-item set-up and the latency of the
+    // deferred passes eat the balance gain above that, and for the one-warp CTAs of small hn at any size
+    return 2 * chunks_times_vn >= 5 * grid_ctas ? 1 : 2 * chunks_times_vn >= 3 * grid_ctas ? 2 : 4;
 }
 
 __device__ __forceinline__ k3_item k3_decode_item(const pvv_dims &d, const pvv_ws &ws, int item, int split = 1)
@@ -285,7 +287,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 
     pvv_pdl_enter();
     const int tid = threadIdx.x;
-    const int split = k3_split_for(ws.chunk_start[d.b] * d.vn, (int)gridDim.x);
+    const int split = THREADS >= 128 ? k3_split_for(ws.chunk_start[d.b] * d.vn, (int)gridDim.x) : 1;
     const int total_items = ws.chunk_start[d.b] * d.vn * split;
     unsigned long long amb_local = 0;
     const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};  // m = -1e30: never an inlier, never in the band
