@@ -452,22 +452,41 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                     const int cnt = npad - sign_lanes_total(neg[k]);  // padded and never-inlier pixels have m < 0
                     if (h < d.hn && cnt && !K3_ABL(8)) atomicAdd(&ws.counts[row + h], cnt);
                 }
-                // queue this thread's flagged (slot, group) pairs for the dense passes below
+                // queue this thread's flagged (slot, group) pairs for the dense passes below: one shared-memory atomic per
+                // warp (lane counts -> warp prefix sum -> one reservation), then every lane writes its own entries
+                uint32_t dm[H];
+                int mine = 0;
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
-                    uint32_t dm = hbase + k * THREADS + tid < d.hn && !K3_ABL(1) ? dmask[k] : 0u;
-                    while (dm) {
-                        const int grp = __ffs(dm) - 1;
-                        dm &= dm - 1;
-                        const int q = atomicAdd(&s_qn, 1);
-                        if (q < K3_QCAP) {
-                            s_q[q] = ((uint32_t)grp << 16) | ((uint32_t)k << 8) | (uint32_t)tid;
-                        } else {  // queue full (pathological inputs): resolve in line
-                            const float4 hl = sH[k * THREADS + tid];  // this thread's own entry
-                            for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j) {
-                                const float m = k3_m(hl.x, hl.y, k3_load_px(sP, j));
-                                if (!(fabsf(m) > hl.z)) resolve(hbase, tid, k, j, m);
+                    dm[k] = hbase + k * THREADS + tid < d.hn && !K3_ABL(1) ? dmask[k] : 0u;
+                    mine += __popc(dm[k]);
+                }
+                if (__any_sync(0xffffffffu, mine)) {
+                    int incl = mine;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+                        if ((tid & 31) >= o) incl += up;
+                    }
+                    int base = 0;
+                    if ((tid & 31) == 31) base = atomicAdd(&s_qn, incl);  // lane 31 holds the warp total
+                    int q = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
+#pragma unroll
+                    for (int k = 0; k < H; ++k) {
+                        uint32_t m_k = dm[k];
+                        while (m_k) {
+                            const int grp = __ffs(m_k) - 1;
+                            m_k &= m_k - 1;
+                            if (q < K3_QCAP) {
+                                s_q[q] = ((uint32_t)grp << 16) | ((uint32_t)k << 8) | (uint32_t)tid;
+                            } else {  // queue full (pathological inputs): resolve in line
+                                const float4 hl = sH[k * THREADS + tid];  // this thread's own entry
+                                for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j) {
+                                    const float m = k3_m(hl.x, hl.y, k3_load_px(sP, j));
+                                    if (!(fabsf(m) > hl.z)) resolve(hbase, tid, k, j, m);
+                                }
                             }
+                            ++q;
                         }
                     }
                 }
