@@ -646,3 +646,20 @@ def test_voting_to_pose_pipeline():
         # keypoints far from the object are voted with less certainty and weigh less: the median reprojection is tight
         assert np.median(np.abs(proj - kp_h[i])) < 8.0
         assert np.abs(poses[i][:, 3] - Rt[:, 3]).max() < 0.1
+
+
+def test_voting_pipeline_equals_serial_calls():
+    """pvnet_b200.pipeline.VotingPipeline (calls round-robined over 3 streams) returns what serial calls return."""
+    from pvnet_b200.pipeline import VotingPipeline
+    jobs = []
+    for i in range(5):
+        mask, vertex, _ = synth.make_batch(2, vn=9, frac=0.03, sigma=0.05, seed=300 + i, h=240, w=320)
+        jobs.append((torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)))
+    serial = [pv.ransac_voting_layer_v3(m, v, 256, 0.99, seed=70 + i) for i, (m, v) in enumerate(jobs)]
+    pipe = VotingPipeline(3, DEV)
+    for rep in range(3):
+        outs = [pipe.submit(m, v, 256, 0.99, seed=70 + i) for i, (m, v) in enumerate(jobs)]
+        pipe.join()
+        torch.cuda.synchronize()
+        for a, b_ in zip(outs, serial):
+            assert torch.equal(a, b_)
