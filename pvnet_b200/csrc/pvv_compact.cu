@@ -232,9 +232,15 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
 }
 
 // ---- K1d: scatter (reads the bitmask, not the mask) ------------------------------------------------
-constexpr int kTilesPerCta = 4;  // empty tiles (most of an image) cost one load, not one CTA
-constexpr int kKpPerCta = 3;     // blockIdx.z = a group of keypoints: the gather is latency-bound, so the keypoint planes of
-                                 // a tile go to different CTAs (the cheap ranking is repeated, the loads are spread)
+#ifndef PVV_TILES_PER_CTA
+#define PVV_TILES_PER_CTA 2
+#endif
+#ifndef PVV_KP_PER_CTA
+#define PVV_KP_PER_CTA 64
+#endif
+constexpr int kTilesPerCta = PVV_TILES_PER_CTA;  // empty tiles (most of an image) cost one load, not one CTA; measured 1/2/3/4/8: 2 is best
+constexpr int kKpPerCta = PVV_KP_PER_CTA;     // blockIdx.z = a group of keypoints (a tuning knob: splitting a tile's keypoint planes over
+                                 // CTAs measured slower at 1/3/5/6 per CTA than no split, so one CTA takes them all)
 
 __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *vertex, pvv_ws ws)
 {
