@@ -663,3 +663,43 @@ def test_voting_pipeline_equals_serial_calls():
         torch.cuda.synchronize()
         for a, b_ in zip(outs, serial):
             assert torch.equal(a, b_)
+
+
+@pytest.mark.skipif(not ref_driver.available(), reason="oracle/_ref (reference CUDA build) not present")
+def test_random_cases_vs_reference_cuda_kernels():
+    """Randomised shapes / thresholds / noise / far and on-pixel keypoints / scaled and zero directions: compaction,
+    hypotheses, inlier counts and argmax bit-equal to the reference's own kernels (oracle/_ref) on the same GPU."""
+    rng = np.random.default_rng(404)
+    checked = 0
+    for case in range(24):
+        h, w = int(rng.integers(24, 200)), int(rng.integers(24, 260))
+        b, vn = int(rng.integers(1, 4)), int(rng.integers(1, 12))
+        hn = int(rng.choice([5, 33, 128, 200, 512, 700]))
+        thresh = float(rng.choice([0.5, 0.9, 0.99, 0.999, 0.9999, 0.99999, 0.3]))
+        masks = np.zeros((b, h, w), np.int64)
+        verts = np.zeros((b, h, w, vn, 2), np.float32)
+        for i in range(b):
+            r = np.random.default_rng(int(rng.integers(1 << 30)))
+            masks[i] = synth.blob_mask(r, float(rng.uniform(0.03, 0.4)), h, w)
+            kp = np.stack([r.uniform(-3 * w, 4 * w, vn), r.uniform(-3 * h, 4 * h, vn)], 1) if rng.random() < 0.3 else \
+                np.stack([r.uniform(0, w, vn), r.uniform(0, h, vn)], 1)
+            if rng.random() < 0.3:
+                kp = np.round(kp)
+            verts[i] = synth.unit_field(masks[i], kp, float(rng.choice([0.0, 0.02, 0.2])), r)
+            if rng.random() < 0.3:
+                verts[i] *= r.choice([0.0, 1e-7, 1e-3, 1.0, 1e3], size=(h, w, vn, 1)).astype(np.float32)
+        tm, tv = torch.from_numpy(masks).to(DEV), torch.from_numpy(verts).to(DEV)
+        out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=case, min_num=5, max_num=10 ** 6, return_debug=True)
+        r_out, r_dbg = ref_driver.v3(tm, tv, hn, thresh, 5, 10 ** 6, dbg["idxs"])
+        for bi in range(b):
+            if r_dbg[bi] is None:
+                assert int(dbg["tn"][bi]) == 0
+                continue
+            tn, coords, direct, inl = _unpack_pool(dbg, bi, vn)
+            assert np.array_equal(coords, r_dbg[bi]["coords"].cpu().numpy()), case
+            assert np.array_equal(_bits(dbg["hyp"][bi]), _bits(r_dbg[bi]["hyp"])), case
+            assert np.array_equal(dbg["counts"][bi].cpu().numpy(), r_dbg[bi]["counts"].cpu().numpy()), (case, thresh)
+            assert np.array_equal(dbg["win_idx"][bi].cpu().numpy(), r_dbg[bi]["win_idx"].cpu().numpy()), case
+            assert np.array_equal(inl, r_dbg[bi]["inlier"].cpu().numpy()), case
+            checked += 1
+    assert checked >= 20
