@@ -513,9 +513,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                     if (!(fabsf(fminf(ep0, em0)) > hl.z)) inband |= 1u << (2 * u);
                     if (!(fabsf(fminf(ep1, em1)) > hl.z)) inband |= 2u << (2 * u);
                 }
-                while (inband) {  // padded pixels have m = -1e30 and never get here
+                while (inband) {
                     const int j = grp * K3_GROUP + 2 * u0 + __ffs(inband) - 1;
                     inband &= inband - 1;
+                    if (j >= n) continue;  // padded pixels (m = -1e30) only get here when T is infinite
                     const int q = atomicAdd(&s_q2n, 1);
                     if (q < K3_QCAP) s_q2[q] = ((uint32_t)j << 16) | ((uint32_t)k << 8) | (uint32_t)t;
                     else resolve(hbase, t, k, j, k3_m(hl.x, hl.y, k3_load_px(sP, j)));
@@ -538,6 +539,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
     }
     if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
 }
+
+#include "pvv_vote_tc.cuh"
 }  // namespace
 
 cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out,
@@ -551,7 +554,7 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
 
 // Guard-band constants for threshold t (DESIGN.md "Guard band").  Returns false when the fast filter does
 // not apply (t outside [0.5, 0.99999]): the caller then runs the exact-only kernel.
-static bool pvv_band_for(float t, band_consts *bc)
+static bool pvv_band_for(float t, band_consts *bc, float *krel_tc)
 {
     if (!(t >= 0.5f && t <= 0.99999f)) return false;
     const double u = 5.9604644775390625e-8;  // 2^-24
@@ -567,6 +570,12 @@ static bool pvv_band_for(float t, band_consts *bc)
     const double kabs = 12.0 * u * (1.0 + tau) * (1.0 + etau);     // rounding of the filter's a and c' (<= 6.5u(1+tau)m)
     bc->tau = (float)tau;
     bc->krel = (float)((erel + kabs) * (1.0 + 4.0 * u));
+    // tensor-pipe filter (pvv_vote_tc.cuh): 3xTF32 split products.  Per product the dropped lo*lo term (4u) and the two
+    // split tails (2u each), the split tail of r (2u), an 8-term accumulation taken as one truncation (2u) per term on
+    // the running maximum (16u), plus the 4.5u of input / constant rounding shared with the FP32 filter: <= 31u(1+tau)M.
+    // Measured on the B200 (tools/tc_probe.cu): 5.5u against the fp32 constants.  Used: 40u.
+    const double kabs_tc = 40.0 * u * (1.0 + tau) * (1.0 + etau);
+    *krel_tc = (float)((erel + kabs_tc) * (1.0 + 4.0 * u));
     bc->abs_floor = (float)(4e-6 * (1.0 + tau));
     bc->ablate = 0;
 #ifdef PVV_K3_ABLATE
@@ -585,13 +594,33 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
     return cudaGetLastError();
 }
 
+// tensor-pipe variant: 2 CTAs per SM (2 x 256 of the SM's 512 TMEM columns), dynamic shared memory, PDL like the rest
+static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, float krel_tc, int sms,
+                                   cudaStream_t st)
+{
+    cudaError_t e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(sms * 2);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = sizeof(tc_smem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, k_count_tc, d, ws, bc, krel_tc);
+}
+
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches)
 {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {0.f, 0.f, 0.f};
-    const bool fast = !force_exact && pvv_band_for(d.thresh, &bc);
+    float krel_tc = 0.f;
+    const bool fast = !force_exact && pvv_band_for(d.thresh, &bc, &krel_tc);
     // CTA shape by hypothesis count: every thread owns 4 hypotheses, one pass covers 4 * THREADS of them
     // (PVV_K3_VARIANT overrides the choice: a tuning knob for tools/k3_variants.py)
     const char *venv = getenv("PVV_K3_VARIANT");
@@ -603,6 +632,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         pvv_launch_pdl(k_count_exact<4, 128>, dim3(sms * (per_sm < 1 ? 1 : per_sm)), dim3(128), st, d, ws);
         e = cudaGetLastError();
     }
+    else if (variant == 7) e = launch_count_tc(d, ws, bc, krel_tc, sms, st);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);
