@@ -46,7 +46,7 @@ long long default_cap(const pvv_job *j)
 
 struct layout {
     size_t zero_bytes, total_bytes;
-    size_t o_counters, o_img_fg, o_counts, o_ticket, o_part, o_flags, o_tn, o_img_off, o_chunk, o_ctab, o_tile_cnt, o_tile_off, o_bits, o_xy, o_dir, o_hyp;
+    size_t o_counters, o_img_fg, o_counts, o_ticket, o_part, o_flags, o_tn, o_img_off, o_chunk, o_ctab, o_tile_cnt, o_tile_off, o_bits, o_xy, o_dir, o_pq, o_hyp;
     long long cap;
     int ntiles, hn_pad;
 };
@@ -75,6 +75,7 @@ layout make_layout(const pvv_job *j)
     L.o_xy = take(sizeof(uint32_t) * (size_t)L.cap);
     L.o_dir = take(sizeof(float2) * (size_t)L.cap * j->vn);
     L.o_hyp = take(sizeof(float2) * (size_t)j->b * j->vn * L.hn_pad);
+    L.o_pq = take(sizeof(float4) * (size_t)L.cap * j->vn);
     L.o_part = take(sizeof(double) * (size_t)j->b * j->vn * PVV_FIN_SPLIT * 5);
     L.total_bytes = o;
     return L;
@@ -98,6 +99,7 @@ pvv_ws carve(const layout &L, void *base)
     ws.pix_xy = (uint32_t *)(p + L.o_xy);
     ws.pix_dir = (float2 *)(p + L.o_dir);
     ws.hyp = (float2 *)(p + L.o_hyp);
+    ws.pix_pq = (float4 *)(p + L.o_pq);
     ws.fin_ticket = (unsigned *)(p + L.o_ticket);
     ws.fin_part = (double *)(p + L.o_part);
     ws.idxs_used = nullptr;

@@ -22,6 +22,7 @@ struct pvv_ws {
                                   //                 subsampling: the mask itself is read exactly once
     uint32_t *pix_xy;             // [cap]      x | y<<16
     float2 *pix_dir;              // [vn][cap]  raw direction vectors (SoA over keypoints)
+    float4 *pix_pq;               // [vn][cap]  frame-independent half-plane constants (tensor-pipe K3 only; k_pixel_consts)
     float2 *hyp;                  // [b][vn][hn] hypotheses
     double *fin_part;             // [b][vn][PVV_FIN_SPLIT][5] partial normal equations of the K4 splits
     int32_t *idxs_used;           // optional debug [b][hn][vn][2]

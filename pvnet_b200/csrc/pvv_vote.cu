@@ -594,14 +594,20 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
     return cudaGetLastError();
 }
 
-// tensor-pipe variant: 2 CTAs per SM (2 x 256 of the SM's 512 TMEM columns), dynamic shared memory, PDL like the rest
+// tensor-pipe variant: the per-pixel constants pre-pass, then one 768-thread CTA per SM (all 512 TMEM columns), dynamic
+// shared memory, both chained by PDL like the rest
 static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, float krel_tc, int sms,
-                                   cudaStream_t st)
+                                   cudaStream_t st, int *launches)
 {
-    cudaError_t e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
+    const long long pblocks = (ws.cap + 255) / 256;  // grid-stride: the pixel count is only known on the device
+    const dim3 pgrid((unsigned)(pblocks < 2 * sms ? pblocks : 2 * sms), (unsigned)d.vn);
+    cudaError_t e = pvv_launch_pdl(k_pixel_consts, pgrid, dim3(256), st, d, ws, bc.tau);
+    if (e != cudaSuccess) return e;
+    ++*launches;
+    e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(sms * 2);
+    cfg.gridDim = dim3(sms);
     cfg.blockDim = dim3(TC_THREADS);
     cfg.dynamicSmemBytes = sizeof(tc_smem);
     cfg.stream = st;
@@ -632,7 +638,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         pvv_launch_pdl(k_count_exact<4, 128>, dim3(sms * (per_sm < 1 ? 1 : per_sm)), dim3(128), st, d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 7) e = launch_count_tc(d, ws, bc, krel_tc, sms, st);
+    else if (variant == 7) e = launch_count_tc(d, ws, bc, krel_tc, sms, st, launches);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);

@@ -32,28 +32,47 @@
 #define K3_ABLV 0
 #endif
 
-constexpr int TC_VOTERS = 256;              // voting threads (8 warps)
-constexpr int TC_THREADS = TC_VOTERS + 32;  // + the MMA warp
-constexpr int TC_PASS_H = 512;              // hypotheses per pass (4 M-blocks of 128)
-constexpr int TC_TILE_PX = 64;              // pixels per MMA tile (N = 128 columns)
-constexpr int TC_TMEM_COLS = 256;           // two accumulator buffers of 128 columns
+constexpr int TC_VOTER_WARPS = 16;                 // voting warps: 4 TMEM lane quarters x 4 column quarters of a tile
+constexpr int TC_VOTERS = TC_VOTER_WARPS * 32;
+constexpr int TC_MMA_WARP = TC_VOTER_WARPS;        // one elected thread issues every tcgen05.mma
+constexpr int TC_PROD_WARPS = 3;                   // producer warps: operands of the next unit, deferred passes of the previous
+constexpr int TC_PRODS = TC_PROD_WARPS * 32;
+constexpr int TC_THREADS = TC_VOTERS + 32 + TC_PRODS;   // 640 = 5 warpgroups
+constexpr int TC_STAGES = 3;                       // unit k lives in stage k % 3: produced | voted on | deferred passes
+constexpr int TC_PASS_H = 512;                     // hypotheses per unit (4 M-blocks of 128)
+constexpr int TC_TILE_PX = 128;                    // pixels per MMA tile (N = 256 columns)
+constexpr int TC_TMEM_COLS = 512;                  // two accumulator buffers of 256 columns: the whole TMEM of the SM
+constexpr int TC_REGS_VOTER = 104, TC_REGS_OTHER = 64;  // setmaxnreg: 512 x 104 + 128 x 64 = 61440 = the launch allocation (640 x 96)
 constexpr long long TC_SPIN_CYCLES = 4000000000ll;  // ~2 s
 
-struct tc_smem {
+// One unit of work = (256-pixel chunk, keypoint, pass of <= 512 hypotheses).
+struct tc_stage {
     uint4 A[2][TC_PASS_H];            // hypotheses, [K half][row]: 16 KB
     uint4 B[2][2 * PVV_CHUNK_PX];     // pixels x {+,-}, [K half][row = 2*pixel + plane]: 16 KB
     float4 H[TC_PASS_H];              // local hypotheses {hx, hy, T of the FP32 filter, T of the tensor-pipe filter}
     float P[K3_SP_FLOATS];            // FP32 constants in the FP32 kernel's pair layout (phase A)
-    float2 dir[2][PVV_CHUNK_PX];      // raw pixels, double-buffered
-    uint32_t xy[2][PVV_CHUNK_PX];
-    uint32_t q[K3_QCAP];              // phase A entries: (group << 16) | hypothesis within the pass
+    uint32_t q[K3_QCAP];              // flagged entries: (group << 16) | hypothesis within the pass
+    long long row, pix;               // offset of the (image, keypoint) row in hyp / counts; of the first pixel in the pool
+    int qn, stop, mbn, nbn, n, hbase, vi, pad;
+};
+struct tc_inputs {                    // raw inputs of one unit, staged by cp.async one iteration ahead
+    float4 pq[PVV_CHUNK_PX];
+    float2 hyp[TC_PASS_H];
+    uint32_t xy[PVV_CHUNK_PX];
+};
+struct tc_smem {
+    tc_stage st[TC_STAGES];
+    tc_inputs in[2];
     uint32_t q2[K3_QCAP];             // phase B entries: (pixel << 16) | hypothesis within the pass
-    unsigned long long bar_full[2], bar_empty[2], bar_ab;
+    unsigned long long bar_ab[TC_STAGES], bar_done[TC_STAGES], bar_full[2], bar_empty[2];
     uint32_t tmem;
-    int ctl_mb, ctl_nb, ctl_stop;
-    int id[2], ext[2], qn, q2n;
+    int ext, q2n;
 };
 
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
 __device__ __forceinline__ uint32_t tc_saddr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void tc_bar_init(unsigned long long *b, int count)
 {
@@ -71,11 +90,13 @@ __device__ __forceinline__ uint32_t tc_bar_try(uint32_t bar_saddr, uint32_t pari
                  : "=r"(done) : "r"(bar_saddr), "r"(parity) : "memory");
     return done;
 }
-__device__ __noinline__ void tc_bar_wait_slow(uint32_t bar_saddr, uint32_t parity)
+__device__ __forceinline__ void tc_bar_wait_slow(uint32_t bar_saddr, uint32_t parity)
 {
     const long long t0 = clock64();
-    while (!tc_bar_try(bar_saddr, parity))
+    while (!tc_bar_try(bar_saddr, parity)) {
+        __nanosleep(64);  // a waiting warp must not eat the issue slots of the voting warps
         if (clock64() - t0 > TC_SPIN_CYCLES) __trap();
+    }
 }
 __device__ __forceinline__ void tc_bar_wait(uint32_t bar_saddr, uint32_t parity)
 {
@@ -136,7 +157,7 @@ __device__ __forceinline__ void tc_group(const uint32_t (&v)[32], float T, int &
     dmask |= flagged ? bit : 0u;
 }
 
-// One 128-column tile of this thread's hypothesis row: wait for the accumulator, pull this warp's 64 columns into
+// One 256-column tile of this thread's hypothesis row: wait for the accumulator, pull this warp's 64 columns into
 // registers, hand the TMEM buffer back, then vote on the two 16-pixel groups.
 __device__ __forceinline__ void tc_tile(uint32_t a_full, uint32_t a_empty, uint32_t tmem_row, uint32_t &t, int lane, float T,
                                         int &neg, uint32_t &dm, uint32_t bit, int abl = 0)
@@ -146,8 +167,8 @@ __device__ __forceinline__ void tc_tile(uint32_t a_full, uint32_t a_empty, uint3
     ++t;
     tc_fence_after();
     uint32_t v0[32], v1[32];
-    tc_ld32(tmem_row + tb * 128u, v0);
-    tc_ld32(tmem_row + tb * 128u + 32u, v1);
+    tc_ld32(tmem_row + tb * 256u, v0);
+    tc_ld32(tmem_row + tb * 256u + 32u, v1);
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");  // warp-collective: every lane's columns have landed
     tc_fence_before();
     if (lane == 0 && !(abl & 32)) tc_bar_arrive(a_empty + 8u * tb);  // the accumulator is in registers: buffer free for the next MMA
@@ -156,25 +177,47 @@ __device__ __forceinline__ void tc_tile(uint32_t a_full, uint32_t a_empty, uint3
     tc_group(v1, T, neg, dm, bit << 1);
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 2) k_count_tc(pvv_dims d, pvv_ws ws, band_consts bc, float krel_tc)
+// Pre-pass (one thread per (keypoint, pooled pixel)): the four frame-independent constants of the two half-planes,
+// each correctly rounded from fp64:  {nx - tau ny, ny + tau nx, nx + tau ny, ny - tau nx}.  All-zero marks a pixel the
+// reference never counts (||n|| < 1e-6, or a non-finite norm).
+__global__ void __launch_bounds__(256) k_pixel_consts(pvv_dims d, pvv_ws ws, float tau_f)
+{
+    pvv_pdl_enter();
+    const long long total = ws.img_off[d.b - 1] + ws.tn[d.b - 1];
+    const float2 *dirs = ws.pix_dir + (long long)blockIdx.y * ws.cap;
+    float4 *out = ws.pix_pq + (long long)blockIdx.y * ws.cap;
+    const double tau = (double)tau_f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const float2 dir = dirs[i];
+        const float n1 = pvv_norm1(dir.x, dir.y);
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        if ((double)n1 >= 1e-6 && n1 < 3.0e38f) {
+            const double inv = rsqrt((double)dir.x * dir.x + (double)dir.y * dir.y);
+            const double nx = dir.x * inv, ny = dir.y * inv;
+            c = make_float4((float)(nx - tau * ny), (float)(ny + tau * nx), (float)(nx + tau * ny), (float)(ny - tau * nx));
+        }
+        out[i] = c;
+    }
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws ws, band_consts bc, float krel_tc)
 {
     extern __shared__ __align__(128) unsigned char tc_smem_raw[];
     tc_smem &S = *reinterpret_cast<tc_smem *>(tc_smem_raw);
-    static_assert(K3_GROUP == 16 && PVV_CHUNK_PX == 256 && TC_TILE_PX == 64 && TC_VOTERS == PVV_CHUNK_PX, "tile / group geometry");
+    static_assert(K3_GROUP == 16 && PVV_CHUNK_PX == 256 && TC_TILE_PX == 128, "tile / group geometry");
 
     pvv_pdl_enter();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int total_items = ws.chunk_start[d.b] * d.vn;
 
     if (tid == 0) {
+        for (int i = 0; i < TC_STAGES; ++i) { tc_bar_init(&S.bar_ab[i], TC_PROD_WARPS); tc_bar_init(&S.bar_done[i], TC_VOTER_WARPS); }
         tc_bar_init(&S.bar_full[0], 1); tc_bar_init(&S.bar_full[1], 1);
-        tc_bar_init(&S.bar_empty[0], TC_VOTERS / 32); tc_bar_init(&S.bar_empty[1], TC_VOTERS / 32);
-        tc_bar_init(&S.bar_ab, 1);
+        tc_bar_init(&S.bar_empty[0], TC_VOTER_WARPS); tc_bar_init(&S.bar_empty[1], TC_VOTER_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        S.id[0] = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u);
-        S.ext[0] = 0; S.ext[1] = 0; S.qn = 0; S.q2n = 0; S.ctl_stop = 0;
+        S.ext = 0; S.q2n = 0;
     }
-    if (warp == TC_VOTERS / 32) {  // the MMA warp owns the TMEM allocation
+    if (warp == TC_MMA_WARP) {  // the MMA warp owns the TMEM allocation
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_saddr(&S.tmem)), "r"(TC_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
@@ -183,260 +226,329 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_count_tc(pvv_dims d, pvv_ws w
     tc_fence_after();
     const uint32_t tmem = S.tmem;
 
-    if (warp == TC_VOTERS / 32) {
-        // ================= MMA issuer: one thread =================
-        if (lane == 0) {
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((128u >> 4) << 24);
-            uint32_t t = 0, ab_parity = 0;
-            while (true) {
-                tc_bar_wait(&S.bar_ab, ab_parity);
-                ab_parity ^= 1u;
-                if (*(volatile int *)&S.ctl_stop) break;
-                const int mbn = *(volatile int *)&S.ctl_mb, nbn = *(volatile int *)&S.ctl_nb;
+    if (warp < TC_VOTER_WARPS) {
+        // ================= voting warps: TMEM -> registers -> counts, nothing else =================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TC_REGS_VOTER));
+        const int q4 = warp & 3;   // TMEM lane quarter = rows 32*q4 .. +31 of the M-block
+        const int cq = warp >> 2;  // column quarter of the tile: pixels 32*cq .. +31 of its 128
+        uint32_t a_full = tc_saddr(&S.bar_full[0]), a_empty = tc_saddr(&S.bar_empty[0]);
+        uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cq * 64);
+        // opaque to the compiler: kept in registers instead of being rematerialised from tid / the shared window base
+        asm volatile("" : "+r"(a_full), "+r"(a_empty), "+r"(tmem_row));
+        uint32_t t = 0;  // tile counter, in lock-step with the MMA issuer's
+        for (uint32_t k = 0;; ++k) {
+            const uint32_t s = k % TC_STAGES;
+            tc_stage &T = S.st[s];
+            tc_bar_wait(&S.bar_ab[s], (k / TC_STAGES) & 1u);
+            if (T.stop) break;
+            const int mbn = T.mbn, nbn = T.nbn, hbase = T.hbase;
+            const long long row = T.row;
+            uint32_t dmask = 0u;  // bit mb*4 + nb*2 + g: flagged 16-pixel group of this thread's hypothesis in M-block mb
+            // Software pipeline over the 16-pixel groups of the unit: the tcgen05.ld of group g+1 is in flight while
+            // group g is voted on (tcgen05.wait::ld waits for every outstanding load, so each wait follows the vote).
+            const int abl = K3_ABLV;
+            uint32_t v0[32], v1[32];
+            auto full_wait = [&](uint32_t tt) {
+                if (!(abl & 32)) tc_bar_wait(a_full + 8u * (tt & 1u), (tt >> 1) & 1u);
                 tc_fence_after();
-                for (int mb = 0; mb < mbn && !K3_ABL(32); ++mb) {
-                    const uint64_t da = tc_desc(tc_saddr(&S.A[0][mb * 128]), sizeof(S.A[0]), 128);
-                    for (int nb = 0; nb < nbn; ++nb, ++t) {
-                        const uint32_t buf = t & 1u;
-                        if (t >= 2) tc_bar_wait(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
-                        tc_fence_after();
-                        const uint64_t db = tc_desc(tc_saddr(&S.B[0][nb * 128]), sizeof(S.B[0]), 128);
-                        asm volatile(
-                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * 128u),
-                            "l"(da), "l"(db), "r"(idesc), "r"(0));
-                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                         tc_saddr(&S.bar_full[buf])) : "memory");
+            };
+            auto landed = [&] { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); };
+            auto release = [&](uint32_t tt) {  // both groups of tile tt are in registers: its TMEM buffer is free
+                tc_fence_before();
+                if (lane == 0 && !(abl & 32)) tc_bar_arrive(a_empty + 8u * (tt & 1u));
+            };
+            auto vote = [&](const uint32_t (&v)[32], float Tt, int &neg, uint32_t &dm, uint32_t bit) {
+                if (abl & 16) neg += v[0] ^ v[31]; else tc_group(v, Tt, neg, dm, bit);
+            };
+            full_wait(t);
+            tc_ld32(tmem_row + (t & 1u) * 256u, v0);
+            landed();
+            for (int mb = 0; mb < mbn; ++mb) {
+                const int hl = mb * 128 + q4 * 32 + lane;
+                const float Tt = T.H[hl].w;
+                int neg = 0;
+                uint32_t dm = 0u;
+                tc_ld32(tmem_row + (t & 1u) * 256u + 32u, v1);
+                vote(v0, Tt, neg, dm, 1u);
+                landed();
+                release(t);
+                if (nbn == 2) {  // full chunk (the common case)
+                    full_wait(t + 1);
+                    tc_ld32(tmem_row + ((t + 1) & 1u) * 256u, v0);
+                    vote(v1, Tt, neg, dm, 2u);
+                    landed();
+                    tc_ld32(tmem_row + ((t + 1) & 1u) * 256u + 32u, v1);
+                    vote(v0, Tt, neg, dm, 4u);
+                    landed();
+                    release(t + 1);
+                    t += 2;
+                    if (mb + 1 < mbn) {
+                        full_wait(t);
+                        tc_ld32(tmem_row + (t & 1u) * 256u, v0);
                     }
+                    vote(v1, Tt, neg, dm, 8u);
+                    landed();
+                } else {
+                    t += 1;
+                    if (mb + 1 < mbn) {
+                        full_wait(t);
+                        tc_ld32(tmem_row + (t & 1u) * 256u, v0);
+                    }
+                    vote(v1, Tt, neg, dm, 2u);
+                    landed();
+                }
+                const int cnt = K3_GROUP * (2 * nbn - __popc(dm)) - sign_lanes_total(neg);
+                if (hbase + hl < d.hn) {
+                    if (cnt) atomicAdd(&ws.counts[row + hbase + hl], cnt);
+                    dmask |= dm << (mb * 4);
                 }
             }
-        }
-        __syncwarp();
-    } else {
-        // ================= voting warps =================
-        const int q4 = warp & 3;     // TMEM lane quarter = rows 32*q4 .. +31 of the M-block
-        const int chalf = warp >> 2; // column half of the tile: pixels 32*chalf .. +31 of its 64
-        unsigned long long amb_local = 0;
-        const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};
-        uint32_t t = 0;  // tile counter, in lock-step with the MMA issuer's
-        const uint32_t a_full = tc_saddr(&S.bar_full[0]), a_empty = tc_saddr(&S.bar_empty[0]);
-        const uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(chalf * 64);
-
-        auto prefetch = [&](const k3_item &it, int buf) {
-            if (tid < it.n) {  // it.n <= PVV_CHUNK_PX = TC_VOTERS
-                cp_async4(&S.xy[buf][tid], ws.pix_xy + it.off + it.p0 + tid);
-                cp_async8(&S.dir[buf][tid], ws.pix_dir + (long long)it.vi * ws.cap + it.off + it.p0 + tid);
+            // queue the flagged (hypothesis, group) pairs for the producers' deferred passes: one reservation per warp
+            if (K3_ABL(1)) dmask = 0u;
+            const int mine = __popc(dmask);
+            if (__any_sync(0xffffffffu, mine)) {
+                int incl = mine;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int up = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += up;
+                }
+                int base = 0;
+                if (lane == 31) base = atomicAdd(&T.qn, incl);
+                int q = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
+                while (dmask) {
+                    const int bitn = __ffs(dmask) - 1;
+                    dmask &= dmask - 1;
+                    const int hl = (bitn >> 2) * 128 + q4 * 32 + lane;
+                    const int grp = ((bitn >> 1) & 1) * 8 + cq * 2 + (bitn & 1);  // 16-pixel group within the chunk
+                    if (q < K3_QCAP) {
+                        T.q[q] = ((uint32_t)grp << 16) | (uint32_t)hl;
+                    } else {  // queue full (pathological inputs): the reference's own decision for the whole group, in line
+                        const float2 hv = ws.hyp[row + hbase + hl];
+                        int c = 0;
+                        for (int j = grp * K3_GROUP; j < min(T.n, (grp + 1) * K3_GROUP); ++j) {
+                            const float2 dir = ws.pix_dir[(long long)T.vi * ws.cap + T.pix + j];
+                            const uint32_t xy = ws.pix_xy[T.pix + j];
+                            c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
+                                                hv.x, hv.y, d.thresh) ? 1 : 0;
+                        }
+                        if (c) atomicAdd(&ws.counts[row + hbase + hl], c);
+                    }
+                    ++q;
+                }
             }
-            cp_async_commit();
-        };
-
-        int item = S.id[0];
-        if (item < total_items) {
-            k3_item it = k3_decode_item(d, ws, item);
-            prefetch(it, 0);
-            if (tid == 0) S.id[1] = (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u);
-
-            for (int buf = 0;; buf ^= 1) {
-                cp_async_wait_all();
-                tc_voters_sync();  // raw pixels landed; S.id[buf ^ 1] visible; the previous item's shared memory is consumed
-                const int next = S.id[buf ^ 1];
-                const int n = it.n, ox = it.ox, oy = it.oy;
-                const float2 *rDir = S.dir[buf];
-                const uint32_t *rXY = S.xy[buf];
-                const int nbn = (n + TC_TILE_PX - 1) / TC_TILE_PX;
-
-                // ---- pixel constants: FP32 (phase A) and their TF32 split as B rows ----
-                int ext = 0;
-                if (tid < nbn * TC_TILE_PX) {
-                    const int j = tid;
-                    px_consts c = never;
-                    if (j < n && !K3_ABL(4)) {
-                        const uint32_t xy = rXY[j];
-                        const float2 dir = rDir[j];
-                        const float n1 = pvv_norm1(dir.x, dir.y);
-                        if ((double)n1 >= 1e-6 && n1 < 3.0e38f) {
-                            const double inv = rsqrt((double)dir.x * dir.x + (double)dir.y * dir.y);
-                            const double nx = dir.x * inv, ny = dir.y * inv, tau = (double)bc.tau;
-                            const int ix = (int)(xy & 0xffffu) - ox, iy = (int)(xy >> 16) - oy;
-                            c.px = (float)(nx - tau * ny);
-                            c.py = (float)(ny + tau * nx);
-                            c.qx = (float)(nx + tau * ny);
-                            c.qy = (float)(ny - tau * nx);
-                            c.pz = (float)(-((double)ix * c.px + (double)iy * c.py));
-                            c.qz = (float)(-((double)ix * c.qx + (double)iy * c.qy));
-                            ext = abs(ix) + abs(iy);
+            __syncwarp();
+            if (lane == 0) tc_bar_arrive(&S.bar_done[s]);
+        }
+    } else {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TC_REGS_OTHER));
+        if (warp == TC_MMA_WARP) {
+            // ================= MMA issuer: one thread =================
+            if (lane == 0) {
+                const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(256 >> 3) << 17) | ((128u >> 4) << 24);
+                uint32_t t = 0;
+                for (uint32_t k = 0;; ++k) {
+                    const uint32_t s = k % TC_STAGES;
+                    tc_stage &T = S.st[s];
+                    tc_bar_wait(&S.bar_ab[s], (k / TC_STAGES) & 1u);
+                    if (T.stop) break;
+                    const int mbn = T.mbn, nbn = T.nbn;
+                    tc_fence_after();
+                    for (int mb = 0; mb < mbn && !K3_ABL(32); ++mb) {
+                        const uint64_t da = tc_desc(tc_saddr(&T.A[0][mb * 128]), sizeof(T.A[0]), 128);
+                        for (int nb = 0; nb < nbn; ++nb, ++t) {
+                            const uint32_t buf = t & 1u;
+                            if (t >= 2) tc_bar_wait(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
+                            tc_fence_after();
+                            const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * 256]), sizeof(T.B[0]), 128);
+                            asm volatile(
+                                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * 256u),
+                                "l"(da), "l"(db), "r"(idesc), "r"(0));
+                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                             tc_saddr(&S.bar_full[buf])) : "memory");
                         }
                     }
-                    k3_store_px(S.P, j, c);
-                    uint32_t ph, pl, qh, ql, rh, rl;
-                    tc_split(c.px, ph, pl); tc_split(c.py, qh, ql); tc_split(c.pz, rh, rl);
-                    S.B[0][2 * j] = make_uint4(ph, pl, ph, qh);
-                    S.B[1][2 * j] = make_uint4(ql, qh, rh, rl);
-                    tc_split(c.qx, ph, pl); tc_split(c.qy, qh, ql); tc_split(c.qz, rh, rl);
-                    S.B[0][2 * j + 1] = make_uint4(ph, pl, ph, qh);
-                    S.B[1][2 * j + 1] = make_uint4(ql, qh, rh, rl);
                 }
-                ext = __reduce_max_sync(0xffffffffu, ext);
-                if (lane == 0 && ext) atomicMax(&S.ext[buf], ext);
-                // ---- prefetch the next item's raw pixels and the id of the one after it ----
-                k3_item nit = it;
-                if (next < total_items) {
-                    nit = k3_decode_item(d, ws, next);
-                    prefetch(nit, buf ^ 1);
-                }
-                if (tid == 0) {
-                    S.id[buf] = next < total_items ? (int)atomicAdd(&ws.counters[PVV_CTR_WORK], 1u) : next;
-                    S.ext[buf ^ 1] = 0;
-                }
-                tc_voters_sync();  // constants and S.ext complete
-                const float P = (float)S.ext[buf];
-                const long long row = ((long long)it.img * d.vn + it.vi) * ws.hn_pad;
+            }
+            __syncwarp();
+        } else {
+            // ================= producers: operands of unit k, then the deferred passes of unit k - 2 =================
+            const int ptid = tid - (TC_VOTERS + 32);
+            auto pbar = [] { asm volatile("bar.sync 1, %0;" ::"n"(TC_PRODS) : "memory"); };
+            unsigned long long amb_local = 0;
+            const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};
 
-                auto resolve = [&](int h, int j) {  // the reference's own decision for one test
-                    const float2 hv = ws.hyp[row + h];
-                    const float2 dir = rDir[j];
-                    const uint32_t xy = rXY[j];
-                    if (pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16), hv.x,
-                                       hv.y, d.thresh))
-                        atomicAdd(&ws.counts[row + h], 1);
-                    ++amb_local;
-                };
-                // phase A body for one (hypothesis, group): FP32 filter on its 16 pixels; in-band tests go to phase B
-                auto refilter = [&](int hbase, int hl, int grp, int u0, int pairs) {
-                    const float4 hh = S.H[hl];
+            auto resolve = [&](const tc_stage &T, int hl, int j) {  // the reference's own decision for one test
+                const float2 hv = ws.hyp[T.row + T.hbase + hl];
+                const float2 dir = ws.pix_dir[(long long)T.vi * ws.cap + T.pix + j];
+                const uint32_t xy = ws.pix_xy[T.pix + j];
+                if (pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16), hv.x, hv.y,
+                                   d.thresh))
+                    atomicAdd(&ws.counts[T.row + T.hbase + hl], 1);
+                ++amb_local;
+            };
+            // deferred passes of one unit: (A) the FP32 filter re-decides every test of a flagged (hypothesis, group) --
+            // the tensor-pipe result is not used inside its band at all; (B) tests inside the FP32 filter's own band get
+            // the reference's exact rounding sequence
+            auto deferred = [&](uint32_t u) {
+                const uint32_t s = u % TC_STAGES;
+                tc_stage &T = S.st[s];
+                tc_bar_wait(&S.bar_done[s], (u / TC_STAGES) & 1u);
+                const int qtot = min(T.qn, K3_QCAP) * K3_SUB;
+                for (int idx = ptid; idx < qtot; idx += TC_PRODS) {
+                    const uint32_t ent = T.q[idx / K3_SUB];
+                    constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
+                    const int hl = (int)(ent & 0xffffu), grp = (int)(ent >> 16), u0 = (idx % K3_SUB) * PAIRS;
+                    const float4 hh = T.H[hl];
                     const f32x2 hxx = pk(hh.x, hh.x), hyy = pk(hh.y, hh.y);
-                    const ulonglong2 *pg = reinterpret_cast<const ulonglong2 *>(S.P) + grp * K3_GSTRIDE + 3 * u0;
+                    const ulonglong2 *pg = reinterpret_cast<const ulonglong2 *>(T.P) + grp * K3_GSTRIDE + 3 * u0;
                     int sure = 0;
                     uint32_t inband = 0u;
-                    for (int u = 0; u < pairs; ++u) {
-                        const ulonglong2 v0 = pg[3 * u], v1 = pg[3 * u + 1], v2 = pg[3 * u + 2];
+#pragma unroll
+                    for (int p = 0; p < PAIRS; ++p) {
+                        const ulonglong2 v0 = pg[3 * p], v1 = pg[3 * p + 1], v2 = pg[3 * p + 2];
                         float ep0, ep1, em0, em1;
                         unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
                         unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
                         const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
-                        if (!(fabsf(m0) > hh.z)) inband |= 1u << (2 * u); else sure += m0 > 0.f;
-                        if (!(fabsf(m1) > hh.z)) inband |= 2u << (2 * u); else sure += m1 > 0.f;
+                        if (!(fabsf(m0) > hh.z)) inband |= 1u << (2 * p); else sure += m0 > 0.f;
+                        if (!(fabsf(m1) > hh.z)) inband |= 2u << (2 * p); else sure += m1 > 0.f;
                     }
-                    if (sure) atomicAdd(&ws.counts[row + hbase + hl], sure);
+                    if (sure) atomicAdd(&ws.counts[T.row + T.hbase + hl], sure);
                     while (inband) {
                         const int j = grp * K3_GROUP + 2 * u0 + __ffs(inband) - 1;
                         inband &= inband - 1;
-                        if (j >= n) continue;  // padded pixels (m = -1e30) only get here when T is infinite
+                        if (j >= T.n) continue;  // padded pixels (m = -1e30) only get here when T is infinite
                         const int q = atomicAdd(&S.q2n, 1);
                         if (q < K3_QCAP) S.q2[q] = ((uint32_t)j << 16) | (uint32_t)hl;
-                        else resolve(hbase + hl, j);
-                    }
-                };
-
-                for (int hbase = 0; hbase < d.hn; hbase += TC_PASS_H) {
-                    const int mbn = min(TC_PASS_H / 128, (d.hn - hbase + 127) / 128);
-                    if (hbase > 0) tc_voters_sync();  // the previous pass's deferred entries (S.q2, S.H) are consumed
-                    if (tid == 0) S.q2n = 0;
-                    // ---- hypotheses of this pass in the chunk-local frame: A rows and band half-widths ----
-                    for (int hl = tid; hl < mbn * 128 && !K3_ABL(64); hl += TC_VOTERS) {
-                        const int h = hbase + hl;
-                        const float2 hv = h < d.hn ? ws.hyp[row + h] : make_float2(0.f, 0.f);
-                        float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy), Tf, Tt;
-                        const float mm = __fadd_rn(__fadd_rn(fabsf(hx), fabsf(hy)), P);
-                        if (mm < 1e15f) {
-                            Tf = __fmaf_rn(bc.krel, mm, bc.abs_floor);
-                            Tt = __fmaf_rn(krel_tc, mm, bc.abs_floor);
-                        } else {  // far-away / non-finite hypothesis: every test takes the exact path
-                            hx = 0.f; hy = 0.f; Tf = Tt = __int_as_float(0x7f800000);
-                        }
-                        S.H[hl] = make_float4(hx, hy, Tf, Tt);
-                        uint32_t xh, xl, yh, yl;
-                        tc_split(hx, xh, xl); tc_split(hy, yh, yl);
-                        S.A[0][hl] = make_uint4(xh, xh, xl, yh);
-                        S.A[1][hl] = make_uint4(yh, yl, 0x3f800000u, 0x3f800000u);
-                    }
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // operands visible to the tensor pipe
-                    tc_voters_sync();
-                    if (tid == 0) {
-                        S.ctl_mb = mbn; S.ctl_nb = nbn;
-                        __threadfence_block();
-                        tc_bar_arrive(&S.bar_ab);
-                    }
-                    // ---- hot loop: tiles out of TMEM ----
-                    uint32_t dmask = 0u;  // bit mb*8 + nb*2 + g: flagged 16-pixel group of this thread's hypothesis in M-block mb
-                    for (int mb = 0; mb < mbn; ++mb) {
-                        const int hl = mb * 128 + q4 * 32 + lane;
-                        const float T = S.H[hl].w;
-                        int neg = 0;
-                        uint32_t dm = 0u;
-                        if (nbn == PVV_CHUNK_PX / TC_TILE_PX) {  // full chunk (the common case): four tiles, unrolled
-                            tc_tile(a_full, a_empty, tmem_row, t, lane, T, neg, dm, 1u, K3_ABLV);
-                            tc_tile(a_full, a_empty, tmem_row, t, lane, T, neg, dm, 4u, K3_ABLV);
-                            tc_tile(a_full, a_empty, tmem_row, t, lane, T, neg, dm, 16u, K3_ABLV);
-                            tc_tile(a_full, a_empty, tmem_row, t, lane, T, neg, dm, 64u, K3_ABLV);
-                        } else {
-                            for (int nb = 0; nb < nbn; ++nb) tc_tile(a_full, a_empty, tmem_row, t, lane, T, neg, dm, 1u << (2 * nb), K3_ABLV);
-                        }
-                        dmask |= dm << (mb * 8);
-                        const int cnt = K3_GROUP * (2 * nbn - __popc(dm)) - sign_lanes_total(neg);
-                        if (hbase + hl < d.hn && cnt) atomicAdd(&ws.counts[row + hbase + hl], cnt);
-                    }
-                    // ---- queue the flagged (hypothesis, group) pairs: one shared-memory reservation per warp ----
-                    {
-                        uint32_t dm = K3_ABL(1) ? 0u : dmask;
-                        // hypotheses beyond hn own no counts
-#pragma unroll
-                        for (int mb = 0; mb < TC_PASS_H / 128; ++mb)
-                            if (hbase + mb * 128 + q4 * 32 + lane >= d.hn) dm &= ~(0xffu << (mb * 8));
-                        const int mine = __popc(dm);
-                        if (__any_sync(0xffffffffu, mine)) {
-                            int incl = mine;
-#pragma unroll
-                            for (int o = 1; o < 32; o <<= 1) {
-                                const int up = __shfl_up_sync(0xffffffffu, incl, o);
-                                if (lane >= o) incl += up;
-                            }
-                            int base = 0;
-                            if (lane == 31) base = atomicAdd(&S.qn, incl);
-                            int q = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
-                            while (dm) {
-                                const int bitn = __ffs(dm) - 1;
-                                dm &= dm - 1;
-                                const int hl = (bitn >> 3) * 128 + q4 * 32 + lane;
-                                const int grp = ((bitn >> 1) & 3) * 4 + chalf * 2 + (bitn & 1);  // 16-pixel group within the chunk
-                                if (q < K3_QCAP) S.q[q] = ((uint32_t)grp << 16) | (uint32_t)hl;
-                                else refilter(hbase, hl, grp, 0, K3_GROUP / 2);  // queue full (pathological inputs): in line
-                                ++q;
-                            }
-                        }
-                    }
-                    tc_voters_sync();
-                    // phase A: K3_SUB lanes per flagged entry
-                    const int qtot = min(S.qn, K3_QCAP) * K3_SUB;
-                    for (int idx = tid; idx < qtot; idx += TC_VOTERS) {
-                        const uint32_t ent = S.q[idx / K3_SUB];
-                        constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
-                        refilter(hbase, (int)(ent & 0xffffu), (int)(ent >> 16), (idx % K3_SUB) * PAIRS, PAIRS);
-                    }
-                    tc_voters_sync();
-                    if (tid == 0) S.qn = 0;
-                    // phase B: exact decisions for the tests inside the FP32 filter's band
-                    const int q2 = min(S.q2n, K3_QCAP);
-                    for (int idx = tid; idx < q2; idx += TC_VOTERS) {
-                        const uint32_t ent = S.q2[idx];
-                        resolve(hbase + (int)(ent & 0xffffu), (int)(ent >> 16));
+                        else resolve(T, hl, j);
                     }
                 }
-                if (next >= total_items) break;
-                item = next;
-                it = nit;
+                pbar();
+                const int q2 = min(S.q2n, K3_QCAP);
+                for (int idx = ptid; idx < q2; idx += TC_PRODS) {
+                    const uint32_t ent = S.q2[idx];
+                    resolve(T, (int)(ent & 0xffffu), (int)(ent >> 16));
+                }
+                pbar();
+                if (ptid == 0) S.q2n = 0;
+            };
+
+            // Units are dealt round-robin over the CTAs (item = blockIdx.x + i * gridDim.x; equal cost per item), so the
+            // producers know them arbitrarily far ahead and every global load is issued an iteration before its use:
+            //   iteration k:  chunk-table entry of unit k+3 | pool offset of unit k+2 | cp.async of the raw inputs of
+            //   unit k+1 into the other staging buffer | operands of unit k out of its staging buffer.
+            const int npass = (d.hn + TC_PASS_H - 1) / TC_PASS_H;
+            auto unit_item = [&](uint32_t u) { return (int)blockIdx.x + (int)(u / (uint32_t)npass) * (int)gridDim.x; };
+            auto load_entry = [&](uint32_t u) {
+                const int item = unit_item(u);
+                return item < total_items ? __ldg(&ws.chunk_tab[item / d.vn]) : make_int4(-1, 0, 0, 0);
+            };
+            auto stage_inputs = [&](uint32_t u, const int4 &e, long long off, int buf) {  // cp.async: pixels + hypotheses
+                if (e.x >= 0 && !K3_ABL(1024)) {
+                    const int vi = unit_item(u) % d.vn, hbase = (int)(u % (uint32_t)npass) * TC_PASS_H;
+                    const long long pix = off + e.y;
+                    for (int j = ptid; j < e.z; j += TC_PRODS) {
+                        cp_async16(&S.in[buf].pq[j], ws.pix_pq + (long long)vi * ws.cap + pix + j);
+                        cp_async4(&S.in[buf].xy[j], ws.pix_xy + pix + j);
+                    }
+                    const long long row = ((long long)e.x * d.vn + vi) * ws.hn_pad + hbase;
+                    const int hcount = min(TC_PASS_H, d.hn - hbase);
+                    for (int hl = ptid; hl < hcount; hl += TC_PRODS) cp_async8(&S.in[buf].hyp[hl], ws.hyp + row + hl);
+                }
+                cp_async_commit();
+            };
+            int4 e0 = load_entry(0), e1 = load_entry(1), e2 = load_entry(2);   // entries of units k, k+1, k+2
+            long long off0 = e0.x >= 0 ? __ldg(&ws.img_off[e0.x]) : 0, off1 = e1.x >= 0 ? __ldg(&ws.img_off[e1.x]) : 0;
+            stage_inputs(0, e0, off0, 0);
+            uint32_t k = 0;
+            for (;; ++k) {
+                const uint32_t s = k % TC_STAGES;
+                tc_stage &T = S.st[s];  // free: the deferred passes of unit k - 3 ended in the previous iteration
+                cp_async_wait_all();
+                pbar();  // unit k's inputs are staged; everything of the previous iteration is complete
+                if (e0.x < 0) {
+                    if (ptid == 0) T.stop = 1;
+                    __syncwarp();
+                    if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
+                    break;
+                }
+                const int4 e3 = load_entry(k + 3);
+                const long long off2 = e2.x >= 0 ? __ldg(&ws.img_off[e2.x]) : 0;
+                stage_inputs(k + 1, e1, off1, (int)((k + 1) & 1u));
+                const tc_inputs &I = S.in[k & 1u];
+                const int vi = unit_item(k) % d.vn, hbase = (int)(k % (uint32_t)npass) * TC_PASS_H;
+                const int n = e0.z, ox = (int)((uint32_t)e0.w & 0xffffu), oy = (int)((uint32_t)e0.w >> 16);
+                const int nbn = (n + TC_TILE_PX - 1) / TC_TILE_PX;
+                const int mbn = min(TC_PASS_H / 128, (d.hn - hbase + 127) / 128);
+                const long long pix = off0 + e0.y;
+                const long long row = ((long long)e0.x * d.vn + vi) * ws.hn_pad;
+                // ---- pixel constants in the chunk-local frame: FP32 (phase A) and their TF32 split as B rows ----
+                int ext = 0;
+                for (int j = ptid; j < nbn * TC_TILE_PX && !K3_ABL(256); j += TC_PRODS) {
+                    px_consts c = never;
+                    if (j < n && !K3_ABL(4)) {
+                        const float4 pq = I.pq[j];
+                        const uint32_t xy = I.xy[j];
+                        if (pq.x != 0.f || pq.y != 0.f) {
+                            const float fx = (float)((int)(xy & 0xffffu) - ox), fy = (float)((int)(xy >> 16) - oy);
+                            c.px = pq.x; c.py = pq.y; c.qx = pq.z; c.qy = pq.w;
+                            c.pz = -__fmaf_rn(fx, c.px, __fmul_rn(fy, c.py));
+                            c.qz = -__fmaf_rn(fx, c.qx, __fmul_rn(fy, c.qy));
+                            ext = max(ext, (int)(fabsf(fx) + fabsf(fy)));
+                        }
+                    }
+                    k3_store_px(T.P, j, c);
+                    uint32_t ph, pl, qh, ql, rh, rl;
+                    tc_split(c.px, ph, pl); tc_split(c.py, qh, ql); tc_split(c.pz, rh, rl);
+                    T.B[0][2 * j] = make_uint4(ph, pl, ph, qh);
+                    T.B[1][2 * j] = make_uint4(ql, qh, rh, rl);
+                    tc_split(c.qx, ph, pl); tc_split(c.qy, qh, ql); tc_split(c.qz, rh, rl);
+                    T.B[0][2 * j + 1] = make_uint4(ph, pl, ph, qh);
+                    T.B[1][2 * j + 1] = make_uint4(ql, qh, rh, rl);
+                }
+                ext = __reduce_max_sync(0xffffffffu, ext);
+                if (lane == 0 && ext) atomicMax(&S.ext, ext);
+                pbar();
+                const float P = (float)S.ext;
+                // ---- hypotheses of this pass in the chunk-local frame: A rows and band half-widths ----
+                for (int hl = ptid; hl < mbn * 128 && !K3_ABL(64); hl += TC_PRODS) {
+                    const float2 hv = hbase + hl < d.hn ? I.hyp[hl] : make_float2(0.f, 0.f);
+                    float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy), Tf, Tt;
+                    const float mm = __fadd_rn(__fadd_rn(fabsf(hx), fabsf(hy)), P);
+                    if (mm < 1e15f) {
+                        Tf = __fmaf_rn(bc.krel, mm, bc.abs_floor);
+                        Tt = __fmaf_rn(krel_tc, mm, bc.abs_floor);
+                    } else {  // far-away / non-finite hypothesis: every test takes the exact path
+                        hx = 0.f; hy = 0.f; Tf = Tt = __int_as_float(0x7f800000);
+                    }
+                    T.H[hl] = make_float4(hx, hy, Tf, Tt);
+                    uint32_t xh, xl, yh, yl;
+                    tc_split(hx, xh, xl); tc_split(hy, yh, yl);
+                    T.A[0][hl] = make_uint4(xh, xh, xl, yh);
+                    T.A[1][hl] = make_uint4(yh, yl, 0x3f800000u, 0x3f800000u);
+                }
+                if (ptid == 0) {
+                    T.stop = 0; T.mbn = mbn; T.nbn = nbn; T.n = n; T.hbase = hbase; T.vi = vi; T.row = row; T.pix = pix; T.qn = 0;
+                }
+                if (!K3_ABL(128)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // operands visible to the tensor pipe
+                pbar();  // every producer passed its reads of S.ext; thread 0's header is written
+                if (ptid == 0) S.ext = 0;
+                if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
+                // ---- deferred passes of the unit the voters finished last ----
+                if (k >= 2 && !K3_ABL(512)) deferred(k - 2);
+                e0 = e1; e1 = e2; e2 = e3; off0 = off1; off1 = off2;
             }
-        }
-        if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
-        tc_voters_sync();
-        if (tid == 0) {
-            S.ctl_stop = 1;
-            __threadfence_block();
-            tc_bar_arrive(&S.bar_ab);
+            // k units were published (0 .. k-1): finish the deferred passes of the last two
+            if (k >= 2) deferred(k - 2);
+            pbar();
+            if (k >= 1) deferred(k - 1);
+            if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == TC_VOTERS / 32)
+    if (warp == TC_MMA_WARP)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_TMEM_COLS));
 }
