@@ -35,36 +35,50 @@
 constexpr int TC_VOTER_WARPS = 16;                 // voting warps: 4 TMEM lane quarters x 4 column quarters of a tile
 constexpr int TC_VOTERS = TC_VOTER_WARPS * 32;
 constexpr int TC_MMA_WARP = TC_VOTER_WARPS;        // one elected thread issues every tcgen05.mma
-constexpr int TC_PROD_WARPS = 3;                   // producer warps: operands of the next unit, deferred passes of the previous
+constexpr int TC_PROD_WARPS = 7;                   // producer warps: operands of the next unit, deferred passes of the previous
 constexpr int TC_PRODS = TC_PROD_WARPS * 32;
 constexpr int TC_THREADS = TC_VOTERS + 32 + TC_PRODS;   // 640 = 5 warpgroups
 constexpr int TC_STAGES = 3;                       // unit k lives in stage k % 3: produced | voted on | deferred passes
 constexpr int TC_PASS_H = 512;                     // hypotheses per unit (4 M-blocks of 128)
 constexpr int TC_TILE_PX = 128;                    // pixels per MMA tile (N = 256 columns)
 constexpr int TC_TMEM_COLS = 512;                  // two accumulator buffers of 256 columns: the whole TMEM of the SM
-constexpr int TC_REGS_VOTER = 104, TC_REGS_OTHER = 64;  // setmaxnreg: 512 x 104 + 128 x 64 = 61440 = the launch allocation (640 x 96)
+constexpr int TC_REGS_VOTER = 96, TC_REGS_OTHER = 48;   // setmaxnreg: 512 x 96 + 256 x 48 = 61440 = the launch allocation (768 x 80)
 constexpr long long TC_SPIN_CYCLES = 4000000000ll;  // ~2 s
 
-// One unit of work = (256-pixel chunk, keypoint, pass of <= 512 hypotheses).
-struct tc_stage {
+// One unit of work = (256-pixel chunk, keypoint, pass of <= 512 hypotheses).  Units are ordered (keypoint, pass, chunk)
+// and every CTA takes one contiguous range of them, so consecutive units of a CTA share their ROW = (image, keypoint,
+// pass): the hypothesis operand (A rows, in a frame whose origin is the middle pixel of the row's first chunk in this
+// CTA) is built once per row, not once per unit.
+constexpr int TC_ROWS = 4;    // row buffers (a row is rewritten 3 rows later: its last unit's deferred passes are over)
+constexpr int TC_RAWS = 4;    // raw-input buffers (unit k+1 is being staged while unit k-2 is in its deferred passes)
+struct tc_row {
     uint4 A[2][TC_PASS_H];            // hypotheses, [K half][row]: 16 KB
-    uint4 B[2][2 * PVV_CHUNK_PX];     // pixels x {+,-}, [K half][row = 2*pixel + plane]: 16 KB
-    float4 H[TC_PASS_H];              // local hypotheses {hx, hy, T of the FP32 filter, T of the tensor-pipe filter}
-    float P[K3_SP_FLOATS];            // FP32 constants in the FP32 kernel's pair layout (phase A)
-    uint32_t q[K3_QCAP];              // flagged entries: (group << 16) | hypothesis within the pass
-    long long row, pix;               // offset of the (image, keypoint) row in hyp / counts; of the first pixel in the pool
-    int qn, stop, mbn, nbn, n, hbase, vi, pad;
+    float4 H[TC_PASS_H];              // {hx, hy, |hx|+|hy| (inf: every test of this hypothesis takes the exact path), -}
+    float2 raw[TC_PASS_H];            // the hypotheses as K2 wrote them (phase B)
+    int cnt[TC_PASS_H];               // inlier counts of the row, accumulated over this CTA's units of it: one global add per
+                                      // hypothesis and ROW instead of one per hypothesis, unit and voting warp
 };
-struct tc_inputs {                    // raw inputs of one unit, staged by cp.async one iteration ahead
-    float4 pq[PVV_CHUNK_PX];
-    float2 hyp[TC_PASS_H];
+struct tc_raw {                       // raw inputs of one unit, staged by cp.async one iteration ahead
+    float4 pq[PVV_CHUNK_PX];          // frame-independent constants (k_pixel_consts)
+    float2 dir[PVV_CHUNK_PX];         // direction vectors and coordinates (phase B)
     uint32_t xy[PVV_CHUNK_PX];
 };
+struct tc_stage {
+    uint4 B[2][2 * PVV_CHUNK_PX];     // pixels x {+,-}, [K half][row = 2*pixel + plane]: 16 KB
+    float P[K3_SP_FLOATS];            // FP32 constants in the FP32 kernel's pair layout (phase A)
+    uint32_t q[K3_QCAP];              // flagged entries: (group << 16) | hypothesis within the pass
+    long long cnt_row;                // offset of the (image, keypoint) row + pass in counts
+    float ext;                        // largest |offset| of a pixel of the unit from the row's frame origin
+    int qn, stop, mbn, nbn, n, hcount, row, last, ox, oy, pad;   // last: the row ends with this unit (its counts are flushed)
+};
 struct tc_smem {
+    tc_row rows[TC_ROWS];
     tc_stage st[TC_STAGES];
-    tc_inputs in[2];
+    tc_raw raw[TC_RAWS];
     uint32_t q2[K3_QCAP];             // phase B entries: (pixel << 16) | hypothesis within the pass
     unsigned long long bar_ab[TC_STAGES], bar_done[TC_STAGES], bar_full[2], bar_empty[2];
+    long long off[8];                 // ring: pool offset of the image of unit k (slot k & 7), fetched two iterations ahead
+    int4 ent[8];                      // ring: chunk-table entry of unit k, fetched three iterations ahead (x = -1: no unit)
     uint32_t tmem;
     int ext, q2n;
 };
@@ -90,19 +104,23 @@ __device__ __forceinline__ uint32_t tc_bar_try(uint32_t bar_saddr, uint32_t pari
                  : "=r"(done) : "r"(bar_saddr), "r"(parity) : "memory");
     return done;
 }
+template <bool BACKOFF>
 __device__ __forceinline__ void tc_bar_wait_slow(uint32_t bar_saddr, uint32_t parity)
 {
     const long long t0 = clock64();
     while (!tc_bar_try(bar_saddr, parity)) {
-        __nanosleep(64);  // a waiting warp must not eat the issue slots of the voting warps
+        if (BACKOFF) __nanosleep(64);  // a waiting warp must not eat the issue slots of the voting warps
         if (clock64() - t0 > TC_SPIN_CYCLES) __trap();
     }
 }
+// BACKOFF = false: the MMA issuer, whose wake-up latency is on the critical path of every tile
+template <bool BACKOFF = true>
 __device__ __forceinline__ void tc_bar_wait(uint32_t bar_saddr, uint32_t parity)
 {
-    if (!tc_bar_try(bar_saddr, parity)) tc_bar_wait_slow(bar_saddr, parity);
+    if (!tc_bar_try(bar_saddr, parity)) tc_bar_wait_slow<BACKOFF>(bar_saddr, parity);
 }
-__device__ __forceinline__ void tc_bar_wait(unsigned long long *b, uint32_t parity) { tc_bar_wait(tc_saddr(b), parity); }
+template <bool BACKOFF = true>
+__device__ __forceinline__ void tc_bar_wait(unsigned long long *b, uint32_t parity) { tc_bar_wait<BACKOFF>(tc_saddr(b), parity); }
 __device__ __forceinline__ void tc_bar_arrive(uint32_t bar_saddr)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_saddr) : "memory");
@@ -208,7 +226,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
 
     pvv_pdl_enter();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int total_items = ws.chunk_start[d.b] * d.vn;
 
     if (tid == 0) {
         for (int i = 0; i < TC_STAGES; ++i) { tc_bar_init(&S.bar_ab[i], TC_PROD_WARPS); tc_bar_init(&S.bar_done[i], TC_VOTER_WARPS); }
@@ -217,6 +234,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         S.ext = 0; S.q2n = 0;
     }
+    for (int i = tid; i < TC_ROWS * TC_PASS_H; i += TC_THREADS) S.rows[i / TC_PASS_H].cnt[i % TC_PASS_H] = 0;
     if (warp == TC_MMA_WARP) {  // the MMA warp owns the TMEM allocation
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_saddr(&S.tmem)), "r"(TC_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -241,8 +259,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             tc_stage &T = S.st[s];
             tc_bar_wait(&S.bar_ab[s], (k / TC_STAGES) & 1u);
             if (T.stop) break;
-            const int mbn = T.mbn, nbn = T.nbn, hbase = T.hbase;
-            const long long row = T.row;
+            const int mbn = T.mbn, nbn = T.nbn, hcount = T.hcount;
+            const float ext = T.ext;
+            tc_row &R = S.rows[T.row];
             uint32_t dmask = 0u;  // bit mb*4 + nb*2 + g: flagged 16-pixel group of this thread's hypothesis in M-block mb
             // Software pipeline over the 16-pixel groups of the unit: the tcgen05.ld of group g+1 is in flight while
             // group g is voted on (tcgen05.wait::ld waits for every outstanding load, so each wait follows the vote).
@@ -260,12 +279,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             auto vote = [&](const uint32_t (&v)[32], float Tt, int &neg, uint32_t &dm, uint32_t bit) {
                 if (abl & 16) neg += v[0] ^ v[31]; else tc_group(v, Tt, neg, dm, bit);
             };
+            if (!(abl & 2048)) {
             full_wait(t);
             tc_ld32(tmem_row + (t & 1u) * 256u, v0);
             landed();
-            for (int mb = 0; mb < mbn; ++mb) {
+            }
+            for (int mb = 0; mb < mbn && !(abl & 2048); ++mb) {
                 const int hl = mb * 128 + q4 * 32 + lane;
-                const float Tt = T.H[hl].w;
+                // band half-width of the tensor-pipe filter, constant over the unit: |a| <= |hx| + |hy| + ext
+                const float Tt = __fmaf_rn(krel_tc, __fadd_rn(R.H[hl].z, ext), bc.abs_floor);
                 int neg = 0;
                 uint32_t dm = 0u;
                 tc_ld32(tmem_row + (t & 1u) * 256u + 32u, v1);
@@ -298,8 +320,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                     landed();
                 }
                 const int cnt = K3_GROUP * (2 * nbn - __popc(dm)) - sign_lanes_total(neg);
-                if (hbase + hl < d.hn) {
-                    if (cnt) atomicAdd(&ws.counts[row + hbase + hl], cnt);
+                if (hl < hcount) {
+                    if (cnt && !K3_ABL(8)) atomicAdd(&R.cnt[hl], cnt);
                     dmask |= dm << (mb * 4);
                 }
             }
@@ -324,15 +346,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                     if (q < K3_QCAP) {
                         T.q[q] = ((uint32_t)grp << 16) | (uint32_t)hl;
                     } else {  // queue full (pathological inputs): the reference's own decision for the whole group, in line
-                        const float2 hv = ws.hyp[row + hbase + hl];
+                        const tc_raw &W = S.raw[k % TC_RAWS];
+                        const float2 hv = R.raw[hl];
                         int c = 0;
                         for (int j = grp * K3_GROUP; j < min(T.n, (grp + 1) * K3_GROUP); ++j) {
-                            const float2 dir = ws.pix_dir[(long long)T.vi * ws.cap + T.pix + j];
-                            const uint32_t xy = ws.pix_xy[T.pix + j];
+                            const float2 dir = W.dir[j];
+                            const uint32_t xy = W.xy[j];
                             c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
                                                 hv.x, hv.y, d.thresh) ? 1 : 0;
                         }
-                        if (c) atomicAdd(&ws.counts[row + hbase + hl], c);
+                        if (c) atomicAdd(&R.cnt[hl], c);
                     }
                     ++q;
                 }
@@ -350,15 +373,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                 for (uint32_t k = 0;; ++k) {
                     const uint32_t s = k % TC_STAGES;
                     tc_stage &T = S.st[s];
-                    tc_bar_wait(&S.bar_ab[s], (k / TC_STAGES) & 1u);
+                    tc_bar_wait<false>(&S.bar_ab[s], (k / TC_STAGES) & 1u);
                     if (T.stop) break;
                     const int mbn = T.mbn, nbn = T.nbn;
+                    const tc_row &R = S.rows[T.row];
                     tc_fence_after();
                     for (int mb = 0; mb < mbn && !K3_ABL(32); ++mb) {
-                        const uint64_t da = tc_desc(tc_saddr(&T.A[0][mb * 128]), sizeof(T.A[0]), 128);
+                        const uint64_t da = tc_desc(tc_saddr(&R.A[0][mb * 128]), sizeof(R.A[0]), 128);
                         for (int nb = 0; nb < nbn; ++nb, ++t) {
                             const uint32_t buf = t & 1u;
-                            if (t >= 2) tc_bar_wait(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
+                            if (t >= 2) tc_bar_wait<false>(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
                             tc_fence_after();
                             const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * 256]), sizeof(T.B[0]), 128);
                             asm volatile(
@@ -379,13 +403,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             unsigned long long amb_local = 0;
             const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};
 
-            auto resolve = [&](const tc_stage &T, int hl, int j) {  // the reference's own decision for one test
-                const float2 hv = ws.hyp[T.row + T.hbase + hl];
-                const float2 dir = ws.pix_dir[(long long)T.vi * ws.cap + T.pix + j];
-                const uint32_t xy = ws.pix_xy[T.pix + j];
+            auto resolve = [&](const tc_stage &T, const tc_raw &W, int hl, int j) {  // the reference's own decision for one test
+                const float2 hv = S.rows[T.row].raw[hl];
+                const float2 dir = W.dir[j];
+                const uint32_t xy = W.xy[j];
                 if (pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16), hv.x, hv.y,
                                    d.thresh))
-                    atomicAdd(&ws.counts[T.row + T.hbase + hl], 1);
+                    atomicAdd(&S.rows[T.row].cnt[hl], 1);
                 ++amb_local;
             };
             // deferred passes of one unit: (A) the FP32 filter re-decides every test of a flagged (hypothesis, group) --
@@ -394,13 +418,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             auto deferred = [&](uint32_t u) {
                 const uint32_t s = u % TC_STAGES;
                 tc_stage &T = S.st[s];
+                const tc_raw &W = S.raw[u % TC_RAWS];
+                tc_row &R = S.rows[T.row];
                 tc_bar_wait(&S.bar_done[s], (u / TC_STAGES) & 1u);
                 const int qtot = min(T.qn, K3_QCAP) * K3_SUB;
                 for (int idx = ptid; idx < qtot; idx += TC_PRODS) {
                     const uint32_t ent = T.q[idx / K3_SUB];
                     constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
                     const int hl = (int)(ent & 0xffffu), grp = (int)(ent >> 16), u0 = (idx % K3_SUB) * PAIRS;
-                    const float4 hh = T.H[hl];
+                    const float4 hh = R.H[hl];
+                    const float Tf = __fmaf_rn(bc.krel, __fadd_rn(hh.z, T.ext), bc.abs_floor);
                     const f32x2 hxx = pk(hh.x, hh.x), hyy = pk(hh.y, hh.y);
                     const ulonglong2 *pg = reinterpret_cast<const ulonglong2 *>(T.P) + grp * K3_GSTRIDE + 3 * u0;
                     int sure = 0;
@@ -412,85 +439,147 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                         unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
                         unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
                         const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
-                        if (!(fabsf(m0) > hh.z)) inband |= 1u << (2 * p); else sure += m0 > 0.f;
-                        if (!(fabsf(m1) > hh.z)) inband |= 2u << (2 * p); else sure += m1 > 0.f;
+                        if (!(fabsf(m0) > Tf)) inband |= 1u << (2 * p); else sure += m0 > 0.f;
+                        if (!(fabsf(m1) > Tf)) inband |= 2u << (2 * p); else sure += m1 > 0.f;
                     }
-                    if (sure) atomicAdd(&ws.counts[T.row + T.hbase + hl], sure);
+                    if (sure) atomicAdd(&R.cnt[hl], sure);
                     while (inband) {
                         const int j = grp * K3_GROUP + 2 * u0 + __ffs(inband) - 1;
                         inband &= inband - 1;
-                        if (j >= T.n) continue;  // padded pixels (m = -1e30) only get here when T is infinite
+                        if (j >= T.n) continue;  // padded pixels (m = -1e30) only get here when the band is infinite
                         const int q = atomicAdd(&S.q2n, 1);
                         if (q < K3_QCAP) S.q2[q] = ((uint32_t)j << 16) | (uint32_t)hl;
-                        else resolve(T, hl, j);
+                        else resolve(T, W, hl, j);
                     }
                 }
                 pbar();
                 const int q2 = min(S.q2n, K3_QCAP);
                 for (int idx = ptid; idx < q2; idx += TC_PRODS) {
                     const uint32_t ent = S.q2[idx];
-                    resolve(T, (int)(ent & 0xffffu), (int)(ent >> 16));
+                    resolve(T, W, (int)(ent & 0xffffu), (int)(ent >> 16));
                 }
                 pbar();
                 if (ptid == 0) S.q2n = 0;
+                if (T.last) {  // the row's last unit: one global add per hypothesis, and the buffer is clean for its next row
+                    for (int hl = ptid; hl < T.hcount; hl += TC_PRODS) {
+                        const int c = R.cnt[hl];
+                        if (c) { atomicAdd(&ws.counts[T.cnt_row + hl], c); R.cnt[hl] = 0; }
+                    }
+                }
             };
 
-            // Units are dealt round-robin over the CTAs (item = blockIdx.x + i * gridDim.x; equal cost per item), so the
-            // producers know them arbitrarily far ahead and every global load is issued an iteration before its use:
-            //   iteration k:  chunk-table entry of unit k+3 | pool offset of unit k+2 | cp.async of the raw inputs of
-            //   unit k+1 into the other staging buffer | operands of unit k out of its staging buffer.
+            // This CTA's contiguous range of units, in (keypoint, pass, chunk) order; every global load is issued an
+            // iteration (or more) before its use: chunk-table entry of unit k+3 | pool offset of unit k+2 | cp.async of
+            // the raw inputs of unit k+1 | operands of unit k.
             const int npass = (d.hn + TC_PASS_H - 1) / TC_PASS_H;
-            auto unit_item = [&](uint32_t u) { return (int)blockIdx.x + (int)(u / (uint32_t)npass) * (int)gridDim.x; };
-            auto load_entry = [&](uint32_t u) {
-                const int item = unit_item(u);
-                return item < total_items ? __ldg(&ws.chunk_tab[item / d.vn]) : make_int4(-1, 0, 0, 0);
+            const uint32_t nchunks = (uint32_t)ws.chunk_start[d.b];
+            const long long units = (long long)nchunks * d.vn * npass;
+            const long long u_lo = units * blockIdx.x / gridDim.x, u_hi = units * (blockIdx.x + 1) / gridDim.x;
+            const uint32_t nunits = (uint32_t)(u_hi - u_lo);   // units of this CTA: unit k = global unit u_lo + k
+            // (chunk, keypoint-pass group) of unit k, advanced without divisions: unit k + add
+            uint32_t ci = u_lo < u_hi ? (uint32_t)(u_lo % nchunks) : 0u, rg = u_lo < u_hi ? (uint32_t)(u_lo / nchunks) : 0u;
+            auto unit_at = [&](uint32_t add, uint32_t &co, uint32_t &ro) {
+                co = ci + add; ro = rg;
+                while (co >= nchunks) { co -= nchunks; ++ro; }
             };
-            auto stage_inputs = [&](uint32_t u, const int4 &e, long long off, int buf) {  // cp.async: pixels + hypotheses
+            // the look-ahead loads go through shared memory (cp.async by one thread): a register-carried prefetch would stall
+            // on its own load as soon as the loop rotates its registers
+            auto fetch_entry = [&](uint32_t add, uint32_t kk) {   // thread 0: entry of unit kk = current unit + add
+                if (kk < nunits) {
+                    uint32_t co, ro;
+                    unit_at(add, co, ro);
+                    cp_async16(&S.ent[kk & 7u], ws.chunk_tab + co);
+                } else {
+                    S.ent[kk & 7u] = make_int4(-1, 0, 0, 0);
+                }
+            };
+            auto fetch_off = [&](uint32_t kk) {                  // thread 0; the entry of unit kk has landed
+                const int img = S.ent[kk & 7u].x;
+                if (img >= 0) cp_async8(&S.off[kk & 7u], ws.img_off + img);
+            };
+            auto stage_inputs = [&](uint32_t rg1, uint32_t k1, const int4 &e, long long off, bool new_row, int rowbuf) {
                 if (e.x >= 0 && !K3_ABL(1024)) {
-                    const int vi = unit_item(u) % d.vn, hbase = (int)(u % (uint32_t)npass) * TC_PASS_H;
+                    const int vi = (int)rg1 / npass, hbase = ((int)rg1 % npass) * TC_PASS_H;
                     const long long pix = off + e.y;
+                    tc_raw &W = S.raw[k1 % TC_RAWS];
                     for (int j = ptid; j < e.z; j += TC_PRODS) {
-                        cp_async16(&S.in[buf].pq[j], ws.pix_pq + (long long)vi * ws.cap + pix + j);
-                        cp_async4(&S.in[buf].xy[j], ws.pix_xy + pix + j);
+                        cp_async16(&W.pq[j], ws.pix_pq + (long long)vi * ws.cap + pix + j);
+                        cp_async8(&W.dir[j], ws.pix_dir + (long long)vi * ws.cap + pix + j);
+                        cp_async4(&W.xy[j], ws.pix_xy + pix + j);
                     }
-                    const long long row = ((long long)e.x * d.vn + vi) * ws.hn_pad + hbase;
-                    const int hcount = min(TC_PASS_H, d.hn - hbase);
-                    for (int hl = ptid; hl < hcount; hl += TC_PRODS) cp_async8(&S.in[buf].hyp[hl], ws.hyp + row + hl);
+                    if (new_row) {
+                        const long long hrow = ((long long)e.x * d.vn + vi) * ws.hn_pad + hbase;
+                        const int hcount = min(TC_PASS_H, d.hn - hbase);
+                        for (int hl = ptid; hl < hcount; hl += TC_PRODS) cp_async8(&S.rows[rowbuf].raw[hl], ws.hyp + hrow + hl);
+                    }
                 }
                 cp_async_commit();
             };
-            int4 e0 = load_entry(0), e1 = load_entry(1), e2 = load_entry(2);   // entries of units k, k+1, k+2
-            long long off0 = e0.x >= 0 ? __ldg(&ws.img_off[e0.x]) : 0, off1 = e1.x >= 0 ? __ldg(&ws.img_off[e1.x]) : 0;
-            stage_inputs(0, e0, off0, 0);
+            if (ptid == 0) {
+                for (uint32_t i = 0; i < 3; ++i) fetch_entry(i, i);
+                cp_async_commit();
+                cp_async_wait_all();
+                fetch_off(0); fetch_off(1);
+                cp_async_commit();
+                cp_async_wait_all();
+            }
+            pbar();
+            int4 e0 = S.ent[0];
+            int rowbuf = 0, ox = 0, oy = 0;   // row buffer and frame origin of unit k
+            bool new_row = true;              // unit k starts a row
+            stage_inputs(rg, 0, e0, S.off[0], true, 0);
             uint32_t k = 0;
             for (;; ++k) {
                 const uint32_t s = k % TC_STAGES;
                 tc_stage &T = S.st[s];  // free: the deferred passes of unit k - 3 ended in the previous iteration
                 cp_async_wait_all();
                 pbar();  // unit k's inputs are staged; everything of the previous iteration is complete
+                e0 = S.ent[k & 7u];
+                const int4 e1 = S.ent[(k + 1) & 7u];
                 if (e0.x < 0) {
                     if (ptid == 0) T.stop = 1;
                     __syncwarp();
                     if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
                     break;
                 }
-                const int4 e3 = load_entry(k + 3);
-                const long long off2 = e2.x >= 0 ? __ldg(&ws.img_off[e2.x]) : 0;
-                stage_inputs(k + 1, e1, off1, (int)((k + 1) & 1u));
-                const tc_inputs &I = S.in[k & 1u];
-                const int vi = unit_item(k) % d.vn, hbase = (int)(k % (uint32_t)npass) * TC_PASS_H;
-                const int n = e0.z, ox = (int)((uint32_t)e0.w & 0xffffu), oy = (int)((uint32_t)e0.w >> 16);
+                if (ptid == 0) { fetch_entry(3, k + 3); fetch_off(k + 2); }   // committed with the staging group below
+                const long long off1 = S.off[(k + 1) & 7u];
+                uint32_t ci1, rg1;
+                unit_at(1, ci1, rg1);
+                const bool next_new_row = e1.x >= 0 && !(e1.x == e0.x && rg1 == rg);
+                const int next_rowbuf = next_new_row ? (rowbuf + 1) % TC_ROWS : rowbuf;
+                stage_inputs(rg1, k + 1, e1, off1, next_new_row, next_rowbuf);
+                const tc_raw &W = S.raw[k % TC_RAWS];
+                tc_row &R = S.rows[rowbuf];
+                const int vi = (int)rg / npass, hbase = ((int)rg % npass) * TC_PASS_H;
+                const int hcount = min(TC_PASS_H, d.hn - hbase);
+                const int n = e0.z;
                 const int nbn = (n + TC_TILE_PX - 1) / TC_TILE_PX;
-                const int mbn = min(TC_PASS_H / 128, (d.hn - hbase + 127) / 128);
-                const long long pix = off0 + e0.y;
-                const long long row = ((long long)e0.x * d.vn + vi) * ws.hn_pad;
-                // ---- pixel constants in the chunk-local frame: FP32 (phase A) and their TF32 split as B rows ----
+                const int mbn = (hcount + 127) / 128;
+                if (new_row) {
+                    // ---- a new row: frame origin = middle pixel of this chunk; hypotheses -> A rows (once per row) ----
+                    ox = (int)((uint32_t)e0.w & 0xffffu); oy = (int)((uint32_t)e0.w >> 16);
+                    for (int hl = ptid; hl < mbn * 128 && !K3_ABL(64); hl += TC_PRODS) {
+                        const float2 hv = hl < hcount ? R.raw[hl] : make_float2(0.f, 0.f);
+                        float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy);
+                        float mm = __fadd_rn(fabsf(hx), fabsf(hy));
+                        if (!(mm < 1e15f)) {  // far-away / non-finite hypothesis: every test takes the exact path
+                            hx = 0.f; hy = 0.f; mm = __int_as_float(0x7f800000);
+                        }
+                        R.H[hl] = make_float4(hx, hy, mm, 0.f);
+                        uint32_t xh, xl, yh, yl;
+                        tc_split(hx, xh, xl); tc_split(hy, yh, yl);
+                        R.A[0][hl] = make_uint4(xh, xh, xl, yh);
+                        R.A[1][hl] = make_uint4(yh, yl, 0x3f800000u, 0x3f800000u);
+                    }
+                }
+                // ---- pixel constants in the row's frame: FP32 (phase A) and their TF32 split as B rows ----
                 int ext = 0;
                 for (int j = ptid; j < nbn * TC_TILE_PX && !K3_ABL(256); j += TC_PRODS) {
                     px_consts c = never;
                     if (j < n && !K3_ABL(4)) {
-                        const float4 pq = I.pq[j];
-                        const uint32_t xy = I.xy[j];
+                        const float4 pq = W.pq[j];
+                        const uint32_t xy = W.xy[j];
                         if (pq.x != 0.f || pq.y != 0.f) {
                             const float fx = (float)((int)(xy & 0xffffu) - ox), fy = (float)((int)(xy >> 16) - oy);
                             c.px = pq.x; c.py = pq.y; c.qx = pq.z; c.qy = pq.w;
@@ -510,35 +599,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                 }
                 ext = __reduce_max_sync(0xffffffffu, ext);
                 if (lane == 0 && ext) atomicMax(&S.ext, ext);
-                pbar();
-                const float P = (float)S.ext;
-                // ---- hypotheses of this pass in the chunk-local frame: A rows and band half-widths ----
-                for (int hl = ptid; hl < mbn * 128 && !K3_ABL(64); hl += TC_PRODS) {
-                    const float2 hv = hbase + hl < d.hn ? I.hyp[hl] : make_float2(0.f, 0.f);
-                    float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy), Tf, Tt;
-                    const float mm = __fadd_rn(__fadd_rn(fabsf(hx), fabsf(hy)), P);
-                    if (mm < 1e15f) {
-                        Tf = __fmaf_rn(bc.krel, mm, bc.abs_floor);
-                        Tt = __fmaf_rn(krel_tc, mm, bc.abs_floor);
-                    } else {  // far-away / non-finite hypothesis: every test takes the exact path
-                        hx = 0.f; hy = 0.f; Tf = Tt = __int_as_float(0x7f800000);
-                    }
-                    T.H[hl] = make_float4(hx, hy, Tf, Tt);
-                    uint32_t xh, xl, yh, yl;
-                    tc_split(hx, xh, xl); tc_split(hy, yh, yl);
-                    T.A[0][hl] = make_uint4(xh, xh, xl, yh);
-                    T.A[1][hl] = make_uint4(yh, yl, 0x3f800000u, 0x3f800000u);
-                }
-                if (ptid == 0) {
-                    T.stop = 0; T.mbn = mbn; T.nbn = nbn; T.n = n; T.hbase = hbase; T.vi = vi; T.row = row; T.pix = pix; T.qn = 0;
-                }
                 if (!K3_ABL(128)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // operands visible to the tensor pipe
-                pbar();  // every producer passed its reads of S.ext; thread 0's header is written
-                if (ptid == 0) S.ext = 0;
+                pbar();
+                if (ptid == 0) {
+                    T.stop = 0; T.mbn = mbn; T.nbn = nbn; T.n = n; T.hcount = hcount; T.row = rowbuf; T.qn = 0; T.ox = ox; T.oy = oy;
+                    T.last = (e1.x < 0 || next_new_row) ? 1 : 0;
+                    T.cnt_row = ((long long)e0.x * d.vn + vi) * ws.hn_pad + hbase;
+                    T.ext = (float)S.ext;
+                    S.ext = 0;
+                }
+                __syncwarp();
                 if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
                 // ---- deferred passes of the unit the voters finished last ----
                 if (k >= 2 && !K3_ABL(512)) deferred(k - 2);
-                e0 = e1; e1 = e2; e2 = e3; off0 = off1; off1 = off2;
+                new_row = next_new_row; rowbuf = next_rowbuf; ci = ci1; rg = rg1;
             }
             // k units were published (0 .. k-1): finish the deferred passes of the last two
             if (k >= 2) deferred(k - 2);
