@@ -264,25 +264,29 @@ def run_ours(args):
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic, traffic_src = None, None
+    traffic, traffic_src, wipt = None, None, None
     try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` capture
         t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["k_count"]
-        traffic, traffic_src = t["dram_bytes_per_launch"], t["source"]
+        traffic, traffic_src, wipt = t["dram_bytes_per_launch"], t["source"], t.get("warp_instr_per_test")
     except Exception:
         pass
     k1_bytes = mask.nbytes + tn_total * VN * 8 + tn_total * (4 + VN * 8) + 2 * (mask.size // 8)  # mask once; bitmask w+r
-    roofline = {"kernel": "k_count (K3 fused inlier counting)", "bound": "fp32", "achieved": achieved, "peak": peak,
+    roofline = {"kernel": "k_pixel_consts + k_count_tc (K3 fused inlier counting, tensor-pipe kernel: hn > 256)", "bound": "fp32",
+                "achieved": achieved, "peak": peak,
                 "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
-                "bound_note": "FP32 SIMT compare/reduce (north_star: no tensor cores); HBM traffic of this kernel is ~0.6% of peak",
+                "bound_note": "the metric stays SURVEY 8(d)'s: 12 FLOP per test against the FFMA peak.  The shipped kernel takes the two "
+                              "half-plane forms of a test off the FP32 pipe (one tcgen05 tf32 MMA per 128 hypotheses x 128 pixels, "
+                              "3xTF32 split, accumulators in TMEM) and is bound by the CUDA cores' ALU pipe / issue slots (min, sign "
+                              "count, guard band); HBM traffic of this kernel is ~1% of peak",
                 "peak_source": "FFMA probe kernel run in this process (pvv_fp32_peak_tflops); MEASURED_PEAKS.json has no FP32 figure",
                 "flop_per_test": FLOP_PER_TEST, "tests_per_launch": tests_per_step, "kernel_ms": st["count"],
                 "tests_per_s": tests_per_step / (st["count"] * 1e-3),
-                # issue-slot utilisation next to the FLOP fraction.  4.9 warp instructions per warp-test is the
-                # SASS count of the shipped hot loop (profiles/r01_k_count_ncu_summary.txt); 4 schedulers per SM, 1 issue/clk
-                "warp_instr_per_test": 4.9,
-                "issue_slot_utilisation": (tests_per_step / (st["count"] * 1e-3) / 32.0 * 4.9 /
+                # issue-slot utilisation next to the FLOP fraction.  Warp instructions per warp-test = ncu's
+                # smsp__inst_executed.sum of the kernel / (tests / 32) (profiles/ncu_traffic.json); 4 schedulers per SM, 1 issue/clk
+                "warp_instr_per_test": wipt,
+                "issue_slot_utilisation": (tests_per_step / (st["count"] * 1e-3) / 32.0 * wipt /
                                            (torch.cuda.get_device_properties(dev).multi_processor_count * 4 *
-                                            (clocks.get("sm_mhz") or 1965) * 1e6)),
+                                            (clocks.get("sm_mhz") or 1965) * 1e6)) if wipt else None,
                 "k1_compaction": {"bound": "hbm", "achieved": k1_bytes / (st["compact"] * 1e-3) / 1e9, "peak": hbm_peak,
                                   "unit": "GB/s", "frac": k1_bytes / (st["compact"] * 1e-3) / 1e9 / hbm_peak,
                                   "kernel_ms": st["compact"], "bytes": k1_bytes,

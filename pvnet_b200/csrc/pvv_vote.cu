@@ -627,10 +627,14 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     band_consts bc = {0.f, 0.f, 0.f};
     float krel_tc = 0.f;
     const bool fast = !force_exact && pvv_band_for(d.thresh, &bc, &krel_tc);
-    // CTA shape by hypothesis count: every thread owns 4 hypotheses, one pass covers 4 * THREADS of them
-    // (PVV_K3_VARIANT overrides the choice: a tuning knob for tools/k3_variants.py)
+    // Kernel by hypothesis count (measured, profiles/r01_sweep.md): above 256 hypotheses the tensor-pipe kernel
+    // (pvv_vote_tc.cuh: tcgen05 tf32 MMA for the half-plane forms, CUDA cores for min / sign count / band) is 6-13 %
+    // faster than the FP32-pipe kernel; at 128 and 256 the FP32-pipe kernel with 32- / 64-thread CTAs (every thread owns
+    // 4 hypotheses, one pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand
+    // staging are not amortised.  PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe): a tuning
+    // and test knob (tools/k3_variants.py, tests/test_gpu_parity.py).
     const char *venv = getenv("PVV_K3_VARIANT");
-    const int variant = venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 0);
+    const int variant = venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
     cudaError_t e;
     if (!fast) {
         int per_sm = 8;

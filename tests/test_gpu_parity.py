@@ -703,3 +703,56 @@ def test_random_cases_vs_reference_cuda_kernels():
             assert np.array_equal(inl, r_dbg[bi]["inlier"].cpu().numpy()), case
             checked += 1
     assert checked >= 20
+
+
+def test_k3_kernel_variants_agree_with_exact_kernel(monkeypatch):
+    """K3 ships two guard-banded kernels and picks by hypothesis count: the FP32-pipe kernel (hn <= 256) and the
+    tensor-pipe kernel (tcgen05 tf32 MMA + TMEM, hn > 256).  PVV_K3_VARIANT forces one; every variant must reproduce the
+    exact-only kernel's counts bit for bit on random ragged shapes (tiny images, partial chunks, hypothesis counts that
+    are not multiples of 128, far / on-pixel keypoints, scaled and zero directions), on the adversarial field, and on
+    the 4096-hypothesis covariance path (8 passes per chunk in the tensor-pipe kernel)."""
+    rng = np.random.default_rng(777)
+    cases = []
+    for case in range(10):
+        h, w = int(rng.integers(24, 220)), int(rng.integers(24, 300))
+        b, vn = int(rng.integers(1, 5)), int(rng.integers(1, 12))
+        hn = int(rng.choice([7, 128, 130, 300, 512, 700, 1100]))
+        thresh = float(rng.choice([0.5, 0.9, 0.99, 0.999, 0.9999, 0.99999]))
+        masks = np.zeros((b, h, w), np.int64)
+        verts = np.zeros((b, h, w, vn, 2), np.float32)
+        for i in range(b):
+            r = np.random.default_rng(int(rng.integers(1 << 30)))
+            masks[i] = synth.blob_mask(r, float(rng.uniform(0.01, 0.5)), h, w)
+            kp = np.stack([r.uniform(-3 * w, 4 * w, vn), r.uniform(-3 * h, 4 * h, vn)], 1) if rng.random() < 0.3 else \
+                np.stack([r.uniform(0, w, vn), r.uniform(0, h, vn)], 1)
+            if rng.random() < 0.3:
+                kp = np.round(kp)
+            verts[i] = synth.unit_field(masks[i], kp, float(rng.choice([0.0, 0.02, 0.2])), r)
+            if rng.random() < 0.3:
+                verts[i] *= r.choice([0.0, 1e-7, 1e-3, 1.0, 1e3, 1e18], size=(h, w, vn, 1)).astype(np.float32)
+        cases.append((torch.from_numpy(masks).to(DEV), torch.from_numpy(verts).to(DEV), hn, thresh, case))
+    adv = np.random.default_rng(3).standard_normal((1, 64, 96, 3, 2)).astype(np.float32)
+    adv[0, :8] *= 1e-7
+    adv[0, 8:10] = 0.0
+    adv[0, 10:12] *= 1e18
+    for t in (0.5, 0.999, 0.99999):
+        cases.append((torch.ones((1, 64, 96), dtype=torch.int64, device=DEV), torch.from_numpy(adv).to(DEV), 600, t, 100))
+    mask, vertex, _ = synth.make_batch(2, vn=9, frac=0.02, sigma=0.05, seed=55)
+    cm, cv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    monkeypatch.delenv("PVV_K3_VARIANT", raising=False)
+    exact = [pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True,
+                                       force_exact=True)[1]["counts"].clone() for m, v, hn, th, c in cases]
+    mean = pv.ransac_voting_layer_v3(cm, cv, 512, 0.99, seed=1)
+    cov_x, dbg_x = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True, force_exact=True)[1:]
+    for variant in ("0", "1", "2", "7"):
+        monkeypatch.setenv("PVV_K3_VARIANT", variant)
+        for (m, v, hn, th, c), want in zip(cases, exact):
+            got = pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True)[1]
+            assert torch.equal(got["counts"], want), (variant, c, hn, th)
+        cov, dbg = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True)[1:]
+        assert torch.equal(dbg["counts"], dbg_x["counts"]) and torch.equal(cov, cov_x), variant
+    monkeypatch.delenv("PVV_K3_VARIANT", raising=False)
+    # the shipped choice: tensor pipe above 256 hypotheses (the exact path is taken, rarely, and the counts above matched)
+    _, d1 = pv.ransac_voting_layer_v3(cm, cv, 512, 0.999, seed=3, return_debug=True)
+    _, d2 = pv.ransac_voting_layer_v3(cm, cv, 512, 0.999, seed=3, return_debug=True, force_exact=True)
+    assert torch.equal(d1["counts"], d2["counts"]) and int(d1["amb_count"]) > 0
