@@ -1,10 +1,10 @@
-// pvv_vote_tc.cuh -- K3, tensor-pipe variant (included by pvv_vote.cu inside its anonymous namespace).
+// pvv_vote_tc.cuh -- K3, tensor-pipe kernel (included by pvv_vote.cu inside its anonymous namespace; shipped for hn > 256).
 //
-// The filter's two half-plane forms  e+- = hx*p + hy*q + r  are a rank-3 bilinear form in (hypothesis, pixel): per work
-// item an E[hypotheses x 2*pixels] matrix = H[hyp x K] . P[2*pixels x K]^T.  The FP32 pipe spent 2 FFMA2 per test on it;
-// here the 5th-generation tensor cores produce it with ONE tcgen05.mma (kind::tf32, M = 128 hypotheses, N = 128 columns =
-// 64 pixels x {e+, e-}, K = 8) per tile, accumulators in TMEM, and the CUDA cores keep only what is not a contraction:
-// m = min(e+, e-), sign counting and the guard-band tracker (2.5 instead of 4.9 issued instructions per test).
+// The filter's two half-plane forms  e+- = hx*p + hy*q + r  are a rank-3 bilinear form in (hypothesis, pixel): per unit
+// of work an E[hypotheses x 2*pixels] matrix = H[hyp x K] . P[2*pixels x K]^T.  The FP32-pipe kernel (k_count) spends
+// 2 FFMA2 per test on it; here the 5th-generation tensor cores produce it with ONE tcgen05.mma (kind::tf32, M = 128
+// hypotheses, N = 256 columns = 128 pixels x {e+, e-}, K = 8) per tile, accumulators in TMEM, and the CUDA cores keep
+// only what is not a contraction: m = min(e+, e-), sign counting and the guard-band tracker.
 //
 // Precision: TF32 has an 11-bit significand, so every fp32 factor is split x = x_hi + x_lo (both exactly representable
 // in TF32) and the K = 8 slots carry the three significant cross terms of each product plus the split constant term:
@@ -12,18 +12,24 @@
 //      B row (pixel, +-)  = [p_hi  p_lo  p_hi  q_hi  | q_lo  q_hi  r_hi r_lo]
 // TF32 x TF32 products are exact in the fp32 accumulator's 24 bits; what is lost is x_lo*y_lo (2^-22 relative), the
 // tail of the split (2^-23) and the accumulation rounding of the 8-term sum.  tools/tc_probe.cu measures the total on
-// the B200 in units of u(1+tau)M (u = 2^-24, M = |hx|+|hy|+P): the guard band of this kernel is built on a bound with
-// margin over that measurement (pvv_band_for: kabs_tc), and is only 10-20 % wider than the FP32 filter's at t = 0.999
-// because the band is dominated by the uncertainty of the REFERENCE's own fp32 quotient, not by the filter's rounding.
+// the B200 in units of u(1+tau)M (u = 2^-24, M = |hx|+|hy|+P): 5.5; the guard band of this kernel is built on 40
+// (pvv_band_for: kabs_tc), and is only ~15 % wider than the FP32 filter's at t = 0.999 because the band is dominated
+// by the uncertainty of the REFERENCE's own fp32 quotient, not by the filter's rounding.
 // The tensor-pipe result is never trusted inside the band: a flagged (hypothesis, 16-pixel group) is left out of the
 // provisional count altogether and re-decided by the FP32 filter (phase A, proved bound) and, inside ITS band, by the
 // reference's exact rounding sequence (phase B).  Counts stay bit-identical to the reference kernel's.
 //
-// CTA = 8 voting warps + 1 MMA warp.  The voting warps stage the operands in shared memory (canonical K-major,
-// non-swizzled core matrices: 8 rows x 16 B; LBO = byte stride between the two K halves, SBO = between 8-row groups:
-// verified on the B200 by tools/tc_probe.cu), one elected thread of the MMA warp issues the tcgen05.mma of tile i+1 into
-// the other TMEM buffer while the voting warps read tile i with tcgen05.ld (32x32b: lane = hypothesis row) -- the
-// tensor pipe (~70 cycles per tile) hides completely behind the ~300 cycles of CUDA-core work per tile.
+// One 768-thread CTA per SM (all 512 TMEM columns: two 256-column accumulator buffers), three roles, setmaxnreg:
+//   * 16 voting warps (96 registers): warp = (TMEM lane quarter, column quarter); per 16-pixel group one tcgen05.ld
+//     32x32b.x32 (lane = hypothesis row), software-pipelined so the load of group g+1 is in flight while group g is voted
+//     on; counts accumulate in shared memory per ROW (image, keypoint, pass) and reach global memory once per row;
+//   * 1 MMA warp: one elected thread issues the tcgen05.mma of tile i+2 as soon as the voters have pulled tile i into
+//     registers (mbarriers full / empty; tcgen05.commit); operands are canonical K-major, non-swizzled core matrices
+//     (8 rows x 16 B; LBO = byte stride between the two K halves, SBO = between 8-row groups: verified by tc_probe.cu);
+//   * 7 producer warps (48 registers): stage the raw inputs of unit k+1 with cp.async, build the B rows of unit k
+//     (pixel constants from the k_pixel_consts pre-pass, translated into the row's frame and split), build the A rows
+//     once per row, and run the deferred passes (phase A / B) of unit k-2 -- the voters never leave their loop.
+// Units are dealt as contiguous ranges in (keypoint, pass, chunk) order, so a CTA changes row ~3 times per launch.
 #pragma once
 
 #ifdef PVV_K3_ABLATE
@@ -37,7 +43,7 @@ constexpr int TC_VOTERS = TC_VOTER_WARPS * 32;
 constexpr int TC_MMA_WARP = TC_VOTER_WARPS;        // one elected thread issues every tcgen05.mma
 constexpr int TC_PROD_WARPS = 7;                   // producer warps: operands of the next unit, deferred passes of the previous
 constexpr int TC_PRODS = TC_PROD_WARPS * 32;
-constexpr int TC_THREADS = TC_VOTERS + 32 + TC_PRODS;   // 640 = 5 warpgroups
+constexpr int TC_THREADS = TC_VOTERS + 32 + TC_PRODS;   // 768 = 6 warpgroups
 constexpr int TC_STAGES = 3;                       // unit k lives in stage k % 3: produced | voted on | deferred passes
 constexpr int TC_PASS_H = 512;                     // hypotheses per unit (4 M-blocks of 128)
 constexpr int TC_TILE_PX = 128;                    // pixels per MMA tile (N = 256 columns)
