@@ -168,7 +168,8 @@ __device__ __forceinline__ void tc_group(const uint32_t (&v)[32], float T, int &
 {
     float m[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) m[i] = fminf(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+    // m = a - |tau c| = min(e+, e-): one FADD with an |.| modifier on the FMA pipe (the ALU pipe is the one this kernel fills)
+    for (int i = 0; i < 16; ++i) m[i] = __fsub_rn(__uint_as_float(v[2 * i]), fabsf(__uint_as_float(v[2 * i + 1])));
     int g = 0;
     float mabs = __int_as_float(0x7f800000);
 #pragma unroll
@@ -201,8 +202,9 @@ __device__ __forceinline__ void tc_tile(uint32_t a_full, uint32_t a_empty, uint3
     tc_group(v1, T, neg, dm, bit << 1);
 }
 
-// Pre-pass (one thread per (keypoint, pooled pixel)): the four frame-independent constants of the two half-planes,
-// each correctly rounded from fp64:  {nx - tau ny, ny + tau nx, nx + tau ny, ny - tau nx}.  All-zero marks a pixel the
+// Pre-pass (one thread per (keypoint, pooled pixel)): the four frame-independent constants of the two linear forms
+//   a = d . n^ = hx*nx + hy*ny + ra          tau c = tau (d x n^) = hx*(tau ny) + hy*(-tau nx) + rc
+// (e+- = a -+ tau c, so m = min(e+, e-) = a - |tau c|), each correctly rounded from fp64: {nx, ny, tau ny, -tau nx}.  All-zero marks a pixel the
 // reference never counts (||n|| < 1e-6, or a non-finite norm).
 __global__ void __launch_bounds__(256) k_pixel_consts(pvv_dims d, pvv_ws ws, float tau_f)
 {
@@ -218,7 +220,7 @@ __global__ void __launch_bounds__(256) k_pixel_consts(pvv_dims d, pvv_ws ws, flo
         if ((double)n1 >= 1e-6 && n1 < 3.0e38f) {
             const double inv = rsqrt((double)dir.x * dir.x + (double)dir.y * dir.y);
             const double nx = dir.x * inv, ny = dir.y * inv;
-            c = make_float4((float)(nx - tau * ny), (float)(ny + tau * nx), (float)(nx + tau * ny), (float)(ny - tau * nx));
+            c = make_float4((float)nx, (float)ny, (float)(tau * ny), (float)(-tau * nx));
         }
         out[i] = c;
     }
@@ -444,7 +446,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                         float ep0, ep1, em0, em1;
                         unpk(ffma2(hxx, v0.x, ffma2(hyy, v0.y, v1.x)), ep0, ep1);
                         unpk(ffma2(hxx, v1.y, ffma2(hyy, v2.x, v2.y)), em0, em1);
-                        const float m0 = fminf(ep0, em0), m1 = fminf(ep1, em1);
+                        const float m0 = __fsub_rn(ep0, fabsf(em0)), m1 = __fsub_rn(ep1, fabsf(em1));  // a - |tau c|
                         if (!(fabsf(m0) > Tf)) inband |= 1u << (2 * p); else sure += m0 > 0.f;
                         if (!(fabsf(m1) > Tf)) inband |= 2u << (2 * p); else sure += m1 > 0.f;
                     }
