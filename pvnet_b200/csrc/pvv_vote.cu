@@ -67,6 +67,10 @@ struct band_consts {
     float krel;       // half-width of the band per unit of max |coordinate| (covers tau's uncertainty + rounding)
     float abs_floor;  // catches ||d|| < 1e-6 (reference skips those)
     int ablate;       // experiments only (tools/k3_ablate.py builds with -DPVV_K3_ABLATE): phases to leave out
+    // the two parts of krel separately (tensor-pipe kernel: they multiply different magnitudes)
+    float erel;       // uncertainty of the reference's own decision, per unit of a bound on ||h - pixel||
+    float kabs;       // rounding of the FP32 filter, per unit of the magnitudes in its frame
+    float kabs_tc;    // rounding of the tensor-pipe filter (3xTF32 split), same unit
 };
 #ifndef K3_HOTVAR
 #define K3_HOTVAR 0
@@ -576,6 +580,9 @@ static bool pvv_band_for(float t, band_consts *bc, float *krel_tc)
     // Measured on the B200 (tools/tc_probe.cu): 5.5u against the fp32 constants.  Used: 40u.
     const double kabs_tc = 40.0 * u * (1.0 + tau) * (1.0 + etau);
     *krel_tc = (float)((erel + kabs_tc) * (1.0 + 4.0 * u));
+    bc->erel = (float)(erel * (1.0 + 4.0 * u));
+    bc->kabs = (float)(kabs * (1.0 + 4.0 * u));
+    bc->kabs_tc = (float)(kabs_tc * (1.0 + 4.0 * u));
     bc->abs_floor = (float)(4e-6 * (1.0 + tau));
     bc->ablate = 0;
 #ifdef PVV_K3_ABLATE
@@ -624,7 +631,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    band_consts bc = {0.f, 0.f, 0.f};
+    band_consts bc = {};
     float krel_tc = 0.f;
     const bool fast = !force_exact && pvv_band_for(d.thresh, &bc, &krel_tc);
     // Kernel by hypothesis count (measured, profiles/r01_sweep.md): above 256 hypotheses the tensor-pipe kernel

@@ -75,6 +75,8 @@ struct tc_stage {
     uint32_t q[K3_QCAP];              // flagged entries: (group << 16) | hypothesis within the pass
     long long cnt_row;                // offset of the (image, keypoint) row + pass in counts
     float ext;                        // largest |offset| of a pixel of the unit from the row's frame origin
+    float ucx, ucy, uext;             // the unit's own centre (its middle pixel) in the row's frame, and the largest |offset|
+                                      // of a pixel of the unit from it: |h - centre| + uext bounds ||h - pixel||
     int qn, stop, mbn, nbn, n, hcount, row, last, ox, oy, pad;   // last: the row ends with this unit (its counts are flushed)
 };
 struct tc_smem {
@@ -86,7 +88,7 @@ struct tc_smem {
     long long off[8];                 // ring: pool offset of the image of unit k (slot k & 7), fetched two iterations ahead
     int4 ent[8];                      // ring: chunk-table entry of unit k, fetched three iterations ahead (x = -1: no unit)
     uint32_t tmem;
-    int ext, q2n;
+    int ext, uext, q2n;
 };
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
@@ -177,9 +179,9 @@ __device__ __forceinline__ void tc_group(const uint32_t (&v)[32], float T, int &
         g += sign_lanes(m[i], m[i + 1]);
         mabs = fminf(fminf(mabs, fabsf(m[i])), fabsf(m[i + 1]));
     }
-    const bool flagged = !(mabs > T);
-    neg += flagged ? 0 : g;
-    dmask |= flagged ? bit : 0u;
+    // clean group (every |m| > T): its negatives count; otherwise only its bit is set -- two predicated instructions
+    asm("{\n\t.reg .pred p;\n\tsetp.gt.f32 p, %2, %3;\n\t@p add.s32 %0, %0, %4;\n\t@!p or.b32 %1, %1, %5;\n\t}"
+        : "+r"(neg), "+r"(dmask) : "f"(mabs), "f"(T), "r"(g), "r"(bit));
 }
 
 // One 256-column tile of this thread's hypothesis row: wait for the accumulator, pull this warp's 64 columns into
@@ -240,7 +242,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
         tc_bar_init(&S.bar_full[0], 1); tc_bar_init(&S.bar_full[1], 1);
         tc_bar_init(&S.bar_empty[0], TC_VOTER_WARPS); tc_bar_init(&S.bar_empty[1], TC_VOTER_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        S.ext = 0; S.q2n = 0;
+        S.ext = 0; S.uext = 0; S.q2n = 0;
     }
     for (int i = tid; i < TC_ROWS * TC_PASS_H; i += TC_THREADS) S.rows[i / TC_PASS_H].cnt[i % TC_PASS_H] = 0;
     if (warp == TC_MMA_WARP) {  // the MMA warp owns the TMEM allocation
@@ -260,7 +262,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
         uint32_t a_full = tc_saddr(&S.bar_full[0]), a_empty = tc_saddr(&S.bar_empty[0]);
         uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cq * 64);
         // opaque to the compiler: kept in registers instead of being rematerialised from tid / the shared window base
-        asm volatile("" : "+r"(a_full), "+r"(a_empty), "+r"(tmem_row));
+        uint32_t lane0 = lane == 0;
+        asm volatile("" : "+r"(a_full), "+r"(a_empty), "+r"(tmem_row), "+r"(lane0));
         uint32_t t = 0;  // tile counter, in lock-step with the MMA issuer's
         for (uint32_t k = 0;; ++k) {
             const uint32_t s = k % TC_STAGES;
@@ -268,7 +271,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             tc_bar_wait(&S.bar_ab[s], (k / TC_STAGES) & 1u);
             if (T.stop) break;
             const int mbn = T.mbn, nbn = T.nbn, hcount = T.hcount;
-            const float ext = T.ext;
+            const float ext = T.ext, ucx = T.ucx, ucy = T.ucy, uext = T.uext;
             tc_row &R = S.rows[T.row];
             uint32_t dmask = 0u;  // bit mb*4 + nb*2 + g: flagged 16-pixel group of this thread's hypothesis in M-block mb
             // Software pipeline over the 16-pixel groups of the unit: the tcgen05.ld of group g+1 is in flight while
@@ -282,7 +285,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             auto landed = [&] { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); };
             auto release = [&](uint32_t tt) {  // both groups of tile tt are in registers: its TMEM buffer is free
                 tc_fence_before();
-                if (lane == 0 && !(abl & 32)) tc_bar_arrive(a_empty + 8u * (tt & 1u));
+                if (lane0 && !(abl & 32)) tc_bar_arrive(a_empty + 8u * (tt & 1u));
             };
             auto vote = [&](const uint32_t (&v)[32], float Tt, int &neg, uint32_t &dm, uint32_t bit) {
                 if (abl & 16) neg += v[0] ^ v[31]; else tc_group(v, Tt, neg, dm, bit);
@@ -295,7 +298,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
             for (int mb = 0; mb < mbn && !(abl & 2048); ++mb) {
                 const int hl = mb * 128 + q4 * 32 + lane;
                 // band half-width of the tensor-pipe filter, constant over the unit: |a| <= |hx| + |hy| + ext
-                const float Tt = __fmaf_rn(krel_tc, __fadd_rn(R.H[hl].z, ext), bc.abs_floor);
+                // T = erel * (bound on ||h - pixel||: the unit's own centre and extent) + kabs_tc * (magnitudes in the row's
+                // frame: |a| <= |hx| + |hy| + ext) + floor, constant over the unit
+                const float4 hh = R.H[hl];
+                const float mu = __fadd_rn(__fadd_rn(fabsf(__fsub_rn(hh.x, ucx)), fabsf(__fsub_rn(hh.y, ucy))), uext);
+                const float Tt = __fmaf_rn(bc.erel, mu, __fmaf_rn(bc.kabs_tc, __fadd_rn(hh.z, ext), bc.abs_floor));
                 int neg = 0;
                 uint32_t dm = 0u;
                 tc_ld32(tmem_row + (t & 1u) * 256u + 32u, v1);
@@ -435,7 +442,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                     constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
                     const int hl = (int)(ent & 0xffffu), grp = (int)(ent >> 16), u0 = (idx % K3_SUB) * PAIRS;
                     const float4 hh = R.H[hl];
-                    const float Tf = __fmaf_rn(bc.krel, __fadd_rn(hh.z, T.ext), bc.abs_floor);
+                    const float mu = __fadd_rn(__fadd_rn(fabsf(__fsub_rn(hh.x, T.ucx)), fabsf(__fsub_rn(hh.y, T.ucy))), T.uext);
+                    const float Tf = __fmaf_rn(bc.erel, mu, __fmaf_rn(bc.kabs, __fadd_rn(hh.z, T.ext), bc.abs_floor));
                     const f32x2 hxx = pk(hh.x, hh.x), hyy = pk(hh.y, hh.y);
                     const ulonglong2 *pg = reinterpret_cast<const ulonglong2 *>(T.P) + grp * K3_GSTRIDE + 3 * u0;
                     int sure = 0;
@@ -582,18 +590,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                     }
                 }
                 // ---- pixel constants in the row's frame: FP32 (phase A) and their TF32 split as B rows ----
-                int ext = 0;
+                int ext = 0, uext = 0;
+                const int ucx = (int)((uint32_t)e0.w & 0xffffu) - ox, ucy = (int)((uint32_t)e0.w >> 16) - oy;  // the unit's centre
                 for (int j = ptid; j < nbn * TC_TILE_PX && !K3_ABL(256); j += TC_PRODS) {
                     px_consts c = never;
                     if (j < n && !K3_ABL(4)) {
                         const float4 pq = W.pq[j];
                         const uint32_t xy = W.xy[j];
                         if (pq.x != 0.f || pq.y != 0.f) {
-                            const float fx = (float)((int)(xy & 0xffffu) - ox), fy = (float)((int)(xy >> 16) - oy);
+                            const int ix = (int)(xy & 0xffffu) - ox, iy = (int)(xy >> 16) - oy;
+                            const float fx = (float)ix, fy = (float)iy;
                             c.px = pq.x; c.py = pq.y; c.qx = pq.z; c.qy = pq.w;
                             c.pz = -__fmaf_rn(fx, c.px, __fmul_rn(fy, c.py));
                             c.qz = -__fmaf_rn(fx, c.qx, __fmul_rn(fy, c.qy));
-                            ext = max(ext, (int)(fabsf(fx) + fabsf(fy)));
+                            ext = max(ext, abs(ix) + abs(iy));
+                            uext = max(uext, abs(ix - ucx) + abs(iy - ucy));
                         }
                     }
                     k3_store_px(T.P, j, c);
@@ -606,15 +617,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                     T.B[1][2 * j + 1] = make_uint4(ql, qh, rh, rl);
                 }
                 ext = __reduce_max_sync(0xffffffffu, ext);
-                if (lane == 0 && ext) atomicMax(&S.ext, ext);
+                uext = __reduce_max_sync(0xffffffffu, uext);
+                if (lane == 0 && ext) { atomicMax(&S.ext, ext); atomicMax(&S.uext, uext); }
                 if (!K3_ABL(128)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // operands visible to the tensor pipe
                 pbar();
                 if (ptid == 0) {
                     T.stop = 0; T.mbn = mbn; T.nbn = nbn; T.n = n; T.hcount = hcount; T.row = rowbuf; T.qn = 0; T.ox = ox; T.oy = oy;
                     T.last = (e1.x < 0 || next_new_row) ? 1 : 0;
                     T.cnt_row = ((long long)e0.x * d.vn + vi) * ws.hn_pad + hbase;
-                    T.ext = (float)S.ext;
-                    S.ext = 0;
+                    T.ext = (float)S.ext; T.uext = (float)S.uext; T.ucx = (float)ucx; T.ucy = (float)ucy;
+                    S.ext = 0; S.uext = 0;
                 }
                 __syncwarp();
                 if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
