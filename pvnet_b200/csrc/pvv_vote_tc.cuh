@@ -170,7 +170,7 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32])
         : "r"(taddr));
 }
 
-// One group of 16 pixels of one hypothesis: v[2i] = e+, v[2i+1] = e- of pixel i.  Adds the group's negatives (sign
+// One group of 16 pixels of one hypothesis: v[2i] = a, v[2i+1] = tau c of pixel i (m = a - |tau c|).  Adds the group's negatives (sign
 // lanes) to `neg` unless any |m| <= T, in which case only `bit` is set in `dmask`.
 __device__ __forceinline__ void tc_group(const uint32_t (&v)[32], float T, int &neg, uint32_t &dmask, uint32_t bit)
 {
@@ -188,26 +188,6 @@ __device__ __forceinline__ void tc_group(const uint32_t (&v)[32], float T, int &
     // clean group (every |m| > T): its negatives count; otherwise only its bit is set -- two predicated instructions
     asm("{\n\t.reg .pred p;\n\tsetp.gt.f32 p, %2, %3;\n\t@p add.s32 %0, %0, %4;\n\t@!p or.b32 %1, %1, %5;\n\t}"
         : "+r"(neg), "+r"(dmask) : "f"(mabs), "f"(T), "r"(g), "r"(bit));
-}
-
-// One 256-column tile of this thread's hypothesis row: wait for the accumulator, pull this warp's 64 columns into
-// registers, hand the TMEM buffer back, then vote on the two 16-pixel groups.
-__device__ __forceinline__ void tc_tile(uint32_t a_full, uint32_t a_empty, uint32_t tmem_row, uint32_t &t, int lane, float T,
-                                        int &neg, uint32_t &dm, uint32_t bit, int abl = 0)
-{
-    const uint32_t tb = t & 1u;
-    if (!(abl & 32)) tc_bar_wait(a_full + 8u * tb, (t >> 1) & 1u);
-    ++t;
-    tc_fence_after();
-    uint32_t v0[32], v1[32];
-    tc_ld32(tmem_row + tb * 256u, v0);
-    tc_ld32(tmem_row + tb * 256u + 32u, v1);
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");  // warp-collective: every lane's columns have landed
-    tc_fence_before();
-    if (lane == 0 && !(abl & 32)) tc_bar_arrive(a_empty + 8u * tb);  // the accumulator is in registers: buffer free for the next MMA
-    if (abl & 16) { neg += v0[0] ^ v1[0]; return; }
-    tc_group(v0, T, neg, dm, bit);
-    tc_group(v1, T, neg, dm, bit << 1);
 }
 
 // Pre-pass (one thread per (keypoint, pooled pixel)): the four frame-independent constants of the two linear forms
