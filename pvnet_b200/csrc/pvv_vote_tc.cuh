@@ -50,6 +50,15 @@ constexpr int TC_TILE_PX = 128;                    // pixels per MMA tile (N = 2
 constexpr int TC_TMEM_COLS = 512;                  // two accumulator buffers of 256 columns: the whole TMEM of the SM
 constexpr int TC_REGS_VOTER = 96, TC_REGS_OTHER = 48;   // setmaxnreg: 512 x 96 + 256 x 48 = 61440 = the launch allocation (768 x 80)
 constexpr long long TC_SPIN_CYCLES = 4000000000ll;  // ~2 s
+#ifndef TC_SLEEP_MMA
+#define TC_SLEEP_MMA 0
+#endif
+#ifndef TC_SLEEP_VOTER
+#define TC_SLEEP_VOTER 32
+#endif
+#ifndef TC_SLEEP_PROD
+#define TC_SLEEP_PROD 400
+#endif
 
 // One unit of work = (256-pixel chunk, keypoint, pass of <= 512 hypotheses).  Units are ordered (keypoint, pass, chunk)
 // and every CTA takes one contiguous range of them, so consecutive units of a CTA share their ROW = (image, keypoint,
@@ -128,12 +137,12 @@ __device__ __forceinline__ void tc_bar_wait_slow(uint32_t bar_saddr, uint32_t pa
         if (clock64() - t0 > TC_SPIN_CYCLES) __trap();
     }
 }
-template <int SLEEP_NS = 32>
+template <int SLEEP_NS = TC_SLEEP_VOTER>
 __device__ __forceinline__ void tc_bar_wait(uint32_t bar_saddr, uint32_t parity)
 {
     if (!tc_bar_try(bar_saddr, parity)) tc_bar_wait_slow<SLEEP_NS>(bar_saddr, parity);
 }
-template <int SLEEP_NS = 32>
+template <int SLEEP_NS = TC_SLEEP_VOTER>
 __device__ __forceinline__ void tc_bar_wait(unsigned long long *b, uint32_t parity) { tc_bar_wait<SLEEP_NS>(tc_saddr(b), parity); }
 __device__ __forceinline__ void tc_bar_arrive(uint32_t bar_saddr)
 {
@@ -374,7 +383,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                 for (uint32_t k = 0;; ++k) {
                     const uint32_t s = k % TC_STAGES;
                     tc_stage &T = S.st[s];
-                    tc_bar_wait<0>(&S.bar_ab[s], (k / TC_STAGES) & 1u);
+                    tc_bar_wait<TC_SLEEP_MMA>(&S.bar_ab[s], (k / TC_STAGES) & 1u);
                     if (T.stop) break;
                     const int mbn = T.mbn, nbn = T.nbn;
                     const tc_row &R = S.rows[T.row];
@@ -383,7 +392,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                         const uint64_t da = tc_desc(tc_saddr(&R.A[0][mb * 128]), sizeof(R.A[0]), 128);
                         for (int nb = 0; nb < nbn; ++nb, ++t) {
                             const uint32_t buf = t & 1u;
-                            if (t >= 2) tc_bar_wait<0>(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
+                            if (t >= 2) tc_bar_wait<TC_SLEEP_MMA>(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
                             tc_fence_after();
                             const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * 256]), sizeof(T.B[0]), 128);
                             asm volatile(
@@ -421,7 +430,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                 tc_stage &T = S.st[s];
                 const tc_raw &W = S.raw[u % TC_RAWS];
                 tc_row &R = S.rows[T.row];
-                tc_bar_wait<400>(&S.bar_done[s], (u / TC_STAGES) & 1u);
+                tc_bar_wait<TC_SLEEP_PROD>(&S.bar_done[s], (u / TC_STAGES) & 1u);
                 const int qtot = min(T.qn, K3_QCAP) * K3_SUB;
                 for (int idx = ptid; idx < qtot; idx += TC_PRODS) {
                     const uint32_t ent = T.q[idx / K3_SUB];
