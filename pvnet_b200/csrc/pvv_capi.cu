@@ -163,7 +163,7 @@ int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *w
     tm.mark();
     if ((e = pvv_launch_compact(d, j->mask, j->vertex, j->selection, ws, st, launches))) return fail_cuda(e);
     tm.mark();
-    if ((e = pvv_launch_hypotheses(d, j->idxs, ws, dbg ? dbg->hyp : nullptr, st, launches))) return fail_cuda(e);
+    if ((e = pvv_launch_hypotheses(d, j->idxs, ws, dbg ? dbg->hyp : nullptr, dbg ? dbg->force_exact : 0, st, launches))) return fail_cuda(e);
     tm.mark();
     if ((e = pvv_launch_count(d, ws, dbg ? dbg->force_exact : 0, st, launches))) return fail_cuda(e);
     tm.mark();

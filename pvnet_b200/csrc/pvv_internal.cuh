@@ -22,7 +22,7 @@ struct pvv_ws {
                                   //                 subsampling: the mask itself is read exactly once
     uint32_t *pix_xy;             // [cap]      x | y<<16
     float2 *pix_dir;              // [vn][cap]  raw direction vectors (SoA over keypoints)
-    float4 *pix_pq;               // [vn][cap]  frame-independent half-plane constants (tensor-pipe K3 only; k_pixel_consts)
+    float4 *pix_pq;               // [vn][cap]  frame-independent half-plane constants (tensor-pipe K3 only; written with K2)
     float2 *hyp;                  // [b][vn][hn] hypotheses
     double *fin_part;             // [b][vn][PVV_FIN_SPLIT][5] partial normal equations of the K4 splits
     int32_t *idxs_used;           // optional debug [b][hn][vn][2]
@@ -81,7 +81,7 @@ inline cudaError_t pvv_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block,
 cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float *vertex, const float *selection,
                                const pvv_ws &ws, cudaStream_t st, int *launches);
 // K2 + K3: hypotheses and fused inlier counting (pvv_vote.cu)
-cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out,
+cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out, int force_exact,
                                   cudaStream_t st, int *launches);
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches);
 // K4 / K5: finalisation (pvv_finalize.cu)

@@ -26,11 +26,9 @@
 namespace {
 
 // ---- K2 -------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out)
+__device__ __forceinline__ void hypothesis_body(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out, int img,
+                                                int e)
 {
-    pvv_pdl_enter();
-    const int img = blockIdx.y;
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= d.vn * d.hn) return;
     const int vi = e / d.hn, hi = e - vi * d.hn;
     const int tn = ws.tn[img];
@@ -59,6 +57,12 @@ __global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *i
     const long long ro = (((long long)img * d.hn + hi) * d.vn + vi) * 2;
     if (hyp_out) { hyp_out[ro] = out.x; hyp_out[ro + 1] = out.y; }
     if (ws.idxs_used) { ws.idxs_used[ro] = t0; ws.idxs_used[ro + 1] = t1; }
+}
+
+__global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out)
+{
+    pvv_pdl_enter();
+    hypothesis_body(d, idxs, ws, hyp_out, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // ---- K3 -------------------------------------------------------------------------------------------
@@ -547,15 +551,6 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 #include "pvv_vote_tc.cuh"
 }  // namespace
 
-cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out,
-                                  cudaStream_t st, int *launches)
-{
-    const dim3 grid((d.vn * d.hn + 255) / 256, d.b);
-    pvv_launch_pdl(k_hypotheses, grid, dim3(256), st, d, idxs, ws, hyp_out);
-    ++*launches;
-    return cudaGetLastError();
-}
-
 // Guard-band constants for threshold t (DESIGN.md "Guard band").  Returns false when the fast filter does
 // not apply (t outside [0.5, 0.99999]): the caller then runs the exact-only kernel.
 static bool pvv_band_for(float t, band_consts *bc, float *krel_tc)
@@ -601,17 +596,48 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
     return cudaGetLastError();
 }
 
-// tensor-pipe variant: the per-pixel constants pre-pass, then one 768-thread CTA per SM (all 512 TMEM columns), dynamic
-// shared memory, both chained by PDL like the rest
-static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, float krel_tc, int sms,
-                                   cudaStream_t st, int *launches)
+// Which kernel counts (measured, profiles/r01_sweep.md): above 256 hypotheses the tensor-pipe kernel (pvv_vote_tc.cuh:
+// tcgen05 tf32 MMA for the two linear forms, CUDA cores for the sign count and the band) is 15-20 % faster than the
+// FP32-pipe kernel; at 128 and 256 the FP32-pipe kernel with 32- / 64-thread CTAs (every thread owns 4 hypotheses, one
+// pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand staging are not amortised.
+// PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe): a tuning and test knob
+// (tools/k3_variants.py, tests/test_gpu_parity.py).  -1: the exact-only kernel.
+static int pvv_count_variant(const pvv_dims &d, int force_exact, band_consts *bc, float *krel_tc)
 {
-    const long long pblocks = (ws.cap + 255) / 256;  // grid-stride: the pixel count is only known on the device
-    const dim3 pgrid((unsigned)(pblocks < 2 * sms ? pblocks : 2 * sms), (unsigned)d.vn);
-    cudaError_t e = pvv_launch_pdl(k_pixel_consts, pgrid, dim3(256), st, d, ws, bc.tau);
-    if (e != cudaSuccess) return e;
+    if (force_exact || !pvv_band_for(d.thresh, bc, krel_tc)) return -1;
+    const char *venv = getenv("PVV_K3_VARIANT");
+    return venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
+}
+
+// K2.  When the tensor-pipe kernel will count, its per-pixel constants pre-pass rides in the same launch (independent
+// work on the same input: the two overlap instead of queueing).
+cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out, int force_exact,
+                                  cudaStream_t st, int *launches)
+{
+    band_consts bc = {};
+    float krel_tc = 0.f;
+    const int hyp_bx = (d.vn * d.hn + 255) / 256;
+    if (pvv_count_variant(d, force_exact, &bc, &krel_tc) == 7) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const long long pblocks = (ws.cap + 255) / 256;  // grid-stride: the pixel count is only known on the device
+        const int consts_bx = (int)(pblocks < 2 * sms ? pblocks : 2 * sms);
+        pvv_launch_pdl(k_hypotheses_and_consts, dim3((unsigned)(hyp_bx * d.b + consts_bx * d.vn)), dim3(256), st, d, idxs, ws,
+                       hyp_out, bc.tau, hyp_bx, consts_bx);
+    } else {
+        pvv_launch_pdl(k_hypotheses, dim3(hyp_bx, d.b), dim3(256), st, d, idxs, ws, hyp_out);
+    }
     ++*launches;
-    e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
+    return cudaGetLastError();
+}
+
+// tensor-pipe kernel: one 768-thread CTA per SM (all 512 TMEM columns), dynamic shared memory, chained by PDL like the
+// rest; its constants pre-pass ran with K2
+static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, float krel_tc, int sms,
+                                   cudaStream_t st)
+{
+    cudaError_t e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(sms);
@@ -633,15 +659,8 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {};
     float krel_tc = 0.f;
-    const bool fast = !force_exact && pvv_band_for(d.thresh, &bc, &krel_tc);
-    // Kernel by hypothesis count (measured, profiles/r01_sweep.md): above 256 hypotheses the tensor-pipe kernel
-    // (pvv_vote_tc.cuh: tcgen05 tf32 MMA for the half-plane forms, CUDA cores for min / sign count / band) is 6-13 %
-    // faster than the FP32-pipe kernel; at 128 and 256 the FP32-pipe kernel with 32- / 64-thread CTAs (every thread owns
-    // 4 hypotheses, one pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand
-    // staging are not amortised.  PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe): a tuning
-    // and test knob (tools/k3_variants.py, tests/test_gpu_parity.py).
-    const char *venv = getenv("PVV_K3_VARIANT");
-    const int variant = venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
+    const int variant = pvv_count_variant(d, force_exact, &bc, &krel_tc);
+    const bool fast = variant >= 0;
     cudaError_t e;
     if (!fast) {
         int per_sm = 8;
@@ -649,7 +668,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         pvv_launch_pdl(k_count_exact<4, 128>, dim3(sms * (per_sm < 1 ? 1 : per_sm)), dim3(128), st, d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 7) e = launch_count_tc(d, ws, bc, krel_tc, sms, st, launches);
+    else if (variant == 7) e = launch_count_tc(d, ws, bc, krel_tc, sms, st);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);

@@ -27,7 +27,7 @@
 //     registers (mbarriers full / empty; tcgen05.commit); operands are canonical K-major, non-swizzled core matrices
 //     (8 rows x 16 B; LBO = byte stride between the two K halves, SBO = between 8-row groups: verified by tc_probe.cu);
 //   * 7 producer warps (48 registers): stage the raw inputs of unit k+1 with cp.async, build the B rows of unit k
-//     (pixel constants from the k_pixel_consts pre-pass, translated into the row's frame and split), build the A rows
+//     (pixel constants from the pre-pass that rides in K2's launch, translated into the row's frame and split), build the A rows
 //     once per row, and run the deferred passes (phase A / B) of unit k-2 -- the voters never leave their loop.
 // Units are dealt as contiguous ranges in (keypoint, pass, chunk) order, so a CTA changes row ~3 times per launch.
 #pragma once
@@ -74,7 +74,7 @@ struct tc_row {
                                       // hypothesis and ROW instead of one per hypothesis, unit and voting warp
 };
 struct tc_raw {                       // raw inputs of one unit, staged by cp.async one iteration ahead
-    float4 pq[PVV_CHUNK_PX];          // frame-independent constants (k_pixel_consts)
+    float4 pq[PVV_CHUNK_PX];          // frame-independent constants (pre-pass)
     float2 dir[PVV_CHUNK_PX];         // direction vectors and coordinates (phase B)
     uint32_t xy[PVV_CHUNK_PX];
 };
@@ -203,14 +203,14 @@ __device__ __forceinline__ void tc_group(const uint32_t (&v)[32], float T, int &
 //   a = d . n^ = hx*nx + hy*ny + ra          tau c = tau (d x n^) = hx*(tau ny) + hy*(-tau nx) + rc
 // (e+- = a -+ tau c, so m = min(e+, e-) = a - |tau c|), each correctly rounded from fp64: {nx, ny, tau ny, -tau nx}.  All-zero marks a pixel the
 // reference never counts (||n|| < 1e-6, or a non-finite norm).
-__global__ void __launch_bounds__(256) k_pixel_consts(pvv_dims d, pvv_ws ws, float tau_f)
+__device__ __forceinline__ void pixel_consts_body(const pvv_dims &d, const pvv_ws &ws, float tau_f, int vi, long long first,
+                                                  long long stride)
 {
-    pvv_pdl_enter();
     const long long total = ws.img_off[d.b - 1] + ws.tn[d.b - 1];
-    const float2 *dirs = ws.pix_dir + (long long)blockIdx.y * ws.cap;
-    float4 *out = ws.pix_pq + (long long)blockIdx.y * ws.cap;
+    const float2 *dirs = ws.pix_dir + (long long)vi * ws.cap;
+    float4 *out = ws.pix_pq + (long long)vi * ws.cap;
     const double tau = (double)tau_f;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    for (long long i = first; i < total; i += stride) {
         const float2 dir = dirs[i];
         const float n1 = pvv_norm1(dir.x, dir.y);
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -220,6 +220,21 @@ __global__ void __launch_bounds__(256) k_pixel_consts(pvv_dims d, pvv_ws ws, flo
             c = make_float4((float)nx, (float)ny, (float)(tau * ny), (float)(-tau * nx));
         }
         out[i] = c;
+    }
+}
+
+// K2 and the pre-pass in one launch (1-D grid): blocks [0, hyp_bx * b) are K2's (hyp_bx per image), the next
+// consts_bx * vn blocks stride over the pooled pixels of one keypoint plane each.
+__global__ void __launch_bounds__(256) k_hypotheses_and_consts(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out,
+                                                               float tau_f, int hyp_bx, int consts_bx)
+{
+    pvv_pdl_enter();
+    const int bx = blockIdx.x;
+    if (bx < hyp_bx * d.b) {
+        hypothesis_body(d, idxs, ws, hyp_out, bx / hyp_bx, (bx % hyp_bx) * 256 + threadIdx.x);
+    } else {
+        const int cb = bx - hyp_bx * d.b;
+        pixel_consts_body(d, ws, tau_f, cb / consts_bx, (long long)(cb % consts_bx) * 256 + threadIdx.x, (long long)consts_bx * 256);
     }
 }
 
