@@ -553,7 +553,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 
 // Guard-band constants for threshold t (DESIGN.md "Guard band").  Returns false when the fast filter does
 // not apply (t outside [0.5, 0.99999]): the caller then runs the exact-only kernel.
-static bool pvv_band_for(float t, band_consts *bc, float *krel_tc)
+static bool pvv_band_for(float t, band_consts *bc)
 {
     if (!(t >= 0.5f && t <= 0.99999f)) return false;
     const double u = 5.9604644775390625e-8;  // 2^-24
@@ -574,7 +574,6 @@ static bool pvv_band_for(float t, band_consts *bc, float *krel_tc)
     // the running maximum (16u), plus the 4.5u of input / constant rounding shared with the FP32 filter: <= 31u(1+tau)M.
     // Measured on the B200 (tools/tc_probe.cu): 5.5u against the fp32 constants.  Used: 40u.
     const double kabs_tc = 40.0 * u * (1.0 + tau) * (1.0 + etau);
-    *krel_tc = (float)((erel + kabs_tc) * (1.0 + 4.0 * u));
     bc->erel = (float)(erel * (1.0 + 4.0 * u));
     bc->kabs = (float)(kabs * (1.0 + 4.0 * u));
     bc->kabs_tc = (float)(kabs_tc * (1.0 + 4.0 * u));
@@ -602,9 +601,9 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
 // pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand staging are not amortised.
 // PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe): a tuning and test knob
 // (tools/k3_variants.py, tests/test_gpu_parity.py).  -1: the exact-only kernel.
-static int pvv_count_variant(const pvv_dims &d, int force_exact, band_consts *bc, float *krel_tc)
+static int pvv_count_variant(const pvv_dims &d, int force_exact, band_consts *bc)
 {
-    if (force_exact || !pvv_band_for(d.thresh, bc, krel_tc)) return -1;
+    if (force_exact || !pvv_band_for(d.thresh, bc)) return -1;
     const char *venv = getenv("PVV_K3_VARIANT");
     return venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
 }
@@ -615,9 +614,8 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
                                   cudaStream_t st, int *launches)
 {
     band_consts bc = {};
-    float krel_tc = 0.f;
     const int hyp_bx = (d.vn * d.hn + 255) / 256;
-    if (pvv_count_variant(d, force_exact, &bc, &krel_tc) == 7) {
+    if (pvv_count_variant(d, force_exact, &bc) == 7) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -634,8 +632,7 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
 
 // tensor-pipe kernel: one 768-thread CTA per SM (all 512 TMEM columns), dynamic shared memory, chained by PDL like the
 // rest; its constants pre-pass ran with K2
-static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, float krel_tc, int sms,
-                                   cudaStream_t st)
+static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st)
 {
     cudaError_t e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
     if (e != cudaSuccess) return e;
@@ -649,7 +646,7 @@ static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const ba
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, k_count_tc, d, ws, bc, krel_tc);
+    return cudaLaunchKernelEx(&cfg, k_count_tc, d, ws, bc);
 }
 
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches)
@@ -658,8 +655,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {};
-    float krel_tc = 0.f;
-    const int variant = pvv_count_variant(d, force_exact, &bc, &krel_tc);
+    const int variant = pvv_count_variant(d, force_exact, &bc);
     const bool fast = variant >= 0;
     cudaError_t e;
     if (!fast) {
@@ -668,7 +664,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         pvv_launch_pdl(k_count_exact<4, 128>, dim3(sms * (per_sm < 1 ? 1 : per_sm)), dim3(128), st, d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 7) e = launch_count_tc(d, ws, bc, krel_tc, sms, st);
+    else if (variant == 7) e = launch_count_tc(d, ws, bc, sms, st);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);

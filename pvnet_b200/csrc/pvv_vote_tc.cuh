@@ -1,15 +1,17 @@
 // pvv_vote_tc.cuh -- K3, tensor-pipe kernel (included by pvv_vote.cu inside its anonymous namespace; shipped for hn > 256).
 //
-// The filter's two half-plane forms  e+- = hx*p + hy*q + r  are a rank-3 bilinear form in (hypothesis, pixel): per unit
-// of work an E[hypotheses x 2*pixels] matrix = H[hyp x K] . P[2*pixels x K]^T.  The FP32-pipe kernel (k_count) spends
-// 2 FFMA2 per test on it; here the 5th-generation tensor cores produce it with ONE tcgen05.mma (kind::tf32, M = 128
-// hypotheses, N = 256 columns = 128 pixels x {e+, e-}, K = 8) per tile, accumulators in TMEM, and the CUDA cores keep
-// only what is not a contraction: m = min(e+, e-), sign counting and the guard-band tracker.
+// The filter's decision quantity  m = a - tau|c|  (a = d . n^, c = d x n^, d = hypothesis - pixel; m = min(e+, e-) of the
+// FP32-pipe kernel's two half-plane forms) is built from two forms that are LINEAR in the hypothesis and in per-pixel
+// constants:  a = hx*nx + hy*ny + ra,  tau c = hx*(tau ny) + hy*(-tau nx) + rc  -- a rank-3 bilinear form in (hypothesis,
+// pixel): per unit of work an E[hypotheses x 2*pixels] matrix = H[hyp x K] . P[2*pixels x K]^T.  The FP32-pipe kernel
+// (k_count) spends 2 FFMA2 per test on it; here the 5th-generation tensor cores produce it with ONE tcgen05.mma
+// (kind::tf32, M = 128 hypotheses, N = 256 columns = 128 pixels x {a, tau c}, K = 8) per tile, accumulators in TMEM, and
+// the CUDA cores keep only what is not a contraction: m = a - |tau c| (one FADD), sign counting, the guard-band tracker.
 //
 // Precision: TF32 has an 11-bit significand, so every fp32 factor is split x = x_hi + x_lo (both exactly representable
 // in TF32) and the K = 8 slots carry the three significant cross terms of each product plus the split constant term:
 //      A row (hypothesis) = [hx_hi hx_hi hx_lo hy_hi | hy_hi hy_lo 1    1   ]
-//      B row (pixel, +-)  = [p_hi  p_lo  p_hi  q_hi  | q_lo  q_hi  r_hi r_lo]
+//      B row (pixel, form) = [p_hi  p_lo  p_hi  q_hi  | q_lo  q_hi  r_hi r_lo]      (p, q, r) = (nx, ny, ra) or (tau ny, -tau nx, rc)
 // TF32 x TF32 products are exact in the fp32 accumulator's 24 bits; what is lost is x_lo*y_lo (2^-22 relative), the
 // tail of the split (2^-23) and the accumulation rounding of the 8-term sum.  tools/tc_probe.cu measures the total on
 // the B200 in units of u(1+tau)M (u = 2^-24, M = |hx|+|hy|+P): 5.5; the guard band of this kernel is built on 40
@@ -79,14 +81,14 @@ struct tc_raw {                       // raw inputs of one unit, staged by cp.as
     uint32_t xy[PVV_CHUNK_PX];
 };
 struct tc_stage {
-    uint4 B[2][2 * PVV_CHUNK_PX];     // pixels x {+,-}, [K half][row = 2*pixel + plane]: 16 KB
+    uint4 B[2][2 * PVV_CHUNK_PX];     // pixels x {a, tau c}, [K half][row = 2*pixel + form]: 16 KB
     float P[K3_SP_FLOATS];            // FP32 constants in the FP32 kernel's pair layout (phase A)
     uint32_t q[K3_QCAP];              // flagged entries: (group << 16) | hypothesis within the pass
     long long cnt_row;                // offset of the (image, keypoint) row + pass in counts
     float ext;                        // largest |offset| of a pixel of the unit from the row's frame origin
     float ucx, ucy, uext;             // the unit's own centre (its middle pixel) in the row's frame, and the largest |offset|
                                       // of a pixel of the unit from it: |h - centre| + uext bounds ||h - pixel||
-    int qn, stop, mbn, nbn, n, hcount, row, last, ox, oy, pad;   // last: the row ends with this unit (its counts are flushed)
+    int qn, stop, mbn, nbn, n, hcount, row, last;   // last: the row ends with this unit (its counts are flushed)
 };
 struct tc_smem {
     tc_row rows[TC_ROWS];
@@ -148,7 +150,6 @@ __device__ __forceinline__ void tc_bar_arrive(uint32_t bar_saddr)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_saddr) : "memory");
 }
-__device__ __forceinline__ void tc_voters_sync() { asm volatile("bar.sync 1, %0;" ::"n"(TC_VOTERS) : "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 
@@ -238,7 +239,7 @@ __global__ void __launch_bounds__(256) k_hypotheses_and_consts(pvv_dims d, const
     }
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws ws, band_consts bc, float krel_tc)
+__global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws ws, band_consts bc)
 {
     extern __shared__ __align__(128) unsigned char tc_smem_raw[];
     tc_smem &S = *reinterpret_cast<tc_smem *>(tc_smem_raw);
@@ -637,7 +638,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws w
                 if (!K3_ABL(128)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // operands visible to the tensor pipe
                 pbar();
                 if (ptid == 0) {
-                    T.stop = 0; T.mbn = mbn; T.nbn = nbn; T.n = n; T.hcount = hcount; T.row = rowbuf; T.qn = 0; T.ox = ox; T.oy = oy;
+                    T.stop = 0; T.mbn = mbn; T.nbn = nbn; T.n = n; T.hcount = hcount; T.row = rowbuf; T.qn = 0;
                     T.last = (e1.x < 0 || next_new_row) ? 1 : 0;
                     T.cnt_row = ((long long)e0.x * d.vn + vi) * ws.hn_pad + hbase;
                     T.ext = (float)S.ext; T.uext = (float)S.uext; T.ucx = (float)ucx; T.ucy = (float)ucy;
