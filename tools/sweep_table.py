@@ -8,7 +8,8 @@ out = ["# configs[2], configs[3] (one rank's share) and the configs[4] sweep on 
        f"FP32 peak measured in the same process: {rows[0]['fp32_peak_tflops_measured']:.1f} TFLOP/s ({rows[0]['gpu']}). "
        "`frac` = K3 tests/s x 12 FLOP / that peak.",
        "`filter = exact`: counts of the guard-banded kernel equal the exact-only kernel's (checked where marked; hn = 2048 "
-       "cases are timing only). Stage times: medians of CUDA-event timings inside the C ABI.", "",
+       "cases are timing only). Stage times: medians of CUDA-event timings inside the C ABI. For hn > 256 `count` is `k_count_tc` alone: "
+       "its constants pre-pass rides in K2's launch (`hypotheses` stage, +9 us at configs[1]), so `frac` is ~3 % higher than with the pre-pass counted.", "",
        "| case | b | vn | hn | tn total | images/s | compact µs | count µs | finalize µs | K3 T tests/s | frac | in-band | filter = exact |",
        "|---|---|---|---|---|---|---|---|---|---|---|---|---|"]
 for r in rows[1:]:
