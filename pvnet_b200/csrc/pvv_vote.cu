@@ -599,7 +599,8 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
 // tcgen05 tf32 MMA for the two linear forms, CUDA cores for the sign count and the band) is 15-20 % faster than the
 // FP32-pipe kernel; at 128 and 256 the FP32-pipe kernel with 32- / 64-thread CTAs (every thread owns 4 hypotheses, one
 // pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand staging are not amortised.
-// PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe): a tuning and test knob
+// PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe, 8 / 9: tensor pipe with 7 / 3
+// producer warps): a tuning and test knob
 // (tools/k3_variants.py, tests/test_gpu_parity.py).  -1: the exact-only kernel.
 static int pvv_count_variant(const pvv_dims &d, int force_exact, band_consts *bc)
 {
@@ -615,7 +616,8 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
 {
     band_consts bc = {};
     const int hyp_bx = (d.vn * d.hn + 255) / 256;
-    if (pvv_count_variant(d, force_exact, &bc) == 7) {
+    const int cv = pvv_count_variant(d, force_exact, &bc);
+    if (cv >= 7 && cv <= 9) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -632,13 +634,14 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
 
 // tensor-pipe kernel: one 768-thread CTA per SM (all 512 TMEM columns), dynamic shared memory, chained by PDL like the
 // rest; its constants pre-pass ran with K2
+template <int PW>
 static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st)
 {
-    cudaError_t e = cudaFuncSetAttribute(k_count_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
+    cudaError_t e = cudaFuncSetAttribute(k_count_tc<PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tc_smem));
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(sms);
-    cfg.blockDim = dim3(TC_THREADS);
+    cfg.blockDim = dim3(tc_cfg<PW>::threads);
     cfg.dynamicSmemBytes = sizeof(tc_smem);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -646,7 +649,7 @@ static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const ba
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, k_count_tc, d, ws, bc);
+    return cudaLaunchKernelEx(&cfg, k_count_tc<PW>, d, ws, bc);
 }
 
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches)
@@ -664,7 +667,11 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         pvv_launch_pdl(k_count_exact<4, 128>, dim3(sms * (per_sm < 1 ? 1 : per_sm)), dim3(128), st, d, ws);
         e = cudaGetLastError();
     }
-    else if (variant == 7) e = launch_count_tc(d, ws, bc, sms, st);
+    else if (variant == 7 || variant == 8 || variant == 9) {
+        // producer warps by how often the deferred passes run (PVV_K3_VARIANT 8 / 9 force 7 / 3)
+        const bool few = variant == 9 || (variant == 7 && d.thresh <= 0.995f);
+        e = few ? launch_count_tc<3>(d, ws, bc, sms, st) : launch_count_tc<7>(d, ws, bc, sms, st);
+    }
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);

@@ -43,14 +43,22 @@
 constexpr int TC_VOTER_WARPS = 16;                 // voting warps: 4 TMEM lane quarters x 4 column quarters of a tile
 constexpr int TC_VOTERS = TC_VOTER_WARPS * 32;
 constexpr int TC_MMA_WARP = TC_VOTER_WARPS;        // one elected thread issues every tcgen05.mma
-constexpr int TC_PROD_WARPS = 7;                   // producer warps: operands of the next unit, deferred passes of the previous
-constexpr int TC_PRODS = TC_PROD_WARPS * 32;
-constexpr int TC_THREADS = TC_VOTERS + 32 + TC_PRODS;   // 768 = 6 warpgroups
+// Producer warps (operands of the next unit, deferred passes of the previous) are a template parameter PW of the kernel:
+//   PW = 7: 768 threads, launch 80 registers -> setmaxnreg voters 96 / others 48 (512 x 96 + 256 x 48 = 768 x 80);
+//   PW = 3: 640 threads, launch 96 registers -> voters 104 / others 64 (512 x 104 + 128 x 64 = 640 x 96).
+// The sums must be equal: setmaxnreg.inc waits until the CTA's pool has the registers.  Seven warps keep up with the
+// deferred passes at t = 0.999 (4.3e-4 of the tests go through them); where those are rare (t <= 0.995) three suffice and
+// the voters' 8 extra registers save them re-materialised addresses: 4 % faster (profiles/r01_k3_tc_ablation.log).
+template <int PW> struct tc_cfg {
+    static constexpr int prods = PW * 32;
+    static constexpr int threads = TC_VOTERS + 32 + PW * 32;
+    static constexpr int regs_voter = PW == 7 ? 96 : 104, regs_other = PW == 7 ? 48 : 64;
+    static_assert(PW == 7 || PW == 3, "register split worked out for 7 and 3 producer warps");
+};
 constexpr int TC_STAGES = 3;                       // unit k lives in stage k % 3: produced | voted on | deferred passes
 constexpr int TC_PASS_H = 512;                     // hypotheses per unit (4 M-blocks of 128)
 constexpr int TC_TILE_PX = 128;                    // pixels per MMA tile (N = 256 columns)
 constexpr int TC_TMEM_COLS = 512;                  // two accumulator buffers of 256 columns: the whole TMEM of the SM
-constexpr int TC_REGS_VOTER = 96, TC_REGS_OTHER = 48;   // setmaxnreg: 512 x 96 + 256 x 48 = 61440 = the launch allocation (768 x 80)
 constexpr long long TC_SPIN_CYCLES = 4000000000ll;  // ~2 s
 #ifndef TC_SLEEP_MMA
 #define TC_SLEEP_MMA 0
@@ -239,8 +247,11 @@ __global__ void __launch_bounds__(256) k_hypotheses_and_consts(pvv_dims d, const
     }
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) k_count_tc(pvv_dims d, pvv_ws ws, band_consts bc)
+template <int PW>
+__global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d, pvv_ws ws, band_consts bc)
 {
+    constexpr int TC_PROD_WARPS = PW, TC_PRODS = tc_cfg<PW>::prods, TC_THREADS = tc_cfg<PW>::threads;
+    constexpr int TC_REGS_VOTER = tc_cfg<PW>::regs_voter, TC_REGS_OTHER = tc_cfg<PW>::regs_other;
     extern __shared__ __align__(128) unsigned char tc_smem_raw[];
     tc_smem &S = *reinterpret_cast<tc_smem *>(tc_smem_raw);
     static_assert(K3_GROUP == 16 && PVV_CHUNK_PX == 256 && TC_TILE_PX == 128, "tile / group geometry");

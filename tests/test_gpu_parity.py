@@ -744,7 +744,7 @@ def test_k3_kernel_variants_agree_with_exact_kernel(monkeypatch):
                                        force_exact=True)[1]["counts"].clone() for m, v, hn, th, c in cases]
     mean = pv.ransac_voting_layer_v3(cm, cv, 512, 0.99, seed=1)
     cov_x, dbg_x = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True, force_exact=True)[1:]
-    for variant in ("0", "1", "2", "7"):
+    for variant in ("0", "1", "2", "7", "8", "9"):   # 8 / 9: the tensor-pipe kernel with 7 / 3 producer warps
         monkeypatch.setenv("PVV_K3_VARIANT", variant)
         for (m, v, hn, th, c), want in zip(cases, exact):
             got = pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True)[1]
