@@ -49,10 +49,14 @@ constexpr int TC_MMA_WARP = TC_VOTER_WARPS;        // one elected thread issues 
 // The sums must be equal: setmaxnreg.inc waits until the CTA's pool has the registers.  Seven warps keep up with the
 // deferred passes at t = 0.999 (4.3e-4 of the tests go through them); where those are rare (t <= 0.995) three suffice and
 // the voters' 8 extra registers save them re-materialised addresses: 4 % faster (profiles/r01_k3_tc_ablation.log).
+#ifndef TC_RV7
+#define TC_RV7 96
+#define TC_RO7 48
+#endif
 template <int PW> struct tc_cfg {
     static constexpr int prods = PW * 32;
     static constexpr int threads = TC_VOTERS + 32 + PW * 32;
-    static constexpr int regs_voter = PW == 7 ? 96 : 104, regs_other = PW == 7 ? 48 : 64;
+    static constexpr int regs_voter = PW == 7 ? TC_RV7 : 104, regs_other = PW == 7 ? TC_RO7 : 64;
     static_assert(PW == 7 || PW == 3, "register split worked out for 7 and 3 producer warps");
 };
 constexpr int TC_STAGES = 3;                       // unit k lives in stage k % 3: produced | voted on | deferred passes
