@@ -13,6 +13,10 @@ as the network emits it), followed for N > 1 by the NCCL all-gather of the [b,vn
 `roofline`: the fused inlier-counting kernel (K3) against the FP32 peak measured live by an FFMA probe.
 `cpu_baseline` / --impl reference: the CPU oracle (oracle/, a restatement of the reference's CUDA math -- the
             reference ships no CPU voting path) on the host cores, on a bounded sample.
+`ref_cuda_baseline`: the reference's OWN CUDA layer (oracle/_ref, built from /root/reference by oracle/build.py, driven by
+            oracle/ref_driver.py with the wrapper's per-image control flow) timed on the same GPU, same batch, same idxs,
+            outside the timed region of `value`: whole call and kernel-only, at configs[1] and at the reference's shipped
+            default (128 hypotheses, max_num 100).
 """
 from __future__ import annotations
 
@@ -31,6 +35,7 @@ if ROOT not in sys.path:
 
 B_PER_GPU, H, W, VN, HN, THRESH = 32, 480, 640, 9, 512, 0.999
 FRAC, SIGMA = 0.03, 0.05
+N_WINDOWS = 5  # timed windows of `steps` steps; the median is reported
 N_SETS = 3  # rotating input sets: ~0.87 GB each, so a step never finds its inputs in the 126 MB L2
 WORKLOAD = "configs[1]: 32x480x640 per GPU, 9 kp, 512 hyp, thresh 0.999, ~3% fg"
 FLOP_PER_TEST = 12.0  # SURVEY.md section 8(d) figure of record
@@ -97,6 +102,15 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def make_config(world):
+    """The `config` object of the JSON line: identical keys and values in both arms (ours and --impl reference)."""
+    return {"workload": WORKLOAD, "images_per_gpu": B_PER_GPU, "global_batch": world * B_PER_GPU, "h": H, "w": W, "vn": VN,
+            "hn": HN, "inlier_thresh": THRESH, "fg_fraction": FRAC, "field_noise_rad": SIGMA,
+            "cache": f"inputs larger than L2: {N_SETS} rotating input sets of ~0.87 GB",
+            "parallelism": f"dp{world} by image, no data-path collective, one packed gather of the results per step"
+                           if world > 1 else "1 GPU"}
+
+
 def _cpu_inputs(images):
     from pvnet_b200 import synth
     mask, vertex, _ = synth.make_batch(images, vn=VN, frac=FRAC, sigma=SIGMA, seed=1234)
@@ -160,12 +174,74 @@ def run_reference(args):
     line = {"metric": METRIC, "value": value, "unit": "images/s", "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": warm, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample_images_per_step": n, "h": H, "w": W, "vn": VN, "hn": HN,
-                       "inlier_thresh": THRESH},
+            "config": make_config(max(1, args.gpus)), "sample_images_per_step": n,
             "cpu_baseline": cpu,
             "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "hyp_pixel_tests_per_s": tests / dt, "gpu_launches": 0}
     _emit(line)
+
+
+def _events_ms(fn, reps, warm):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.median(ts))
+
+
+def ref_cuda_leg(pv, tm, tv, tn_total):
+    """The reference's own CUDA voting layer (src/ransac_voting_kernel.cu compiled for sm_100a into oracle/_ref, driven by
+    oracle/ref_driver.v3 = ransac_voting_gpu.py:520-604 statement by statement) on the same B200, same 32-image batch and
+    the same idxs as ours.  `whole_call`: the layer as a user calls it (per-image Python loop, host syncs, ~25 launches per
+    image).  `kernel_only`: zeros([hn,vn,tn]) + voting_for_hypothesis + sum(2) per image (:563-567), inputs prepared
+    outside the timing.  Ours is the same call through pvnet_b200 on the same tensors.  Runs after the timed regions."""
+    import torch
+    from oracle import ref_driver
+    if not ref_driver.available():
+        return {"unavailable": "oracle/_ref/ref_ransac_voting.so is absent (built from /root/reference by oracle/build.py)"}
+    rv = ref_driver.ext()
+    res = {"source": "oracle/_ref/ref_ransac_voting.so = /root/reference/lib/ransac_voting_gpu_layer/src compiled for sm_100a "
+                     "with the reference's (default) nvcc flags; driver oracle/ref_driver.py", "images": int(tm.shape[0])}
+    for tag, hn, thresh, max_num in (("configs1_512hyp_0.999", HN, THRESH, 30000), ("shipped_default_128hyp_0.99_max100", 128, 0.99, 100)):
+        out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, max_num=max_num, seed=0, return_debug=True)
+        idxs = dbg["idxs"]
+        sel = pv.make_selection(0, tm.shape[0], H, W, tm.device) if max_num < 30000 else None
+        r_out, r_dbg = ref_driver.v3(tm, tv, hn, thresh, 100, max_num, idxs, sel)
+        same = all(torch.equal(dbg["counts"][i].long(), r_dbg[i]["counts"].long()) for i in range(tm.shape[0]) if r_dbg[i] is not None)
+        tests = float(dbg["tn"].sum()) * VN * hn
+        # (no `selection=` here: the library draws the same stream from seed 0, and an injected selection makes the call
+        # synchronise to check for pool overflow)
+        ours_ms = _events_ms(lambda: pv.ransac_voting_layer_v3(tm, tv, hn, thresh, max_num=max_num, seed=0, idxs=idxs), 9, 5)
+        ref_ms = _events_ms(lambda: ref_driver.v3(tm, tv, hn, thresh, 100, max_num, idxs, sel), 5, 5)
+        prepared = [(d["direct"], d["coords"], d["hyp"]) for d in r_dbg if d is not None]
+
+        def kernels_only():
+            for direct, coords, hyp in prepared:
+                inl = torch.zeros((hn, VN, coords.shape[0]), dtype=torch.uint8, device=tm.device)
+                rv.voting_for_hypothesis(direct, coords, hyp, inl, thresh)
+                torch.sum(inl, 2)
+        k_ms = _events_ms(kernels_only, 5, 5)
+        st = []
+        for i in range(8):
+            pv.ransac_voting_layer_v3(tm, tv, hn, thresh, max_num=max_num, seed=0, idxs=idxs, stage_ms=st)
+        ours_k_ms = float(np.median([x["count"] for x in st[2:]]))
+        n = int(tm.shape[0])
+        res[tag] = {"counts_bit_equal": bool(same), "hyp_pixel_tests": tests,
+                    "reference_whole_call": {"images_per_s": n / (ref_ms * 1e-3), "ms": ref_ms},
+                    "reference_kernel_only": {"ms": k_ms, "tests_per_s": tests / (k_ms * 1e-3),
+                                              "what": "zeros + voting_for_hypothesis + sum(2) per image (ransac_voting_gpu.py:563-567)"},
+                    "ours_whole_call": {"images_per_s": n / (ours_ms * 1e-3), "ms": ours_ms},
+                    "ours_counting_kernel": {"ms": ours_k_ms, "tests_per_s": tests / (ours_k_ms * 1e-3)},
+                    "ours_over_reference_whole_call": ref_ms / ours_ms, "ours_over_reference_kernel_only": k_ms / ours_k_ms}
+    return res
 
 
 def run_ours(args):
@@ -211,20 +287,30 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record()
-    for i in range(args.steps):
-        step(i)
-    e1.record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    # N_WINDOWS timed windows of exactly `steps` steps each, every one bracketed by barrier + synchronize and timed with
+    # CUDA events on the launching stream (max over ranks); the reported value is the MEDIAN window (a single window is
+    # ~10 ms of device time: one scheduling hiccup would otherwise move the number)
+    windows = []
+    for wdw in range(N_WINDOWS):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+        e0.record()
+        for i in range(args.steps):
+            step(wdw * args.steps + i)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        wms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([wms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            wms = float(t.item())
+        windows.append(wms)
+    ms = float(np.median(windows))
     clocks = sampler.stop()
     value = world * b * args.steps / (ms * 1e-3)
 
@@ -322,19 +408,22 @@ def run_ours(args):
                "note": "pinned host tensors; mask copied, foreground vertex vectors gathered in place over PCIe"}
 
     if rank == 0:
-        cpu = None
+        cpu, ref_cuda = None, None
         if world == 1 and not args.no_cpu:
+            try:
+                ref_cuda = ref_cuda_leg(pv, sets[0][0], sets[0][1], tn_total)
+            except Exception as exc:  # the checker's reference build is optional on the box; say why it is missing
+                ref_cuda = {"unavailable": f"{type(exc).__name__}: {exc}"}
             c = cpu_leg(args.cpu_seconds)
             cpu = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")}
         line = {"metric": METRIC, "value": value, "unit": "images/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "images_per_gpu": b, "global_batch": world * b, "h": H, "w": W, "vn": VN,
-                           "hn": HN, "inlier_thresh": THRESH, "fg_pixels_per_batch": tn_total,
-                           "cache": f"inputs larger than L2: {N_SETS} rotating input sets of ~0.87 GB",
-                           "parallelism": f"dp{world} by image, one NCCL all-gather of keypoints per step" if world > 1 else "1 GPU"},
+                "config": make_config(world), "fg_pixels_per_batch": tn_total,
+                "timed_windows_ms": windows, "timed_windows_note": f"{N_WINDOWS} windows of {args.steps} steps; value = median window",
                 "hyp_pixel_tests_per_s": world * tests_per_step * args.steps / (ms * 1e-3),
-                "stage_ms": st, "pipelined": pipelined, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "stage_ms": st, "pipelined": pipelined, "roofline": roofline, "cpu_baseline": cpu, "ref_cuda_baseline": ref_cuda,
+                "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step}
         _emit(line)
     if world > 1:

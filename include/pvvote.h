@@ -34,7 +34,9 @@ typedef enum pvv_status {
     PVV_ERR_INVALID = -1,     /* bad argument (null pointer, non-positive size, unsupported dtype, thresh range) */
     PVV_ERR_WORKSPACE = -2,   /* workspace too small for pvv_workspace_bytes() of this job */
     PVV_ERR_CUDA = -3,        /* a CUDA runtime call failed; pvv_last_cuda_error() has the code */
-    PVV_ERR_UNSUPPORTED = -4  /* shape outside compiled limits (vn > 64, w or h > 65535) */
+    PVV_ERR_UNSUPPORTED = -4, /* shape outside compiled limits (vn > 64, w or h > 65535) */
+    PVV_ERR_POOL_OVERFLOW = -5 /* host-buffer entry points only (they synchronise): the compacted pixels did not fit
+                                  pool_capacity; the outputs are written, with zeros for the images that were dropped */
 } pvv_status;
 
 /* mask element types accepted (the reference takes whatever `.byte()` / `== 1` accept) */
@@ -54,9 +56,11 @@ enum {
     PVV_FG_EQ1 = 1   /* estimate_voting_distribution_with_mean: fg = (mask == 1)                     (:339-340) */
 };
 
-/* bit flags written to pvv_debug.status / workspace status word (device side, sticky) */
+/* bit flags written to pvv_job.status / pvv_debug.status (device side) */
 enum {
-    PVV_FLAG_POOL_OVERFLOW = 1 /* compacted pixels exceeded pool capacity: affected images were zeroed */
+    PVV_FLAG_POOL_OVERFLOW = 1 /* compacted pixels exceeded the pool capacity: images are admitted in batch order, one
+                                  that does not fit is dropped (zero keypoints) and takes no room, later ones that fit
+                                  are kept.  Cannot happen with the default capacity and library-drawn subsampling. */
 };
 
 /*
@@ -91,6 +95,8 @@ typedef struct pvv_job {
     void *stream;
     int32_t seg_classes;      /* PVV_MASK_LOGITS_F32 only: C */
     int64_t seg_class_stride; /* PVV_MASK_LOGITS_F32 only: stride of the class dimension, in elements */
+    int32_t *status;          /* device, optional: receives the PVV_FLAG_* bits of this call (0 = clean) on job->stream,
+                                 without a host synchronisation -- the caller reads it at its next sync point */
 } pvv_job;
 
 /* Optional device-side introspection buffers (any may be NULL); used by the parity tests. */
@@ -113,6 +119,10 @@ typedef struct pvv_debug {
     uint64_t *amb_count;  /* [1] number of tests that took the exact path */
     float *stage_ms;      /* HOST pointer [5] or NULL: device time of compaction, hypotheses, counting, finalise and the
                              whole call, from CUDA events on job->stream.  Setting it makes the call synchronise. */
+    int32_t k3_variant;   /* 0: the library picks the inlier-counting kernel; n > 0: force variant n - 1 (tests and tuning:
+                             0..6 FP32-pipe CTA shapes, 7 tensor pipe, 8 / 9 tensor pipe with a fixed builder-warp count) */
+    const float *hyp_inject; /* device [b,hn_total,vn,2] or NULL: use these hypotheses instead of intersecting pixel pairs
+                             (tests only: places hypotheses on the decision cone, tests/test_gpu_parity.py) */
 } pvv_debug;
 
 /* Scratch size for a job (depends on b,h,w,vn,hn_total,max_num,pool_capacity only). */

@@ -12,7 +12,7 @@ MASK_U8, MASK_I32, MASK_I64, MASK_F32, MASK_LOGITS_F32 = 0, 1, 2, 3, 4
 FG_BYTE, FG_EQ1 = 0, 1
 FLAG_POOL_OVERFLOW = 1
 STATUS_NAMES = {0: "PVV_OK", -1: "PVV_ERR_INVALID", -2: "PVV_ERR_WORKSPACE", -3: "PVV_ERR_CUDA",
-                -4: "PVV_ERR_UNSUPPORTED"}
+                -4: "PVV_ERR_UNSUPPORTED", -5: "PVV_ERR_POOL_OVERFLOW"}
 
 
 class Job(C.Structure):
@@ -24,6 +24,7 @@ class Job(C.Structure):
         ("idxs", C.c_void_p), ("selection", C.c_void_p), ("seed", C.c_uint64), ("image_id_base", C.c_int64),
         ("pool_capacity", C.c_int64), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("stream", C.c_void_p), ("seg_classes", C.c_int32), ("seg_class_stride", C.c_int64),
+        ("status", C.c_void_p),
     ]
 
 
@@ -33,7 +34,7 @@ class Debug(C.Structure):
         ("idxs", C.c_void_p), ("hyp", C.c_void_p), ("counts", C.c_void_p), ("win_idx", C.c_void_p),
         ("win_count", C.c_void_p), ("win_pts", C.c_void_p), ("win_inlier", C.c_void_p), ("normal_eq", C.c_void_p),
         ("status", C.c_void_p), ("pool_capacity", C.c_int64), ("force_exact", C.c_int32), ("amb_count", C.c_void_p),
-        ("stage_ms", C.c_void_p),
+        ("stage_ms", C.c_void_p), ("k3_variant", C.c_int32), ("hyp_inject", C.c_void_p),
     ]
 
 

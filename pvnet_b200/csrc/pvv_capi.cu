@@ -18,17 +18,12 @@ int fail_cuda(cudaError_t e)
     return PVV_ERR_CUDA;
 }
 
-int validate(const pvv_job *j)
+// pvv_job.status: the call's PVV_FLAG_* bits, copied on the job's stream (no host synchronisation)
+cudaError_t export_status(const pvv_job *j, const pvv_ws &ws)
 {
-    if (!j || !j->mask || !j->vertex || !j->workspace) return PVV_ERR_INVALID;
-    if (j->b <= 0 || j->h <= 0 || j->w <= 0 || j->vn <= 0 || j->hn_total <= 0) return PVV_ERR_INVALID;
-    if (j->mask_dtype < PVV_MASK_U8 || j->mask_dtype > PVV_MASK_LOGITS_F32) return PVV_ERR_INVALID;
-    if (j->mask_dtype == PVV_MASK_LOGITS_F32 && j->seg_classes < 1) return PVV_ERR_INVALID;
-    if (j->fg_rule != PVV_FG_BYTE && j->fg_rule != PVV_FG_EQ1) return PVV_ERR_INVALID;
-    if (!(j->inlier_thresh == j->inlier_thresh)) return PVV_ERR_INVALID;
-    if (j->vn > PVV_MAX_VN || j->h > 65535 || j->w > 65535 || (long long)j->h * j->w > (1LL << 23) || j->b > 65535)
-        return PVV_ERR_UNSUPPORTED;
-    return PVV_OK;
+    if (!j->status) return cudaSuccess;
+    return cudaMemcpyAsync(j->status, &ws.counters[PVV_CTR_STATUS], sizeof(int32_t), cudaMemcpyDeviceToDevice,
+                           (cudaStream_t)j->stream);
 }
 
 long long default_cap(const pvv_job *j)
@@ -40,8 +35,29 @@ long long default_cap(const pvv_job *j)
         const long long bound = (long long)j->max_num + (long long)(8.0 * sqrt((double)j->max_num)) + 256;
         per = bound < npx ? bound : npx;
     }
-    long long cap = per * j->b;
-    return (cap + 63) / 64 * 64;
+    return per * j->b;
+}
+
+// pool pixels allocated for a requested capacity: every image may lose up to PVV_POOL_ALIGN - 1 pixels to the alignment
+// of its start, and the bulk copies of K3 read whole 16-byte units past a chunk's last pixel
+long long pool_alloc(const pvv_job *j)
+{
+    const long long want = j->pool_capacity > 0 ? j->pool_capacity : default_cap(j);
+    return (want + (long long)PVV_POOL_ALIGN * (j->b + 1) + 63) / 64 * 64;
+}
+
+int validate(const pvv_job *j)
+{
+    if (!j || !j->mask || !j->vertex || !j->workspace) return PVV_ERR_INVALID;
+    if (j->b <= 0 || j->h <= 0 || j->w <= 0 || j->vn <= 0 || j->hn_total <= 0) return PVV_ERR_INVALID;
+    if (j->mask_dtype < PVV_MASK_U8 || j->mask_dtype > PVV_MASK_LOGITS_F32) return PVV_ERR_INVALID;
+    if (j->mask_dtype == PVV_MASK_LOGITS_F32 && j->seg_classes < 1) return PVV_ERR_INVALID;
+    if (j->fg_rule != PVV_FG_BYTE && j->fg_rule != PVV_FG_EQ1) return PVV_ERR_INVALID;
+    if (!(j->inlier_thresh == j->inlier_thresh)) return PVV_ERR_INVALID;
+    if (j->vn > PVV_MAX_VN || j->h > 65535 || j->w > 65535 || (long long)j->h * j->w > (1LL << 23) || j->b > 65535)
+        return PVV_ERR_UNSUPPORTED;
+    if (pool_alloc(j) >= (1LL << 31)) return PVV_ERR_UNSUPPORTED;  // pool pixel indices are 32-bit
+    return PVV_OK;
 }
 
 struct layout {
@@ -54,7 +70,7 @@ struct layout {
 layout make_layout(const pvv_job *j)
 {
     layout L;
-    L.cap = j->pool_capacity > 0 ? (j->pool_capacity + 63) / 64 * 64 : default_cap(j);
+    L.cap = pool_alloc(j);
     L.ntiles = (int)(((long long)j->h * j->w + PVV_TILE_PX - 1) / PVV_TILE_PX);
     L.hn_pad = (j->hn_total + 3) / 4 * 4;
     size_t o = 0;
@@ -163,9 +179,11 @@ int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *w
     tm.mark();
     if ((e = pvv_launch_compact(d, j->mask, j->vertex, j->selection, ws, st, launches))) return fail_cuda(e);
     tm.mark();
-    if ((e = pvv_launch_hypotheses(d, j->idxs, ws, dbg ? dbg->hyp : nullptr, dbg ? dbg->force_exact : 0, st, launches))) return fail_cuda(e);
+    const int force_exact = dbg ? dbg->force_exact : 0, k3_variant = dbg ? dbg->k3_variant : 0;
+    if ((e = pvv_launch_hypotheses(d, j->idxs, ws, dbg ? dbg->hyp : nullptr, force_exact, k3_variant,
+                                   dbg ? dbg->hyp_inject : nullptr, st, launches))) return fail_cuda(e);
     tm.mark();
-    if ((e = pvv_launch_count(d, ws, dbg ? dbg->force_exact : 0, st, launches))) return fail_cuda(e);
+    if ((e = pvv_launch_count(d, ws, force_exact, k3_variant, st, launches))) return fail_cuda(e);
     tm.mark();
     *d_out = d;
     *ws_out = ws;
@@ -183,7 +201,7 @@ int pvv_last_cuda_error(void) { return t_last_cuda_error; }
 int64_t pvv_default_pool_capacity(const pvv_job *job)
 {
     if (!job || job->b <= 0 || job->h <= 0 || job->w <= 0) return 0;
-    return job->pool_capacity > 0 ? (job->pool_capacity + 63) / 64 * 64 : default_cap(job);
+    return pool_alloc(job);
 }
 
 size_t pvv_workspace_bytes(const pvv_job *job)
@@ -206,6 +224,7 @@ static int run_v3(const pvv_job *job, float *out_kp, float *out_conf, const pvv_
     if ((e = pvv_launch_v3_finalize(d, ws, out_kp, out_conf, dbg, st, &launches))) return fail_cuda(e);
     tm.mark();
     tm.finish();
+    if ((e = export_status(job, ws))) return fail_cuda(e);
     if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
     t_last_launches = launches;
     return PVV_OK;
@@ -241,6 +260,7 @@ int pvv_hypotheses(const pvv_job *job, float *out_hyp, int32_t *out_counts, cons
     cudaStream_t st = (cudaStream_t)job->stream;
     cudaError_t e;
     if ((e = pvv_launch_export_counts(d, ws, out_counts, st, &launches))) return fail_cuda(e);
+    if ((e = export_status(job, ws))) return fail_cuda(e);
     local.counts = nullptr;
     if (dbg && (e = pvv_launch_debug_export(d, ws, &local, st, &launches))) return fail_cuda(e);
     t_last_launches = launches;
@@ -267,6 +287,7 @@ int pvv_motion(const pvv_job *job, float *out_kp)
     if (e) return fail_cuda(e);
     if ((e = pvv_launch_compact(d, j.mask, j.vertex, nullptr, ws, st, &launches))) return fail_cuda(e);
     if ((e = pvv_launch_motion_mean(d, ws, out_kp, st, &launches))) return fail_cuda(e);
+    if ((e = export_status(&j, ws))) return fail_cuda(e);
     t_last_launches = launches;
     return PVV_OK;
 }
@@ -286,6 +307,7 @@ int pvv_cov(const pvv_job *job, const float *mean, float *out_cov, const pvv_deb
     if ((e = pvv_launch_cov_finalize(d, ws, mean, out_cov, st, &launches))) return fail_cuda(e);
     tm.mark();
     tm.finish();
+    if ((e = export_status(job, ws))) return fail_cuda(e);
     if ((e = pvv_launch_debug_export(d, ws, dbg, st, &launches))) return fail_cuda(e);
     t_last_launches = launches;
     return PVV_OK;

@@ -8,6 +8,8 @@
 #define PVV_MAX_VN 64
 #define PVV_TILE_PX 1024   // pixels per compaction tile (K1)
 #define PVV_CHUNK_PX 256   // pixels per voting work item (K3)
+#define PVV_POOL_ALIGN 16  // every image starts on a multiple of this many pixels in the pool: the SoA rows of a voting
+                           // chunk (4 / 8 / 16 bytes per pixel) are then 16-byte aligned sources for bulk copies (TMA)
 #ifndef PVV_FIN_SPLIT
 #define PVV_FIN_SPLIT 4     // CTAs sharing the pixels of one (image, keypoint) in K4
 #endif
@@ -128,5 +130,8 @@ __device__ __forceinline__ uint32_t pvv_mask_value(const void *mask, int dtype, 
     if (fg_rule == PVV_FG_EQ1) return v == 1 ? 1u : 0u;
     return (uint32_t)(v & 0xFF);
 }
+
+// pool pixels an image of n compacted pixels occupies (its start is aligned, see PVV_POOL_ALIGN)
+__host__ __device__ __forceinline__ int pvv_pool_span(int n) { return (n + PVV_POOL_ALIGN - 1) & ~(PVV_POOL_ALIGN - 1); }
 
 struct pvv_ws;  // workspace view, pvv_capi.cu

@@ -194,23 +194,47 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
     if (!s_last) return;
     __threadfence();
 
+    // Pool overflow (a user-set pool_capacity that is too small, or an injected `selection` that keeps far more than
+    // max_num pixels): images are admitted greedily in batch order; one that does not fit is dropped (zero keypoints,
+    // PVV_IMG_OVERFLOW) and takes no room, so every later image that still fits is kept.  Sequential, but b is small and
+    // this only runs when the batch as a whole does not fit.
+    __shared__ long long s_need;
+    if (threadIdx.x == 0) s_need = 0;
+    __syncthreads();
+    {
+        long long need = 0;
+        for (int i = threadIdx.x; i < d.b; i += kThreads) need += pvv_pool_span(((volatile int *)ws.tn)[i]);
+        if (need) atomicAdd((unsigned long long *)&s_need, (unsigned long long)need);
+    }
+    __syncthreads();
+    if (s_need > ws.cap) {
+        if (threadIdx.x == 0) {
+            long long used = 0;
+            for (int i = 0; i < d.b; ++i) {
+                const long long span = pvv_pool_span(((volatile int *)ws.tn)[i]);
+                if (used + span > ws.cap) {
+                    ws.img_flags[i] |= PVV_IMG_OVERFLOW | PVV_IMG_SKIPPED;
+                    ws.tn[i] = 0;
+                } else {
+                    used += span;
+                }
+            }
+            atomicOr(&ws.counters[PVV_CTR_STATUS], (unsigned)PVV_FLAG_POOL_OVERFLOW);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+
     // batch-level scan: pool offsets and voting-chunk ranges.  b is small; chunks of kThreads with a carry.
     long long off = 0;
     int chunk = 0;
     for (int base = 0; base < d.b; base += kThreads) {
         const int i = base + threadIdx.x;
-        int n = i < d.b ? ((volatile int *)ws.tn)[i] : 0;
-        // prefix of n (pixels) -- int is enough per 256 images of <= 2^31/256... keep it safe with two scans
+        const int n = i < d.b ? ((volatile int *)ws.tn)[i] : 0;
+        // every image starts on a PVV_POOL_ALIGN-pixel boundary of the pool (16-byte aligned bulk copies in K3)
         int total_n;
-        const int ex_n = block_excl_scan(n, &total_n);
-        long long my_off = off + ex_n;
-        if (i < d.b && my_off + n > ws.cap) {  // pool overflow: drop the image, flag it
-            atomicOr(&ws.counters[PVV_CTR_STATUS], (unsigned)PVV_FLAG_POOL_OVERFLOW);
-            ws.img_flags[i] |= PVV_IMG_OVERFLOW | PVV_IMG_SKIPPED;
-            ws.tn[i] = 0;
-            n = 0;
-            my_off = my_off > ws.cap ? ws.cap : my_off;
-        }
+        const int ex_n = block_excl_scan(pvv_pool_span(n), &total_n);
+        const long long my_off = off + ex_n;
         const int c = (n + PVV_CHUNK_PX - 1) / PVV_CHUNK_PX;
         int total_c;
         const int ex_c = block_excl_scan(c, &total_c);

@@ -35,7 +35,7 @@ bool is_pinned(const void *p, void **dev_ptr)
 }
 
 struct host_plan {
-    size_t dev_ws, o_mask, o_vertex, o_idxs, o_sel, o_mean, o_out, o_tn, total;
+    size_t dev_ws, o_mask, o_vertex, o_idxs, o_sel, o_mean, o_out, o_tn, o_status, total;
     long long mask_span, vertex_span;
     bool vertex_zero_copy;
     void *vertex_dev;
@@ -62,16 +62,18 @@ int plan_host(const pvv_job *j, host_plan *P)
     P->o_mean = take(sizeof(float) * (size_t)j->b * j->vn * 2);
     P->o_out = take(sizeof(float) * (size_t)j->b * j->vn * 4);
     P->o_tn = take(sizeof(int) * (size_t)j->b);
+    P->o_status = take(sizeof(int32_t) * 4);   // one PVV_FLAG_* word per sub-batch
     P->total = o;
     return PVV_OK;
 }
 
 // One sub-batch [i0, i1) of the job on the compute stream; device-side inputs already point at the full arrays.
 int run_sub(const pvv_job &dj, int i0, int i1, bool cov, float confidence, int max_iter, const float *mean_dev,
-            float *out_dev, int *tn_dev)
+            float *out_dev, int *tn_dev, int32_t *status_dev)
 {
     pvv_job sj = dj;
     sj.b = i1 - i0;
+    sj.status = status_dev;
     sj.mask = (const char *)dj.mask + (size_t)i0 * dj.mask_strides[0] * mask_elem(dj.mask_dtype);
     sj.vertex = dj.vertex + (long long)i0 * dj.vertex_strides[0];
     if (dj.idxs) sj.idxs = dj.idxs + (size_t)i0 * dj.hn_total * dj.vn * 2;
@@ -140,11 +142,13 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     }
     float *out_dev = (float *)(base + P.o_out);
     int *tn_dev = (int *)(base + P.o_tn);
+    int32_t *status_dev = (int32_t *)(base + P.o_status);
+    if ((e = cudaMemsetAsync(status_dev, 0, sizeof(int32_t) * 4, st))) return PVV_ERR_CUDA;
     const size_t out_bytes = sizeof(float) * (size_t)j->b * j->vn * (cov ? 4 : 2);
 
     if (nsub == 1) {
         if ((e = cudaMemcpyAsync(base + P.o_mask, j->mask, mbytes, cudaMemcpyHostToDevice, st))) return PVV_ERR_CUDA;
-        r = run_sub(dj, 0, j->b, cov, confidence, max_iter, mean_dev, out_dev, tn_dev);
+        r = run_sub(dj, 0, j->b, cov, confidence, max_iter, mean_dev, out_dev, tn_dev, status_dev);
         if (r != PVV_OK) return r;
     } else {
         cudaStream_t cs = nullptr;
@@ -165,7 +169,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
         for (int s = 0; ok && r == PVV_OK && s < nsub; ++s) {
             const int i0 = (int)((long long)j->b * s / nsub), i1 = (int)((long long)j->b * (s + 1) / nsub);
             ok = cudaStreamWaitEvent(st, ev[s], 0) == cudaSuccess;
-            if (ok) r = run_sub(dj, i0, i1, cov, confidence, max_iter, mean_dev, out_dev, tn_dev);
+            if (ok) r = run_sub(dj, i0, i1, cov, confidence, max_iter, mean_dev, out_dev, tn_dev, status_dev + s);
         }
         // destroying an event / a stream with work in flight is legal: the resources go away when that work completes,
         // and the caller's stream already waits on every copy through the events
@@ -176,6 +180,9 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     }
     if ((e = cudaMemcpyAsync(out_host, out_dev, out_bytes, cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
     d2h += (int64_t)out_bytes;
+    int32_t status_host[4] = {0, 0, 0, 0};
+    if ((e = cudaMemcpyAsync(status_host, status_dev, sizeof(status_host), cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
+    d2h += (int64_t)sizeof(status_host);
     if (P.vertex_zero_copy && h2d_bytes) {
         // account the foreground vectors the scatter kernel pulled over the bus: sum(tn) * vn * 8 bytes
         int *tn_host = (int *)malloc(sizeof(int) * j->b);
@@ -193,6 +200,8 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     }
     if (h2d_bytes) *h2d_bytes = h2d;
     if (d2h_bytes) *d2h_bytes = d2h;
+    // the call has synchronised: a pool overflow (user-set pool_capacity too small) is reported, not silent
+    if ((status_host[0] | status_host[1] | status_host[2] | status_host[3]) & PVV_FLAG_POOL_OVERFLOW) return PVV_ERR_POOL_OVERFLOW;
     return PVV_OK;
 }
 

@@ -82,8 +82,9 @@ cudaError_t pvv_launch_compact(const pvv_dims &d, const void *mask, const float 
                                const pvv_ws &ws, cudaStream_t st, int *launches);
 // K2 + K3: hypotheses and fused inlier counting (pvv_vote.cu)
 cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out, int force_exact,
-                                  cudaStream_t st, int *launches);
-cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches);
+                                  int k3_variant, const float *hyp_inject, cudaStream_t st, int *launches);
+cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, int k3_variant, cudaStream_t st,
+                             int *launches);
 // K4 / K5: finalisation (pvv_finalize.cu)
 cudaError_t pvv_launch_v3_finalize(const pvv_dims &d, const pvv_ws &ws, float *out_kp, float *out_conf,
                                    const pvv_debug *dbg, cudaStream_t st, int *launches);

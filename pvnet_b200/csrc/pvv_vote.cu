@@ -27,7 +27,7 @@ namespace {
 
 // ---- K2 -------------------------------------------------------------------------------------------
 __device__ __forceinline__ void hypothesis_body(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out, int img,
-                                                int e)
+                                                int e, const float *hyp_inject = nullptr)
 {
     if (e >= d.vn * d.hn) return;
     const int vi = e / d.hn, hi = e - vi * d.hn;
@@ -42,7 +42,10 @@ __device__ __forceinline__ void hypothesis_body(const pvv_dims &d, const int32_t
         } else {
             pvv_draw_pair(d.seed, d.image_id_base + img, hi, vi, d.vn, tn, t0, t1);
         }
-        if ((unsigned)t0 < (unsigned)tn && (unsigned)t1 < (unsigned)tn) {
+        if (hyp_inject) {  // tests only (pvv_debug.hyp_inject): hypotheses placed by the caller
+            const long long o = (((long long)img * d.hn + hi) * d.vn + vi) * 2;
+            out = make_float2(hyp_inject[o], hyp_inject[o + 1]);
+        } else if ((unsigned)t0 < (unsigned)tn && (unsigned)t1 < (unsigned)tn) {
             const long long off = ws.img_off[img];
             const uint32_t xy0 = ws.pix_xy[off + t0], xy1 = ws.pix_xy[off + t1];
             const float2 d0 = ws.pix_dir[(long long)vi * ws.cap + off + t0];
@@ -59,10 +62,11 @@ __device__ __forceinline__ void hypothesis_body(const pvv_dims &d, const int32_t
     if (ws.idxs_used) { ws.idxs_used[ro] = t0; ws.idxs_used[ro + 1] = t1; }
 }
 
-__global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out)
+__global__ void __launch_bounds__(256) k_hypotheses(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out,
+                                                    const float *hyp_inject)
 {
     pvv_pdl_enter();
-    hypothesis_body(d, idxs, ws, hyp_out, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x);
+    hypothesis_body(d, idxs, ws, hyp_out, blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x, hyp_inject);
 }
 
 // ---- K3 -------------------------------------------------------------------------------------------
@@ -599,24 +603,23 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
 // tcgen05 tf32 MMA for the two linear forms, CUDA cores for the sign count and the band) is 15-20 % faster than the
 // FP32-pipe kernel; at 128 and 256 the FP32-pipe kernel with 32- / 64-thread CTAs (every thread owns 4 hypotheses, one
 // pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand staging are not amortised.
-// PVV_K3_VARIANT overrides the choice (0..6: FP32-pipe shapes, 7: tensor pipe, 8 / 9: tensor pipe with 7 / 3
-// producer warps): a tuning and test knob
-// (tools/k3_variants.py, tests/test_gpu_parity.py).  -1: the exact-only kernel.
-static int pvv_count_variant(const pvv_dims &d, int force_exact, band_consts *bc)
+// pvv_debug.k3_variant overrides the choice (n > 0 forces variant n - 1; 0..6: FP32-pipe shapes, 7: tensor pipe, 8 / 9:
+// tensor pipe with 7 / 3 producer warps): a tuning and test knob (tools/k3_variants.py, tests/test_gpu_parity.py).
+// -1: the exact-only kernel.
+static int pvv_count_variant(const pvv_dims &d, int force_exact, int k3_variant, band_consts *bc)
 {
     if (force_exact || !pvv_band_for(d.thresh, bc)) return -1;
-    const char *venv = getenv("PVV_K3_VARIANT");
-    return venv ? atoi(venv) : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
+    return k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
 }
 
 // K2.  When the tensor-pipe kernel will count, its per-pixel constants pre-pass rides in the same launch (independent
 // work on the same input: the two overlap instead of queueing).
 cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const pvv_ws &ws, float *hyp_out, int force_exact,
-                                  cudaStream_t st, int *launches)
+                                  int k3_variant, const float *hyp_inject, cudaStream_t st, int *launches)
 {
     band_consts bc = {};
     const int hyp_bx = (d.vn * d.hn + 255) / 256;
-    const int cv = pvv_count_variant(d, force_exact, &bc);
+    const int cv = pvv_count_variant(d, force_exact, k3_variant, &bc);
     if (cv >= 7 && cv <= 9) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
@@ -624,9 +627,9 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
         const long long pblocks = (ws.cap + 255) / 256;  // grid-stride: the pixel count is only known on the device
         const int consts_bx = (int)(pblocks < 2 * sms ? pblocks : 2 * sms);
         pvv_launch_pdl(k_hypotheses_and_consts, dim3((unsigned)(hyp_bx * d.b + consts_bx * d.vn)), dim3(256), st, d, idxs, ws,
-                       hyp_out, bc.tau, hyp_bx, consts_bx);
+                       hyp_out, hyp_inject, bc.tau, hyp_bx, consts_bx);
     } else {
-        pvv_launch_pdl(k_hypotheses, dim3(hyp_bx, d.b), dim3(256), st, d, idxs, ws, hyp_out);
+        pvv_launch_pdl(k_hypotheses, dim3(hyp_bx, d.b), dim3(256), st, d, idxs, ws, hyp_out, hyp_inject);
     }
     ++*launches;
     return cudaGetLastError();
@@ -652,13 +655,14 @@ static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const ba
     return cudaLaunchKernelEx(&cfg, k_count_tc<PW>, d, ws, bc);
 }
 
-cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, cudaStream_t st, int *launches)
+cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, int k3_variant, cudaStream_t st,
+                             int *launches)
 {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {};
-    const int variant = pvv_count_variant(d, force_exact, &bc);
+    const int variant = pvv_count_variant(d, force_exact, k3_variant, &bc);
     const bool fast = variant >= 0;
     cudaError_t e;
     if (!fast) {

@@ -63,7 +63,7 @@ constexpr int TC_STAGES = 3;                       // unit k lives in stage k % 
 constexpr int TC_PASS_H = 512;                     // hypotheses per unit (4 M-blocks of 128)
 constexpr int TC_TILE_PX = 128;                    // pixels per MMA tile (N = 256 columns)
 constexpr int TC_TMEM_COLS = 512;                  // two accumulator buffers of 256 columns: the whole TMEM of the SM
-constexpr long long TC_SPIN_CYCLES = 4000000000ll;  // ~2 s
+constexpr uint32_t TC_SPIN_ROUNDS = 1u << 22;       // x 64 polls: seconds of continuous polling by one warp
 #ifndef TC_SLEEP_MMA
 #define TC_SLEEP_MMA 0
 #endif
@@ -127,7 +127,7 @@ __device__ __forceinline__ void tc_bar_arrive(unsigned long long *b)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc_saddr(b)) : "memory");
 }
-// Bounded wait: in a correct run the limit (seconds) is never reached; a broken pipeline traps instead of hanging the GPU.
+// Bounded wait: in a correct run the limit is never reached; a broken pipeline traps instead of hanging the GPU.
 __device__ __forceinline__ uint32_t tc_bar_try(uint32_t bar_saddr, uint32_t parity)
 {
     uint32_t done;
@@ -141,14 +141,17 @@ __device__ __forceinline__ uint32_t tc_bar_try(uint32_t bar_saddr, uint32_t pari
 template <int SLEEP_NS>
 __device__ __forceinline__ void tc_bar_wait_slow(uint32_t bar_saddr, uint32_t parity)
 {
-    const long long t0 = clock64();
-    for (;;) {
+    // The bound counts THIS warp's polls, not wall-clock cycles: a context that is time-sliced out (another process on the
+    // GPU, MPS, a debugger) does not advance it, so a correct run cannot trip it.  A legitimate wait lasts microseconds.
+    for (uint32_t rounds = 0;; ++rounds) {
 #pragma unroll 1
         for (int i = 0; i < 64; ++i) {
             if (tc_bar_try(bar_saddr, parity)) return;
             if (SLEEP_NS) __nanosleep(SLEEP_NS);
         }
-        if (clock64() - t0 > TC_SPIN_CYCLES) __trap();
+#ifndef PVV_NO_WATCHDOG
+        if (rounds > TC_SPIN_ROUNDS) __trap();
+#endif
     }
 }
 template <int SLEEP_NS = TC_SLEEP_VOTER>
@@ -239,12 +242,12 @@ __device__ __forceinline__ void pixel_consts_body(const pvv_dims &d, const pvv_w
 // K2 and the pre-pass in one launch (1-D grid): blocks [0, hyp_bx * b) are K2's (hyp_bx per image), the next
 // consts_bx * vn blocks stride over the pooled pixels of one keypoint plane each.
 __global__ void __launch_bounds__(256) k_hypotheses_and_consts(pvv_dims d, const int32_t *idxs, pvv_ws ws, float *hyp_out,
-                                                               float tau_f, int hyp_bx, int consts_bx)
+                                                               const float *hyp_inject, float tau_f, int hyp_bx, int consts_bx)
 {
     pvv_pdl_enter();
     const int bx = blockIdx.x;
     if (bx < hyp_bx * d.b) {
-        hypothesis_body(d, idxs, ws, hyp_out, bx / hyp_bx, (bx % hyp_bx) * 256 + threadIdx.x);
+        hypothesis_body(d, idxs, ws, hyp_out, bx / hyp_bx, (bx % hyp_bx) * 256 + threadIdx.x, hyp_inject);
     } else {
         const int cb = bx - hyp_bx * d.b;
         pixel_consts_body(d, ws, tau_f, cb / consts_bx, (long long)(cb % consts_bx) * 256 + threadIdx.x, (long long)consts_bx * 256);

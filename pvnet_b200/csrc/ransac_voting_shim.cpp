@@ -9,6 +9,8 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
 
+#include <atomic>
+#include <random>
 #include <tuple>
 
 #include "../../include/pvvote.h"
@@ -25,6 +27,17 @@ void check_status(int st, const char *what)
 {
     TORCH_CHECK(st == PVV_OK, what, " failed with pvv_status ", st, st == PVV_ERR_CUDA ? " cudaError " : "",
                 st == PVV_ERR_CUDA ? std::to_string(pvv_last_cuda_error()) : std::string());
+}
+
+// `seed=None` means a fresh draw stream per call, like the reference's .random_() (ransac_voting_gpu.py:553): a process-local
+// counter, started from std::random_device, hashed (splitmix64).  The user's torch RNG state is not touched.
+int64_t fresh_seed()
+{
+    static std::atomic<uint64_t> ctr{((uint64_t)std::random_device{}() << 32) ^ (uint64_t)std::random_device{}()};
+    uint64_t z = ctr.fetch_add(0x9E3779B97F4A7C15ull) + 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return (int64_t)((z ^ (z >> 31)) >> 2);
 }
 
 void *cur_stream(const at::Tensor &t) { return (void *)c10::cuda::getCurrentCUDAStream(t.get_device()).stream(); }
@@ -165,11 +178,11 @@ void voting_for_hypothesis_vanishing_point(at::Tensor direct, at::Tensor coords,
 // ransac_voting_gpu.py:520-604 as one call
 at::Tensor ransac_voting_layer_v3(at::Tensor mask, at::Tensor vertex, int64_t round_hyp_num, double inlier_thresh,
                                   double confidence, int64_t max_iter, int64_t min_num, int64_t max_num,
-                                  c10::optional<at::Tensor> idxs, c10::optional<at::Tensor> selection, int64_t seed,
-                                  int64_t image_id_base)
+                                  c10::optional<at::Tensor> idxs, c10::optional<at::Tensor> selection,
+                                  c10::optional<int64_t> seed, int64_t image_id_base)
 {
-    pvv_job j = make_job(mask, vertex, round_hyp_num, inlier_thresh, min_num, max_num, PVV_FG_BYTE, idxs, selection, seed,
-                         image_id_base);
+    pvv_job j = make_job(mask, vertex, round_hyp_num, inlier_thresh, min_num, max_num, PVV_FG_BYTE, idxs, selection,
+                         seed.has_value() ? *seed : fresh_seed(), image_id_base);
     const c10::cuda::CUDAGuard guard(mask.device());
     j.stream = cur_stream(mask);
     auto ws = at::empty({(int64_t)pvv_workspace_bytes(&j)}, mask.options().dtype(at::kByte));
@@ -183,12 +196,12 @@ at::Tensor ransac_voting_layer_v3(at::Tensor mask, at::Tensor vertex, int64_t ro
 // ransac_voting_gpu.py:333-406 as one call
 std::tuple<at::Tensor, at::Tensor> estimate_voting_distribution_with_mean(
     at::Tensor mask, at::Tensor vertex, at::Tensor mean, int64_t round_hyp_num, int64_t min_hyp_num, double inlier_thresh,
-    int64_t min_num, int64_t max_num, c10::optional<at::Tensor> idxs, c10::optional<at::Tensor> selection, int64_t seed,
-    int64_t image_id_base)
+    int64_t min_num, int64_t max_num, c10::optional<at::Tensor> idxs, c10::optional<at::Tensor> selection,
+    c10::optional<int64_t> seed, int64_t image_id_base)
 {
     const int64_t rounds = (min_hyp_num + round_hyp_num - 1) / round_hyp_num;
     pvv_job j = make_job(mask, vertex, rounds * round_hyp_num, inlier_thresh, min_num, max_num, PVV_FG_EQ1, idxs, selection,
-                         seed, image_id_base);
+                         seed.has_value() ? *seed : fresh_seed(), image_id_base);
     const c10::cuda::CUDAGuard guard(mask.device());
     j.stream = cur_stream(mask);
     auto mean_c = mean.to(vertex.options()).contiguous();
@@ -211,10 +224,10 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("ransac_voting_layer_v3", &ransac_voting_layer_v3, "fused v3", py::arg("mask"), py::arg("vertex"),
           py::arg("round_hyp_num"), py::arg("inlier_thresh") = 0.99, py::arg("confidence") = 0.99, py::arg("max_iter") = 100,
           py::arg("min_num") = 100, py::arg("max_num") = 30000, py::arg("idxs") = py::none(),
-          py::arg("selection") = py::none(), py::arg("seed") = 0, py::arg("image_id_base") = 0);
+          py::arg("selection") = py::none(), py::arg("seed") = py::none(), py::arg("image_id_base") = 0);
     m.def("estimate_voting_distribution_with_mean", &estimate_voting_distribution_with_mean, "fused distribution",
           py::arg("mask"), py::arg("vertex"), py::arg("mean"), py::arg("round_hyp_num") = 256,
           py::arg("min_hyp_num") = 4096, py::arg("inlier_thresh") = 0.99, py::arg("min_num") = 20,
           py::arg("max_num") = 30000, py::arg("idxs") = py::none(), py::arg("selection") = py::none(),
-          py::arg("seed") = 0, py::arg("image_id_base") = 0);
+          py::arg("seed") = py::none(), py::arg("image_id_base") = 0);
 }

@@ -43,10 +43,34 @@ def gather_packed(local: torch.Tensor, global_b: int, group=None) -> torch.Tenso
     return torch.cat(parts, 0)
 
 
-def ransac_voting_layer_v3_sharded(mask_local, vertex_local, round_hyp_num, global_b, *, group=None, seed=0,
+def _shared_seed(seed, group, device):
+    """seed=None: a fresh draw stream per call (like the reference's .random_()), drawn on rank 0 and broadcast so that
+    every rank keys its draws with the same (seed, global image id)."""
+    if seed is not None:
+        return int(seed)
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return int(torch.randint(0, 2 ** 62, (1,), generator=_seed_gen()).item())
+    t = torch.randint(0, 2 ** 62, (1,), generator=_seed_gen()).to(device)
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return int(t.item())
+
+
+_GEN = None
+
+
+def _seed_gen():
+    global _GEN
+    if _GEN is None:
+        _GEN = torch.Generator(device="cpu")
+        _GEN.manual_seed(torch.initial_seed() & (2 ** 63 - 1))
+    return _GEN
+
+
+def ransac_voting_layer_v3_sharded(mask_local, vertex_local, round_hyp_num, global_b, *, group=None, seed=None,
                                    with_cov=False, cov_kwargs=None, vote_fn=None, cov_fn=None, **kwargs):
     """Each rank passes ITS slice (shard_bounds) of the batch.  Returns keypoints [global_b,vn,2] (and, with
     with_cov=True, covariances [global_b,vn,2,2] from estimate_voting_distribution_with_mean) on every rank.
+    `seed=None` draws a fresh seed on rank 0 and broadcasts it (one tiny collective); pass a seed to avoid it.
     `vote_fn` / `cov_fn` default to the CUDA entry points; the CPU tests inject stand-ins to exercise the plumbing."""
     if vote_fn is None or (with_cov and cov_fn is None):
         from . import ransac_voting_gpu as pv
@@ -55,6 +79,7 @@ def ransac_voting_layer_v3_sharded(mask_local, vertex_local, round_hyp_num, glob
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     lo, hi = shard_bounds(global_b, world, rank)
+    seed = _shared_seed(seed, group, mask_local.device)
     if mask_local.shape[0] != hi - lo:
         raise ValueError(f"rank {rank} owns images [{lo},{hi}) but was given {mask_local.shape[0]}")
     kp = vote_fn(mask_local, vertex_local, round_hyp_num, seed=seed, image_id_base=lo, **kwargs)

@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import torch
 
@@ -32,9 +33,22 @@ def _stream_ptr(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+_SEED_GEN = None
+
+
 def _fresh_seed():
-    # like the reference's .random_(): a new draw stream per call, taken from torch's CPU generator (no GPU sync)
-    return int(torch.randint(0, 2 ** 62, (1,)).item())
+    """Like the reference's .random_(): a new draw stream per call.  A private generator, seeded once from torch's global
+    seed, so that torch.manual_seed() still makes runs reproducible but no call advances the user's own RNG state."""
+    global _SEED_GEN
+    if _SEED_GEN is None:
+        _SEED_GEN = torch.Generator(device="cpu")
+        _SEED_GEN.manual_seed(torch.initial_seed() & (2 ** 63 - 1))
+    return int(torch.randint(0, 2 ** 62, (1,), generator=_SEED_GEN).item())
+
+
+# tuning / test knob: PVV_K3_VARIANT=<n> forces inlier-counting kernel variant n (read once, at import; the C ABI takes
+# it through pvv_debug.k3_variant -- the library itself never reads the environment)
+_K3_VARIANT_ENV = os.environ.get("PVV_K3_VARIANT")
 
 
 def _prep_mask(mask):
@@ -111,9 +125,11 @@ def _alloc_debug(job, dev, b, vn, hn, want_pool):
 
 
 def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_num, max_num, idxs, selection, seed,
-         image_id_base, return_debug, force_exact, pool_capacity, stage_ms=None):
+         image_id_base, return_debug, force_exact, pool_capacity, stage_ms=None, k3_variant=None, hyp_inject=None):
     L = _lib.lib()
     b, h, w, vn, _ = vertex.shape
+    if k3_variant is None and _K3_VARIANT_ENV is not None:
+        k3_variant = int(_K3_VARIANT_ENV)
     fg_rule = _lib.FG_EQ1 if kind == "cov" else _lib.FG_BYTE
     mask = _prep_mask(mask)
     if seed is None:
@@ -121,6 +137,12 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
     host = not mask.is_cuda
     if host != (not vertex.is_cuda):
         raise ValueError("mask and vertex must live on the same side (both CUDA or both CPU)")
+    if not host and mask.device != vertex.device:
+        raise ValueError(f"mask is on {mask.device} but vertex is on {vertex.device}")
+    if host:
+        for name, t in (("idxs", idxs), ("selection", selection), ("mean", mean)):
+            if t is not None and t.is_cuda:
+                raise ValueError(f"host-buffer call: `{name}` must be a CPU tensor like mask and vertex")
     if not torch.cuda.is_available():
         raise RuntimeError("pvnet_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     dev = torch.device("cuda", torch.cuda.current_device()) if host else mask.device
@@ -164,9 +186,20 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
             d, dbg_t = _alloc_debug(job, dev, b, vn, hn_total, want_pool=return_debug)
             d.force_exact = 1 if force_exact else 0
             dbg_ref = C.byref(d)
-        elif stage_ms is not None:
+        elif stage_ms is not None or k3_variant is not None or hyp_inject is not None:
             d = _lib.Debug()
             dbg_ref = C.byref(d)
+        if k3_variant is not None:
+            d.k3_variant = int(k3_variant) + 1
+        if hyp_inject is not None:
+            hyp_inject = hyp_inject.to(device=dev, dtype=torch.float32).reshape(b, hn_total, vn, 2).contiguous()
+            d.hyp_inject = hyp_inject.data_ptr()
+        # A pool overflow can only happen with a user-set pool_capacity or an injected `selection`; those calls check the
+        # status word (one 4-byte read, which synchronises) and raise instead of returning zeroed images silently.
+        status = None
+        if pool_capacity or selection is not None:
+            status = torch.zeros(1, dtype=torch.int32, device=dev)
+            job.status = status.data_ptr()
         if stage_ms is not None:
             buf = (C.c_float * 5)()
             d.stage_ms = C.cast(buf, C.c_void_p)
@@ -185,6 +218,10 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
             st = L.pvv_cov(C.byref(job), mean_d.data_ptr(), out.data_ptr(), dbg_ref)
         _lib.check(st, f"pvv_{kind}")
         ws.record_stream(torch.cuda.current_stream(dev))
+        if status is not None and not return_debug and not torch.cuda.is_current_stream_capturing():
+            if int(status.item()) & _lib.FLAG_POOL_OVERFLOW:
+                raise RuntimeError(f"pvv_{kind}: pool overflow -- the compacted foreground pixels do not fit pool_capacity="
+                                   f"{pool_capacity or 'default'}; images that did not fit were dropped (raise pool_capacity)")
         if stage_ms is not None:
             stage_ms.append(dict(zip(("compact", "hypotheses", "count", "finalize", "total"), list(buf))))
     if extra is not None:
@@ -197,24 +234,25 @@ def _run(kind, mask, vertex, mean, hn_total, thresh, confidence, max_iter, min_n
 
 def ransac_voting_layer_v3(mask, vertex, round_hyp_num, inlier_thresh=0.99, confidence=0.99, max_iter=100,
                            min_num=100, max_num=30000, *, idxs=None, selection=None, seed=None, image_id_base=0,
-                           return_debug=False, force_exact=False, pool_capacity=None, stage_ms=None):
+                           return_debug=False, force_exact=False, pool_capacity=None, stage_ms=None, k3_variant=None,
+                           hyp_inject=None):
     """mask [b,h,w] (any integer dtype), vertex [b,h,w,vn,2] float32 (any strides) -> keypoints [b,vn,2] float32.
 
     Reference: ransac_voting_gpu.py:520-604.  Images with fewer than `min_num` foreground pixels give zeros; images
     with more than `max_num` are Bernoulli-subsampled.  `confidence` / `max_iter` are accepted but cannot change the
     result: the reference draws idxs once (:553) and re-votes the same hypotheses every round."""
     return _run("v3", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
-                selection, seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms)
+                selection, seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms, k3_variant, hyp_inject)
 
 
 def ransac_voting_layer_v5(mask, vertex, round_hyp_num, inlier_thresh=0.999, confidence=0.99, max_iter=20, min_num=5,
                            max_num=100, *, idxs=None, selection=None, seed=None, image_id_base=0, return_debug=False,
-                           force_exact=False, pool_capacity=None):
+                           force_exact=False, pool_capacity=None, k3_variant=None):
     """-> (keypoints [b,vn,2], confidence [b,vn]).  Reference: ransac_voting_gpu.py:769-864 = v3 with its own defaults
     plus a re-vote of the refined keypoints at the fixed threshold 0.999 (:854-856); confidence = inlier count / tn,
     zeros for skipped images (:786-791)."""
     r = _run("v5", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
-             selection, seed, image_id_base, return_debug, force_exact, pool_capacity)
+             selection, seed, image_id_base, return_debug, force_exact, pool_capacity, None, k3_variant)
     if return_debug:
         return r[0][0], r[0][1], r[1]
     return r
@@ -222,12 +260,12 @@ def ransac_voting_layer_v5(mask, vertex, round_hyp_num, inlier_thresh=0.999, con
 
 def generate_hypothesis(mask, vertex, round_hyp_num, inlier_thresh=0.999, confidence=0.99, max_iter=20, min_num=5,
                         max_num=30000, *, idxs=None, selection=None, seed=None, image_id_base=0, return_debug=False,
-                        force_exact=False, pool_capacity=None):
+                        force_exact=False, pool_capacity=None, k3_variant=None, hyp_inject=None):
     """-> (hypotheses [b,hn,vn,2] float32, inlier counts [b,hn,vn] int64).  Reference: ransac_voting_gpu.py:989-1040 (what
     tools/demo.py:127 feeds to visualize_hypothesis).  Skipped images give zeros (the reference raises NameError there:
     `batch_win_pts` is undefined at :1009)."""
     r = _run("hyp", mask, vertex, None, round_hyp_num, inlier_thresh, confidence, max_iter, min_num, max_num, idxs,
-             selection, seed, image_id_base, return_debug, force_exact, pool_capacity)
+             selection, seed, image_id_base, return_debug, force_exact, pool_capacity, None, k3_variant, hyp_inject)
     if return_debug:
         return r[0][0], r[0][1].long(), r[1]
     return r[0], r[1].long()
@@ -256,12 +294,12 @@ def ransac_motion_voting(mask, vertex):
 def estimate_voting_distribution_with_mean(mask, vertex, mean, round_hyp_num=256, min_hyp_num=4096, topk=128,
                                            inlier_thresh=0.99, min_num=20, max_num=30000, output_hyp=False, *,
                                            idxs=None, selection=None, seed=None, image_id_base=0, return_debug=False,
-                                           force_exact=False, pool_capacity=None, stage_ms=None):
+                                           force_exact=False, pool_capacity=None, stage_ms=None, k3_variant=None):
     """-> (mean, cov [b,vn,2,2]).  Reference: ransac_voting_gpu.py:333-406 (`topk`, `output_hyp` are ignored there too).
     `idxs`, when injected, is int32 [b, rounds, round_hyp_num, vn, 2] with rounds = ceil(min_hyp_num/round_hyp_num)."""
     rounds = int(math.ceil(min_hyp_num / round_hyp_num))
     r = _run("cov", mask, vertex, mean, rounds * round_hyp_num, inlier_thresh, 0.0, 0, min_num, max_num, idxs, selection,
-             seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms)
+             seed, image_id_base, return_debug, force_exact, pool_capacity, stage_ms, k3_variant)
     if return_debug:
         return mean, r[0], r[1]
     return mean, r

@@ -87,10 +87,11 @@ def test_workspace_sizing_is_host_only_and_monotone(built_lib):
     j2 = _job(b=4)
     assert L.pvv_workspace_bytes(C.byref(j2)) > n1
     j3 = _job(max_num=10 ** 9)                                         # no subsampling bound: whole images
-    assert L.pvv_default_pool_capacity(C.byref(j3)) == 2 * 480 * 640
+    # no bound below the image: whole images, plus the alignment slack (every image starts on a 16-pixel boundary)
+    assert 2 * 480 * 640 <= L.pvv_default_pool_capacity(C.byref(j3)) <= 2 * 480 * 640 + 16 * 3 + 64
     j4 = _job()
     j4.pool_capacity = 1000
-    assert L.pvv_default_pool_capacity(C.byref(j4)) == 1024
+    assert 1000 + 16 * 2 <= L.pvv_default_pool_capacity(C.byref(j4)) <= 1000 + 16 * 3 + 64
     bad = _job(b=0)
     assert L.pvv_workspace_bytes(C.byref(bad)) == 0
     assert L.pvv_workspace_bytes(None) == 0

@@ -472,6 +472,12 @@ def test_eval_wrapper_equals_reference_composition():
     assert torch.equal(kp5, kp5w) and torch.equal(conf5, conf5w)
     got_mask = w(torch.argmax(seg, 1), vertex_pred, use_argmax=False)    # the reference's other branch: seg_pred is a mask
     assert torch.equal(got_mask, want)
+    # train_linemod's call: an already arg-maxed mask with use_argmax left at its default, and that site's arguments
+    tw = EvalWrapper.preset("train_linemod", seed=9)
+    assert (tw.round_hyp_num, tw.inlier_thresh, tw.layer_kwargs["max_num"]) == (128, 0.99, 100)
+    got_t = tw(torch.argmax(seg, 1), vertex_pred)
+    want_t = pv.ransac_voting_layer_v3(torch.argmax(seg, 1), vnet, 128, inlier_thresh=0.99, max_num=100, seed=9)
+    assert torch.equal(got_t, want_t)
 
 
 def test_vanishing_point_primitives_vs_oracle_and_reference_kernels():
@@ -705,9 +711,9 @@ def test_random_cases_vs_reference_cuda_kernels():
     assert checked >= 20
 
 
-def test_k3_kernel_variants_agree_with_exact_kernel(monkeypatch):
+def test_k3_kernel_variants_agree_with_exact_kernel():
     """K3 ships two guard-banded kernels and picks by hypothesis count: the FP32-pipe kernel (hn <= 256) and the
-    tensor-pipe kernel (tcgen05 tf32 MMA + TMEM, hn > 256).  PVV_K3_VARIANT forces one; every variant must reproduce the
+    tensor-pipe kernel (tcgen05 tf32 MMA + TMEM, hn > 256).  `k3_variant` (pvv_debug.k3_variant) forces one; every variant must reproduce the
     exact-only kernel's counts bit for bit on random ragged shapes (tiny images, partial chunks, hypothesis counts that
     are not multiples of 128, far / on-pixel keypoints, scaled and zero directions), on the adversarial field, and on
     the 4096-hypothesis covariance path (8 passes per chunk in the tensor-pipe kernel)."""
@@ -739,20 +745,231 @@ def test_k3_kernel_variants_agree_with_exact_kernel(monkeypatch):
         cases.append((torch.ones((1, 64, 96), dtype=torch.int64, device=DEV), torch.from_numpy(adv).to(DEV), 600, t, 100))
     mask, vertex, _ = synth.make_batch(2, vn=9, frac=0.02, sigma=0.05, seed=55)
     cm, cv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
-    monkeypatch.delenv("PVV_K3_VARIANT", raising=False)
     exact = [pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True,
                                        force_exact=True)[1]["counts"].clone() for m, v, hn, th, c in cases]
     mean = pv.ransac_voting_layer_v3(cm, cv, 512, 0.99, seed=1)
     cov_x, dbg_x = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True, force_exact=True)[1:]
-    for variant in ("0", "1", "2", "7", "8", "9"):   # 8 / 9: the tensor-pipe kernel with 7 / 3 producer warps
-        monkeypatch.setenv("PVV_K3_VARIANT", variant)
+    for variant in (0, 1, 2, 7, 8, 9):   # 8 / 9: the tensor-pipe kernel with its two fixed builder-warp counts
         for (m, v, hn, th, c), want in zip(cases, exact):
-            got = pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True)[1]
+            got = pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True,
+                                            k3_variant=variant)[1]
             assert torch.equal(got["counts"], want), (variant, c, hn, th)
-        cov, dbg = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True)[1:]
+        cov, dbg = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True,
+                                                             k3_variant=variant)[1:]
         assert torch.equal(dbg["counts"], dbg_x["counts"]) and torch.equal(cov, cov_x), variant
-    monkeypatch.delenv("PVV_K3_VARIANT", raising=False)
     # the shipped choice: tensor pipe above 256 hypotheses (the exact path is taken, rarely, and the counts above matched)
     _, d1 = pv.ransac_voting_layer_v3(cm, cv, 512, 0.999, seed=3, return_debug=True)
     _, d2 = pv.ransac_voting_layer_v3(cm, cv, 512, 0.999, seed=3, return_debug=True, force_exact=True)
     assert torch.equal(d1["counts"], d2["counts"]) and int(d1["amb_count"]) > 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Round 2: the stated configurations at full size against the reference's own CUDA layer, the pool-overflow contract,
+# and a direct attack on the guard band.
+# ---------------------------------------------------------------------------------------------------------------------
+def _compare_with_reference_v3(tm, tv, out, dbg, hn, thresh, min_num, max_num, selection=None):
+    r_out, r_dbg = ref_driver.v3(tm, tv, hn, thresh, min_num, max_num, dbg["idxs"], selection)
+    b, vn = out.shape[:2]
+    live = 0
+    for bi in range(b):
+        if r_dbg[bi] is None:
+            assert int(dbg["tn"][bi]) == 0 and not out[bi].any()
+            continue
+        tn, coords, direct, inl = _unpack_pool(dbg, bi, vn)
+        assert np.array_equal(coords, r_dbg[bi]["coords"].cpu().numpy()), bi                      # compacted set, order
+        assert np.array_equal(_bits(direct), _bits(r_dbg[bi]["direct"])), bi
+        assert np.array_equal(_bits(dbg["hyp"][bi]), _bits(r_dbg[bi]["hyp"])), bi                # hypotheses, bits
+        assert np.array_equal(dbg["counts"][bi].cpu().numpy(), r_dbg[bi]["counts"].cpu().numpy()), bi   # inlier counts
+        assert np.array_equal(dbg["win_idx"][bi].cpu().numpy(), r_dbg[bi]["win_idx"].cpu().numpy()), bi  # argmax
+        assert np.array_equal(inl, r_dbg[bi]["inlier"].cpu().numpy()), bi                         # winner re-vote flags
+        live += 1
+    np.testing.assert_allclose(out.cpu().numpy(), r_out.cpu().numpy(), rtol=RTOL, atol=0)        # 1e-4 relative
+    return live
+
+
+@pytest.mark.skipif(not ref_driver.available(), reason="oracle/_ref (reference CUDA build) not present")
+def test_configs1_full_batch_vs_reference_cuda_layer():
+    """BASELINE configs[1] exactly as benchmarked -- 32 x 480x640, 9 keypoints, 512 hypotheses, thresh 0.999, int64 mask,
+    the network's strided vertex layout -- against the reference's own kernels on the same GPU: integer outputs bit for
+    bit, keypoints within 1e-4 relative."""
+    b, vn, hn = 32, 9, 512
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=1234)
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, 0.999, seed=0, return_debug=True)
+    assert _compare_with_reference_v3(tm, tv, out, dbg, hn, 0.999, 100, 30000) == b
+    assert int(dbg["amb_count"]) > 0 and int(dbg["status"]) == 0
+
+
+@pytest.mark.skipif(not ref_driver.available(), reason="oracle/_ref (reference CUDA build) not present")
+def test_configs2_default_budget_vs_reference_cuda_layer():
+    """BASELINE configs[2] at the layer's defaults: estimate_voting_distribution_with_mean with 16 rounds x 256 = 4096
+    hypotheses (8 passes per chunk in the tensor-pipe kernel), thresh 0.99, on 8 images, against the reference's kernels
+    driven round by round ([256,vn,tn] matrices).  Counts bit for bit, covariances within 1e-4 relative."""
+    b, vn = 8, 9
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.03, sigma=0.05, seed=4321)
+    mask[5] = 0                                                   # skipped image: the reference's hyp = 0, ratio = 1 stand-in
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    kp = pv.ransac_voting_layer_v3(tm, tv, 512, 0.99, seed=1)
+    mean, cov, dbg = pv.estimate_voting_distribution_with_mean(tm, tv, kp, seed=2, return_debug=True)
+    assert dbg["counts"].shape == (b, 4096, vn)
+    ridx = dbg["idxs"].view(b, 16, 256, vn, 2)
+    _, r_cov = ref_driver.cov(tm, tv, kp, 256, 4096, 0.99, 20, 30000, ridx)
+    np.testing.assert_allclose(cov.cpu().numpy(), r_cov.cpu().numpy(), rtol=RTOL, atol=1e-6)
+    # counts of one image against the reference kernel directly (all 4096 hypotheses of it)
+    rv = ref_driver.ext()
+    coords, direct = ref_driver._compact(tm[0], tv[0], "eq1", 20, 30000, None)
+    hyp = rv.generate_hypothesis(direct, coords, dbg["idxs"][0].contiguous())
+    want = torch.zeros((4096, vn), dtype=torch.int64, device=DEV)
+    for r in range(16):
+        inl = torch.zeros((256, vn, coords.shape[0]), dtype=torch.uint8, device=DEV)
+        rv.voting_for_hypothesis(direct, coords, hyp[256 * r:256 * r + 256].contiguous(), inl, 0.99)
+        want[256 * r:256 * r + 256] = inl.sum(2)
+    assert torch.equal(dbg["counts"][0].long(), want)
+
+
+@pytest.mark.skipif(not ref_driver.available(), reason="oracle/_ref (reference CUDA build) not present")
+def test_configs3_instance_masks_vs_reference_cuda_layer():
+    """BASELINE configs[3] (Occlusion-LINEMOD shape): 8 disjoint object instances per image, flattened to the batch
+    dimension (4 images x 8 instances = 32 entries, each its own small mask and vertex field), a few instances below
+    min_num.  v3 (512, 0.99) and the covariance path against the reference's kernels."""
+    imgs, inst, vn, hn = 4, 8, 9, 512
+    b = imgs * inst
+    rng = np.random.default_rng(88)
+    masks = np.zeros((b, 480, 640), np.int64)
+    verts = np.zeros((b, 480, 640, vn, 2), np.float32)
+    for e in range(b):
+        r = np.random.default_rng(int(rng.integers(1 << 30)))
+        frac = 0.0001 if e % 11 == 5 else float(r.uniform(0.002, 0.012))   # ~30 px blobs are below min_num: skipped
+        masks[e] = synth.blob_mask(r, frac)
+        verts[e] = synth.unit_field(masks[e], synth.keypoints_in_bbox(r, masks[e], vn), 0.05, r)
+    tm, tv = torch.from_numpy(masks).to(DEV), synth.as_net_output(verts, device=DEV)
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, 0.99, seed=5, return_debug=True)
+    live = _compare_with_reference_v3(tm, tv, out, dbg, hn, 0.99, 100, 30000)
+    assert 0 < live < b                                           # some instances voted, some were skipped
+    mean, cov, cdbg = pv.estimate_voting_distribution_with_mean(tm, tv, out, 128, 512, seed=6, return_debug=True)
+    _, r_cov = ref_driver.cov(tm, tv, out, 128, 512, 0.99, 20, 30000, cdbg["idxs"].view(b, 4, 128, vn, 2))
+    np.testing.assert_allclose(cov.cpu().numpy(), r_cov.cpu().numpy(), rtol=RTOL, atol=1e-6)
+
+
+@pytest.mark.skipif(not ref_driver.available(), reason="oracle/_ref (reference CUDA build) not present")
+@pytest.mark.parametrize("hn,thresh,vn", [(2048, 0.999, 9), (2048, 0.99, 17), (128, 0.99, 9)])
+def test_sweep_corner_cases_vs_reference_cuda_layer(hn, thresh, vn):
+    """configs[4] corners: 2048 hypotheses (4 passes of the tensor-pipe kernel), 17 keypoints, and the reference's shipped
+    default of 128 hypotheses with max_num = 100 (tools/train_linemod.py:122-125: heavy subsampling, library selection
+    stream fed to the reference)."""
+    b = 3
+    mask, vertex, _ = synth.make_batch(b, vn=vn, frac=0.05, sigma=0.05, seed=700 + hn + vn)
+    tm, tv = torch.from_numpy(mask).to(DEV), synth.as_net_output(vertex, device=DEV)
+    max_num = 100 if hn == 128 else 30000
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=11, max_num=max_num, return_debug=True)
+    sel = pv.make_selection(11, b, 480, 640, torch.device(DEV)) if max_num == 100 else None
+    if max_num == 100:
+        assert 40 < int(dbg["tn"].max()) < 200                        # ~15 000 foreground pixels subsampled to ~100
+    assert _compare_with_reference_v3(tm, tv, out, dbg, hn, thresh, 100, max_num, sel) == b
+
+
+def test_pool_overflow_contract():
+    """A pool that is too small drops exactly the images that do not fit (admitted in batch order), keeps later ones that
+    do, and is never silent: the status word is set, the non-debug call raises, and so does the host-buffer call."""
+    mask, vertex, _ = synth.make_batch(4, vn=5, frac=0.05, sigma=0.05, seed=66, h=96, w=128)
+    mask[3] = 0
+    mask[3, 10:14, 20:60] = 1                                     # a small last image: 160 pixels
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    fg = [int(m.sum()) for m in mask]
+    full, dfull = pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13, return_debug=True)
+    assert int(dfull["status"]) == 0
+    cap = fg[0] + 200                                             # image 0 fits, 1 and 2 do not, 3 (160 px) does
+    assert fg[1] > 260 and fg[2] > 260
+    out, dbg = pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13, return_debug=True, pool_capacity=cap)
+    assert int(dbg["status"]) & 1
+    assert dbg["tn"].cpu().tolist() == [fg[0], 0, 0, fg[3]]
+    assert torch.equal(out[0], full[0]) and torch.equal(out[3], full[3])     # survivors are untouched (same global draws)
+    assert not out[1].any() and not out[2].any()
+    with pytest.raises(RuntimeError, match="pool overflow"):
+        pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13, pool_capacity=cap)
+    with pytest.raises(RuntimeError, match="pool overflow"):
+        pv.estimate_voting_distribution_with_mean(tm, tv, full, 32, 64, seed=13, pool_capacity=cap)
+    with pytest.raises(RuntimeError, match="PVV_ERR_POOL_OVERFLOW"):
+        pv.ransac_voting_layer_v3(torch.from_numpy(mask), torch.from_numpy(vertex), 64, 0.99, seed=13, pool_capacity=cap)
+    # a capacity that fits is checked too, and passes
+    ok = pv.ransac_voting_layer_v3(tm, tv, 64, 0.99, seed=13, pool_capacity=sum(fg))
+    assert torch.equal(ok, full)
+
+
+def _flip_point(nx, ny, cx, cy, p_in, p_out, thresh):
+    """Bisect along the segment from an inlier position to an outlier position (float64 parameter, float32 points) until
+    the reference's own decision (oracle C restatement of ransac_voting_kernel.cu:112-125) flips between two float32
+    points that are at most an ulp or two apart.  Returns (last inlier point, first outlier point)."""
+    L = orc.lib()
+    f = np.float32
+
+    def at(s):
+        return f(p_in[0] + s * (p_out[0] - p_in[0])), f(p_in[1] + s * (p_out[1] - p_in[1]))
+
+    lo, hi = 0.0, 1.0
+    a, c = at(lo), at(hi)
+    assert L.orc_inlier_test(nx, ny, cx, cy, a[0], a[1], thresh) == 1 and L.orc_inlier_test(nx, ny, cx, cy, c[0], c[1], thresh) == 0
+    for _ in range(64):
+        mid = 0.5 * (lo + hi)
+        m = at(mid)
+        if L.orc_inlier_test(nx, ny, cx, cy, m[0], m[1], thresh):
+            lo, a = mid, m
+        else:
+            hi, c = mid, m
+    return a, c
+
+
+@pytest.mark.parametrize("thresh", [0.5, 0.99, 0.999, 0.99999])
+def test_guard_band_attack_with_injected_hypotheses(thresh):
+    """The cases the bit-exactness proof is about: hypotheses whose cosine against one chosen pixel sits
+    within a few ulp of `thresh`.  For 120 (pixel, direction) pairs per threshold the flip point of the REFERENCE's decision
+    is found by bisection in float32 with the C oracle (from a point on the cone's axis to a point outside the cone, at
+    3 .. 3000 px from the pixel: inside and far outside the image); hypotheses at the last inlier / first outlier point and
+    +-{1, 2, 8, 64} ulp from them in x and in y are injected (pvv_debug.hyp_inject).  Every inlier count must equal the
+    oracle's for the FP32-pipe kernel shapes and the tensor-pipe kernel, and the exact path must have been taken for at
+    least one test per injected hypothesis."""
+    rng = np.random.default_rng(int(thresh * 1e6))
+    h, w, vn = 64, 96, 2
+    mask = np.ones((1, h, w), np.int64)
+    ang = rng.uniform(0, 2 * np.pi, (1, h, w, vn))
+    scale = rng.choice([1.0, 1.0, 0.37, 3.0], (1, h, w, vn))             # unnormalised directions too
+    vertex = (np.stack([np.cos(ang), np.sin(ang)], -1) * scale[..., None]).astype(np.float32)
+    half = np.arccos(thresh)
+    hyps = [[], []]
+    for vi in range(vn):
+        for _ in range(60):
+            y, x = int(rng.integers(0, h)), int(rng.integers(0, w))
+            nx, ny = (float(v) for v in vertex[0, y, x, vi])
+            dist = float(rng.choice([3.0, 17.0, 120.0, 700.0, 3000.0]))
+            phi = np.arctan2(ny, nx)
+            side = rng.choice([-1.0, 1.0])
+            p_in = (x + dist * np.cos(phi), y + dist * np.sin(phi))                                   # on the axis
+            p_out = (x + dist * np.cos(phi + 2 * side * half), y + dist * np.sin(phi + 2 * side * half))  # twice the half-angle
+            a, c = _flip_point(nx, ny, float(x), float(y), p_in, p_out, thresh)
+            for bx, by in (a, c):
+                for k in (0, 1, 2, 8, 64):
+                    for sgn in (-1, 1):
+                        hx, hy = bx, by
+                        for _ in range(k):
+                            hx = np.nextafter(hx, np.float32(sgn * np.inf), dtype=np.float32)
+                            hy = np.nextafter(hy, np.float32(sgn * np.inf), dtype=np.float32)
+                        hyps[vi].append((hx, by))
+                        hyps[vi].append((bx, hy))
+    hn = min(len(hyps[0]), len(hyps[1]))
+    assert hn == 60 * 2 * 5 * 2 * 2
+    inj = np.zeros((1, hn, vn, 2), np.float32)
+    for vi in range(vn):
+        inj[0, :, vi] = np.array(hyps[vi][:hn], np.float32)
+    tm, tv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    coords, direct = orc.compact(mask[0], vertex[0], "v3", 1, 10 ** 9)[:2]
+    want = orc.vote_counts(direct, coords, inj[0], thresh)
+    ran = 0
+    for variant in (None, 0, 1, 2, 7, 8, 9):
+        out, dbg = pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=1, max_num=10 ** 6, return_debug=True,
+                                             k3_variant=variant, hyp_inject=torch.from_numpy(inj))
+        assert np.array_equal(_bits(dbg["hyp"][0]), _bits(inj[0])), variant              # the injected hypotheses were voted on
+        got = dbg["counts"][0].cpu().numpy()
+        assert np.array_equal(got, want), (variant, thresh, int((got != want).sum()))
+        assert int(dbg["amb_count"]) >= hn * vn, (variant, int(dbg["amb_count"]))        # the band caught the planted tests
+        ran += 1
+    assert ran == 7

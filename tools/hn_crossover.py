@@ -12,10 +12,9 @@ for thresh in (0.999, 0.99):
     for hn in (128, 192, 256, 320, 384, 512):
         row = []
         for var in (0, 1, 2, 7):
-            os.environ["PVV_K3_VARIANT"] = str(var)
             st = []
             for i in range(10):
-                pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=0, stage_ms=st)
+                pv.ransac_voting_layer_v3(tm, tv, hn, thresh, seed=0, stage_ms=st, k3_variant=var)
             row.append((var, float(np.median([s["count"] + s["hypotheses"] for s in st[2:]]))))
         best = min(row, key=lambda r: r[1])
         print(f"thresh {thresh} hn {hn:4d}: " + "  ".join(f"v{v} {t * 1e3:6.1f} us" for v, t in row) + f"   best v{best[0]}", flush=True)

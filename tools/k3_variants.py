@@ -13,10 +13,9 @@ print("probe FFMA  TF:", L.pvv_probe_tflops(0, 4096, None), " FFMA2 TF:", L.pvv_
 for thresh in (0.999, 0.99):
     base = (thresh, pv.ransac_voting_layer_v3(tm, tv, 512, thresh, seed=0, return_debug=True, force_exact=True)[1]["counts"].clone())
     for var in [int(v) for v in (sys.argv[1:] or ["0", "1", "2", "3", "4", "5", "6", "7"])]:
-        os.environ["PVV_K3_VARIANT"] = str(var)
         st = []
         for i in range(12):
-            out, dbg = pv.ransac_voting_layer_v3(tm, tv, 512, thresh, seed=0, stage_ms=st, return_debug=True)
+            out, dbg = pv.ransac_voting_layer_v3(tm, tv, 512, thresh, seed=0, stage_ms=st, return_debug=True, k3_variant=var)
         ms = float(np.median([s["count"] for s in st[2:]]))
         c = dbg["counts"].clone()
         print(f"thresh {thresh} variant {var}: count {ms:.4f} ms  {tests/ms/1e9:.3f} T tests/s  amb {int(dbg['amb_count'])/tests:.2e}"

@@ -38,10 +38,7 @@ def run(nstreams, steps=200):
 
 
 for var in ("", "6", "3"):
-    if var:
-        os.environ["PVV_K3_VARIANT"] = var
-    else:
-        os.environ.pop("PVV_K3_VARIANT", None)
+    pv._K3_VARIANT_ENV = var or None   # the module-level default of the k3_variant keyword
     for ns in (1, 2, 3):
         ms = run(ns)
         print(f"K3 variant {var or 'default'} streams {ns}: {ms:.4f} ms/step  {32 / ms * 1e3:.0f} images/s", flush=True)
