@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpvvote.so")
+# PVV_LIB_PATH: load another build of the same library (development A/B builds under tools/_build); never a fallback
+LIB_PATH = os.environ.get("PVV_LIB_PATH") or os.path.join(_HERE, "libpvvote.so")
 
 PVV_OK = 0
 MASK_U8, MASK_I32, MASK_I64, MASK_F32, MASK_LOGITS_F32 = 0, 1, 2, 3, 4

@@ -63,8 +63,9 @@ int validate(const pvv_job *j)
 struct layout {
     size_t zero_bytes, total_bytes;
     size_t o_counters, o_img_fg, o_counts, o_ticket, o_part, o_flags, o_tn, o_img_off, o_chunk, o_ctab, o_tile_cnt, o_tile_off, o_bits, o_xy, o_dir, o_pq, o_hyp;
+    size_t o_rank, o_org, o_tcq, o_tcq_cnt;
     long long cap;
-    int ntiles, hn_pad;
+    int ntiles, hn_pad, tcq_slice_cap;
 };
 
 layout make_layout(const pvv_job *j)
@@ -79,6 +80,7 @@ layout make_layout(const pvv_job *j)
     L.o_img_fg = take(sizeof(long long) * j->b);
     L.o_counts = take(sizeof(int) * (size_t)j->b * j->vn * L.hn_pad);
     L.o_ticket = take(sizeof(unsigned) * (size_t)j->b * j->vn);
+    L.o_tcq_cnt = take(sizeof(int) * PVV_TCQ_SLICES);
     L.zero_bytes = o;
     L.o_flags = take(sizeof(int) * j->b);
     L.o_tn = take(sizeof(int) * j->b);
@@ -93,6 +95,17 @@ layout make_layout(const pvv_job *j)
     L.o_hyp = take(sizeof(float2) * (size_t)j->b * j->vn * L.hn_pad);
     L.o_pq = take(sizeof(float4) * (size_t)L.cap * j->vn);
     L.o_part = take(sizeof(double) * (size_t)j->b * j->vn * PVV_FIN_SPLIT * 5);
+    L.o_rank = take(sizeof(int) * j->b);
+    L.o_org = take(sizeof(uint32_t) * j->b);
+    {   // queue of the tensor-pipe K3's flagged (hypothesis, 16-pixel group) pairs: 64 per unit of work on average (measured
+        // 57 at thresh 0.999, 8 at 0.99; a unit has 8192), within [2^17, 2^22] entries; whatever does not fit is resolved in
+        // line by the kernel
+        const long long units = ((long long)L.cap / PVV_CHUNK_PX + j->b) * j->vn * ((j->hn_total + 511) / 512);
+        long long entries = 64 * units;
+        entries = entries < (1LL << 17) ? (1LL << 17) : entries > (1LL << 22) ? (1LL << 22) : entries;
+        L.tcq_slice_cap = (int)(entries / PVV_TCQ_SLICES);
+        L.o_tcq = take(sizeof(uint2) * (size_t)L.tcq_slice_cap * PVV_TCQ_SLICES);
+    }
     L.total_bytes = o;
     return L;
 }
@@ -118,6 +131,12 @@ pvv_ws carve(const layout &L, void *base)
     ws.pix_pq = (float4 *)(p + L.o_pq);
     ws.fin_ticket = (unsigned *)(p + L.o_ticket);
     ws.fin_part = (double *)(p + L.o_part);
+    ws.img_rank = (int *)(p + L.o_rank);
+    ws.img_org = (uint32_t *)(p + L.o_org);
+    ws.tcq = (uint2 *)(p + L.o_tcq);
+    ws.tcq_cnt = (int *)(p + L.o_tcq_cnt);
+    ws.tcq_slices = PVV_TCQ_SLICES;
+    ws.tcq_slice_cap = L.tcq_slice_cap;
     ws.idxs_used = nullptr;
     ws.cap = L.cap;
     ws.ntiles = L.ntiles;

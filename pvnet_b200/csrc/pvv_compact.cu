@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
 
     // batch-level scan: pool offsets and voting-chunk ranges.  b is small; chunks of kThreads with a carry.
     long long off = 0;
-    int chunk = 0;
+    int chunk = 0, rank = 0;
     for (int base = 0; base < d.b; base += kThreads) {
         const int i = base + threadIdx.x;
         const int n = i < d.b ? ((volatile int *)ws.tn)[i] : 0;
@@ -238,20 +238,28 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
         const int c = (n + PVV_CHUNK_PX - 1) / PVV_CHUNK_PX;
         int total_c;
         const int ex_c = block_excl_scan(c, &total_c);
+        int total_r;
+        const int ex_r = block_excl_scan(n > 0 ? 1 : 0, &total_r);   // rank of the image among those that vote
         if (i < d.b) {
             ws.img_off[i] = my_off;
             ws.chunk_start[i] = chunk + ex_c;
+            ws.img_rank[i] = rank + ex_r;
         }
         off += total_n;
         chunk += total_c;
+        rank += total_r;
     }
-    if (threadIdx.x == 0) ws.chunk_start[d.b] = chunk;
+    if (threadIdx.x == 0) { ws.chunk_start[d.b] = chunk; ws.counters[PVV_CTR_NIMG] = (unsigned)rank; }
     __syncthreads();
-    // voting-chunk table: K3 turns a work item into (image, pixel range) with one load instead of a search
+    // voting-chunk table: K3 turns a work item into (image, pixel range) with one load instead of a search.
+    //   .x image   .y POOL index of the chunk's first pixel   .z pixels | first-chunk-of-its-image << 15 | image rank << 16
+    //   .w x | y << 16 of the chunk's middle pixel (written by K1d)
     for (int i = threadIdx.x; i < d.b; i += kThreads) {
-        const int n = ws.tn[i], cs = ws.chunk_start[i];
+        const int n = ws.tn[i], cs = ws.chunk_start[i], rk = ws.img_rank[i];
+        const int off0 = (int)ws.img_off[i];
         for (int p0 = 0, c = 0; p0 < n; p0 += PVV_CHUNK_PX, ++c)
-            *reinterpret_cast<int3 *>(&ws.chunk_tab[cs + c]) = make_int3(i, p0, min(PVV_CHUNK_PX, n - p0));
+            *reinterpret_cast<int3 *>(&ws.chunk_tab[cs + c]) =
+                make_int3(i, off0 + p0, min(PVV_CHUNK_PX, n - p0) | (c == 0 ? 1 << 15 : 0) | (rk << 16));
     }
 }
 
@@ -308,7 +316,12 @@ __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *v
                 ws.pix_xy[base + j] = s_xy[j];
                 // the middle pixel of a voting chunk is the origin of that chunk's local frame in K3
                 const int t = toff + j, c = t / PVV_CHUNK_PX;
-                if (t - c * PVV_CHUNK_PX == (min(PVV_CHUNK_PX, tn - c * PVV_CHUNK_PX) >> 1)) ws.chunk_tab[cs + c].w = (int)s_xy[j];
+                if (t - c * PVV_CHUNK_PX == (min(PVV_CHUNK_PX, tn - c * PVV_CHUNK_PX) >> 1)) {
+                    ws.chunk_tab[cs + c].w = (int)s_xy[j];
+                    // the middle pixel of the image's middle chunk (its median pixel in raster order) is the origin of
+                    // the image's frame in the tensor-pipe K3
+                    if (c == ((tn + PVV_CHUNK_PX - 1) / PVV_CHUNK_PX) >> 1) ws.img_org[img] = s_xy[j];
+                }
             }
             const float *src = vertex + s_off[j];
             float2 *dst = ws.pix_dir + base + j;

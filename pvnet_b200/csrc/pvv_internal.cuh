@@ -14,8 +14,14 @@ struct pvv_ws {
     int *tn;                      // [b]  compacted pixels per image (0 when skipped)
     long long *img_off;           // [b]  offset of the image's pixels in the pool
     int *chunk_start;             // [b+1] first voting chunk of each image; [b] = total
-    int4 *chunk_tab;              // [cap/256 + b] per voting chunk: {image, first pixel, pixels, x|y<<16 of the middle pixel}
+    int4 *chunk_tab;              // [cap/256 + b] per voting chunk: {image, POOL index of its first pixel, pixels | first chunk of
+                                  //               its image << 15 | image rank << 16, x|y<<16 of the middle pixel}
                                   //               (.x .y .z by K1c, .w by K1d): K3 decodes a work item with one load
+    int *img_rank;                // [b]  rank of the image among the images that vote (tn > 0)
+    uint32_t *img_org;            // [b]  x|y<<16 of the image's median foreground pixel: origin of its frame in the tensor-pipe K3
+    uint2 *tcq;                   // tensor-pipe K3: flagged (hypothesis, 16-pixel group) entries, one slice per CTA of k_count_tc2
+    int *tcq_cnt;                 // [tcq_slices] entries pushed per slice (may exceed tcq_slice_cap: the excess was resolved in line)
+    int tcq_slices, tcq_slice_cap;
     int *tile_cnt;                // [b][ntiles] foreground pixels per compaction tile
     int *tile_off;                // [b][ntiles] exclusive prefix of tile_cnt within the image
     uint32_t *fg_bits;            // [b][ntiles][32] foreground bitmask (bit i of word w = pixel 32w+i of the tile), after
@@ -31,7 +37,9 @@ struct pvv_ws {
     int hn_pad;                   // hn rounded up to a multiple of 4 (hyp / counts row pitch)
 };
 
-enum { PVV_CTR_TICKET = 0, PVV_CTR_WORK = 1, PVV_CTR_STATUS = 2, PVV_CTR_AMB_LO = 4, PVV_CTR_AMB_HI = 5 };
+enum { PVV_CTR_TICKET = 0, PVV_CTR_WORK = 1, PVV_CTR_STATUS = 2, PVV_CTR_AMB_LO = 4, PVV_CTR_AMB_HI = 5,
+       PVV_CTR_NIMG = 6 /* images that vote (tn > 0) */ };
+#define PVV_TCQ_SLICES 148   // = CTAs of the tensor-pipe counting kernel (one per SM of a B200)
 enum { PVV_IMG_SKIPPED = 1, PVV_IMG_SUBSAMPLED = 2, PVV_IMG_OVERFLOW = 4 };
 
 struct pvv_dims {

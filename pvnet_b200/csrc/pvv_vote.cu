@@ -19,6 +19,7 @@
 //     16-pixel group) pairs are re-evaluated by the CTA (phase A, the loop's own packed FMA chains) and the tests truly
 //     inside the band get the reference's exact rounding sequence (phase B, pvv_exact_test).  Counts are bit-identical
 //     to the reference kernel's (error analysis in DESIGN.md "Guard band").
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "pvv_internal.cuh"
@@ -206,15 +207,15 @@ __device__ __forceinline__ k3_item k3_decode_item(const pvv_dims &d, const pvv_w
     item /= split;
     const int ci = item / d.vn;
     it.vi = item - ci * d.vn;
-    const int4 e = __ldg(&ws.chunk_tab[ci]);  // {image, first pixel, pixels, x|y<<16 of the middle pixel}, written by K1
+    const int4 e = __ldg(&ws.chunk_tab[ci]);  // {image, pool index of the first pixel, pixels | flags, x|y<<16 of the middle pixel}
     const int span = PVV_CHUNK_PX / split;
     it.img = e.x;
     it.p0 = e.y + sub * span;
-    it.n = max(0, min(span, e.z - sub * span));  // 0: the chunk ends before this range (an empty item)
+    it.n = max(0, min(span, (e.z & 0x7fff) - sub * span));  // 0: the chunk ends before this range (an empty item)
     // frame origin = the chunk's middle pixel: halves the extent P of the chunk around it, and with it the band
     it.ox = (int)((uint32_t)e.w & 0xffffu);
     it.oy = (int)((uint32_t)e.w >> 16);
-    it.off = __ldg(&ws.img_off[e.x]);
+    it.off = 0;   // p0 is a pool index already
     return it;
 }
 

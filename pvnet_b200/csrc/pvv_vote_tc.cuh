@@ -550,9 +550,10 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
             auto stage_inputs = [&](uint32_t rg1, uint32_t k1, const int4 &e, long long off, bool new_row, int rowbuf) {
                 if (e.x >= 0 && !K3_ABL(1024)) {
                     const int vi = (int)rg1 / npass, hbase = ((int)rg1 % npass) * TC_PASS_H;
-                    const long long pix = off + e.y;
+                    const long long pix = e.y;   // a pool index (off is no longer needed)
+                    (void)off;
                     tc_raw &W = S.raw[k1 % TC_RAWS];
-                    for (int j = ptid; j < e.z; j += TC_PRODS) {
+                    for (int j = ptid; j < (e.z & 0x7fff); j += TC_PRODS) {
                         cp_async16(&W.pq[j], ws.pix_pq + (long long)vi * ws.cap + pix + j);
                         cp_async8(&W.dir[j], ws.pix_dir + (long long)vi * ws.cap + pix + j);
                         cp_async4(&W.xy[j], ws.pix_xy + pix + j);
@@ -603,7 +604,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 tc_row &R = S.rows[rowbuf];
                 const int vi = (int)rg / npass, hbase = ((int)rg % npass) * TC_PASS_H;
                 const int hcount = min(TC_PASS_H, d.hn - hbase);
-                const int n = e0.z;
+                const int n = e0.z & 0x7fff;
                 const int nbn = (n + TC_TILE_PX - 1) / TC_TILE_PX;
                 const int mbn = (hcount + 127) / 128;
                 if (new_row) {
