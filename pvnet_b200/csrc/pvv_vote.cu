@@ -554,6 +554,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 }
 
 #include "pvv_vote_tc.cuh"
+#include "pvv_vote_tc2.cuh"
 }  // namespace
 
 // Guard-band constants for threshold t (DESIGN.md "Guard band").  Returns false when the fast filter does
@@ -621,7 +622,7 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
     band_consts bc = {};
     const int hyp_bx = (d.vn * d.hn + 255) / 256;
     const int cv = pvv_count_variant(d, force_exact, k3_variant, &bc);
-    if (cv >= 7 && cv <= 9) {
+    if (cv >= 7 && cv <= 10) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -656,6 +657,29 @@ static cudaError_t launch_count_tc(const pvv_dims &d, const pvv_ws &ws, const ba
     return cudaLaunchKernelEx(&cfg, k_count_tc<PW>, d, ws, bc);
 }
 
+// second-generation tensor-pipe kernel + its deferred-pass kernel (pvv_vote_tc2.cuh)
+template <int NB>
+static cudaError_t launch_count_tc2(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st, int *launches)
+{
+    cudaError_t e = cudaFuncSetAttribute(k_count_tc2<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(t2_smem<NB>));
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(sms < ws.tcq_slices ? sms : ws.tcq_slices);
+    cfg.blockDim = dim3(t2_cfg<NB>::threads);
+    cfg.dynamicSmemBytes = sizeof(t2_smem<NB>);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if ((e = cudaLaunchKernelEx(&cfg, k_count_tc2<NB>, d, ws, bc)) != cudaSuccess) return e;
+    const int parts = 4;
+    pvv_launch_pdl(k_count_tc_deferred, dim3(ws.tcq_slices * parts), dim3(T2_DEF_THREADS), st, d, ws, bc, parts);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exact, int k3_variant, cudaStream_t st,
                              int *launches)
 {
@@ -677,6 +701,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         const bool few = variant == 9 || (variant == 7 && d.thresh <= 0.995f);
         e = few ? launch_count_tc<3>(d, ws, bc, sms, st) : launch_count_tc<7>(d, ws, bc, sms, st);
     }
+    else if (variant == 10) e = launch_count_tc2<3>(d, ws, bc, sms, st, launches);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);
