@@ -30,6 +30,8 @@ constexpr int T2_NS = 6;         // stage ring: B operand + header of units k ..
 constexpr int T2_NROW = 3;       // row ring: a row buffer is rewritten 3 rows later
 constexpr int T2_VOTER_WARPS = 16;
 constexpr int T2_MMA_WARP = 16;
+constexpr int T2_TILE_PX = 64;                 // pixels per MMA tile
+constexpr int T2_TILE_COLS = 2 * T2_TILE_PX;   // N of one MMA = TMEM columns of one accumulator buffer: 4 buffers fill the SM's 512
 constexpr uint32_t T2_SUSPEND_NS = 20000;   // try_wait suspend-time hint; the hardware wakes the warp when the phase completes
 
 // setmaxnreg moves registers inside the CTA's pool, which is what the CTA was LAUNCHED with (threads x launch registers),
@@ -66,7 +68,7 @@ template <int NB> struct t2_smem {
     t2_row rows[T2_NROW];
     t2_stage st[T2_NS];
     t2_raw raw[NB][2];
-    unsigned long long bar_ready[T2_NS], bar_done[T2_NS], bar_full[2], bar_empty[2], bar_raw[NB][2];
+    unsigned long long bar_ready[T2_NS], bar_done[T2_NS], bar_full[4], bar_empty[4], bar_raw[NB][2];
     uint32_t tmem;
     int qn;                       // entries pushed to this CTA's slice of the deferred queue
 };
@@ -128,13 +130,12 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
 
     if (tid == 0) {
         for (int i = 0; i < T2_NS; ++i) { tc_bar_init(&S.bar_ready[i], 1); tc_bar_init(&S.bar_done[i], T2_VOTER_WARPS); }
-        tc_bar_init(&S.bar_full[0], 1); tc_bar_init(&S.bar_full[1], 1);
-        tc_bar_init(&S.bar_empty[0], T2_VOTER_WARPS); tc_bar_init(&S.bar_empty[1], T2_VOTER_WARPS);
+        for (int i = 0; i < 4; ++i) { tc_bar_init(&S.bar_full[i], 1); tc_bar_init(&S.bar_empty[i], 4); }
         for (int i = 0; i < NB; ++i) { tc_bar_init(&S.bar_raw[i][0], 1); tc_bar_init(&S.bar_raw[i][1], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         S.qn = 0;
     }
-    if (warp == T2_MMA_WARP) {  // the MMA warp owns the TMEM allocation: all 512 columns (two 256-column accumulators)
+    if (warp == T2_MMA_WARP) {  // the MMA warp owns the TMEM allocation: all 512 columns (four 128-column accumulators)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_saddr(&S.tmem)), "r"(TC_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
@@ -145,21 +146,25 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
 
     if (warp < T2_VOTER_WARPS) {
         // ================= voting warps: TMEM -> registers -> counts =================
+        // Warp = (TMEM lane quarter q4 = hypotheses 32*q4 .. +31 of an M-block, phase p): the warps of phase p take the tiles
+        // t = p (mod 4), whose accumulator is always TMEM buffer p.  A tile = 128 hypotheses x 64 pixels; a warp pulls its
+        // 32 lanes of all four 16-pixel groups.  The four warps of a scheduler are the four phases of one lane quarter, so
+        // they work on four different tiles: a buffer is handed back by 4 warps (not 16), and between two tiles of a warp
+        // lie three tiles of the others -- the MMA / commit / wake-up latency of the next tile is never exposed.
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_VOTER));
-        const int q4 = warp & 3;   // TMEM lane quarter = hypotheses 32*q4 .. +31 of the M-block
-        const int cq = warp >> 2;  // column quarter of the tile: pixels 32*cq .. +31 of its 128
-        uint32_t a_full = tc_saddr(&S.bar_full[0]), a_empty = tc_saddr(&S.bar_empty[0]);
-        uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cq * 64);
+        const int q4 = warp & 3, p = warp >> 2;
+        uint32_t a_full = tc_saddr(&S.bar_full[p]), a_empty = tc_saddr(&S.bar_empty[p]);
+        uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(p * T2_TILE_COLS);
         uint32_t lane0 = lane == 0;
         asm volatile("" : "+r"(a_full), "+r"(a_empty), "+r"(tmem_row), "+r"(lane0));  // kept in registers, not rematerialised
-        uint32_t t = 0;            // tile counter, in lock-step with the MMA issuer's
+        uint32_t tb = 0;           // index of the unit's first tile, in lock-step with the MMA issuer's count
         int cnt[4] = {0, 0, 0, 0}; // inlier counts of this thread's 4 hypotheses (one per M-block), accumulated over the row
         int cur_seq = -1, cur_hcount = 0, cur_mbn = 0;
         long long cur_row = 0;
         unsigned long long amb_local = 0;
         uint2 *slice = ws.tcq + (size_t)blockIdx.x * ws.tcq_slice_cap;
 
-        auto flush = [&] {  // the row is over: one global add per hypothesis
+        auto flush = [&] {  // the row is over: one global add per hypothesis and phase
 #pragma unroll
             for (int mb = 0; mb < 4; ++mb) {
                 const int hl = mb * 128 + q4 * 32 + lane;
@@ -167,15 +172,7 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                 cnt[mb] = 0;
             }
         };
-        auto full_wait = [&](uint32_t tt) {
-            t2_wait(a_full + 8u * (tt & 1u), (tt >> 1) & 1u, 1);
-            tc_fence_after();
-        };
         auto landed = [&] { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); };
-        auto release = [&](uint32_t tt) {  // both groups of tile tt are in registers: its TMEM buffer is free
-            tc_fence_before();
-            if (lane0) tc_bar_arrive(a_empty + 8u * (tt & 1u));
-        };
 
         uint32_t s = 0, ph = 0;
         for (;;) {
@@ -189,48 +186,46 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
             }
             const float ext = T.h.ext, ucx = T.h.ucx, ucy = T.h.ucy, uext = T.h.uext;
             const t2_row &R = S.rows[T.h.rowbuf];
-            uint32_t dmask = 0u;   // bit mb*4 + nb*2 + g: flagged 16-pixel group of this thread's hypothesis in M-block mb
+            uint32_t dmask = 0u;   // bit 4k + g: flagged 16-pixel group g of the k-th tile this warp took from the unit
+            uint32_t jlist = 0u;   // nibble k: that tile's index mb * nbn + nb within the unit
+            int ktile = 0;
             uint32_t v0[32], v1[32];
-            // Both groups of a tile are in registers before its first vote, so its TMEM buffer goes back at once; the first
-            // group of the next tile is loaded under the vote on this tile's second group.
-            full_wait(t);
-            tc_ld32(tmem_row + (t & 1u) * 256u, v0);
-            tc_ld32(tmem_row + (t & 1u) * 256u + 32u, v1);
-            landed();
-            release(t);
-#pragma unroll
-            for (int mb = 0; mb < 4; ++mb) {
-                if (mb < mbn) {
-                    const int hl = mb * 128 + q4 * 32 + lane;
-                    const float4 hh = R.H[hl];
-                    const float mu = __fadd_rn(__fadd_rn(fabsf(__fsub_rn(hh.x, ucx)), fabsf(__fsub_rn(hh.y, ucy))), uext);
-                    const float Tt = __fmaf_rn(bc.erel, mu, __fmaf_rn(bc.kabs_tc, __fadd_rn(hh.z, ext), bc.abs_floor));
-                    int neg = 0;
-                    uint32_t dm = 0u;
-#pragma unroll
-                    for (int nb = 0; nb < 2; ++nb) {
-                        if (nb < nbn) {
-                            const bool more = !(mb == mbn - 1 && nb == nbn - 1);
-                            tc_group(v0, Tt, neg, dm, 1u << (2 * nb));
-                            if (more) {
-                                full_wait(t + 1);
-                                tc_ld32(tmem_row + ((t + 1) & 1u) * 256u, v0);
-                            }
-                            tc_group(v1, Tt, neg, dm, 2u << (2 * nb));
-                            if (more) {
-                                tc_ld32(tmem_row + ((t + 1) & 1u) * 256u + 32u, v1);
-                                landed();
-                                release(t + 1);
-                            }
-                            ++t;
-                        }
-                    }
-                    if (hl < hcount) {
-                        cnt[mb] += K3_GROUP * (2 * nbn - __popc(dm)) - sign_lanes_total(neg);
-                        dmask |= dm << (mb * 4);
-                    }
+            // this warp's tiles of the unit: j = mb * nbn + nb with tb + j = p (mod 4); one copy of the tile body
+            const int ntile = mbn * nbn;
+            const uint32_t inv = nbn == 4 ? 64u : nbn == 3 ? 86u : nbn == 2 ? 128u : 256u;   // (j * inv) >> 8 = j / nbn for j < 16
+#pragma unroll 1
+            for (int j = (int)(((uint32_t)p - tb) & 3u); j < ntile; j += 4) {
+                const uint32_t tt = tb + (uint32_t)j;
+                const int mb = (int)(((uint32_t)j * inv) >> 8);
+                const int hl = mb * 128 + q4 * 32 + lane;
+                const float4 hh = R.H[hl];
+                const float mu = __fadd_rn(__fadd_rn(fabsf(__fsub_rn(hh.x, ucx)), fabsf(__fsub_rn(hh.y, ucy))), uext);
+                const float Tt = __fmaf_rn(bc.erel, mu, __fmaf_rn(bc.kabs_tc, __fadd_rn(hh.z, ext), bc.abs_floor));
+                int neg = 0;
+                uint32_t dm = 0u;
+                t2_wait(a_full, (tt >> 2) & 1u, 1);
+                tc_fence_after();
+                tc_ld32(tmem_row, v0);
+                tc_ld32(tmem_row + 32u, v1);
+                landed();
+                tc_group(v0, Tt, neg, dm, 1u);
+                tc_ld32(tmem_row + 64u, v0);
+                tc_group(v1, Tt, neg, dm, 2u);
+                tc_ld32(tmem_row + 96u, v1);
+                landed();
+                tc_fence_before();          // the whole tile is in registers: its TMEM buffer is free
+                if (lane0) tc_bar_arrive(a_empty);
+                tc_group(v0, Tt, neg, dm, 4u);
+                tc_group(v1, Tt, neg, dm, 8u);
+                if (hl < hcount) {
+                    const int c = K3_GROUP * (4 - __popc(dm)) - sign_lanes_total(neg);
+                    cnt[0] += mb == 0 ? c : 0; cnt[1] += mb == 1 ? c : 0; cnt[2] += mb == 2 ? c : 0; cnt[3] += mb == 3 ? c : 0;
+                    dmask |= dm << (4 * ktile);
                 }
+                jlist |= (uint32_t)j << (4 * ktile);
+                ++ktile;
             }
+            tb += (uint32_t)(mbn * nbn);
             // queue the flagged (hypothesis, group) pairs for k_count_tc_deferred: one reservation per warp and unit
             const int mine = __popc(dmask);
             if (__any_sync(0xffffffffu, mine)) {
@@ -247,8 +242,10 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                 while (dmask) {
                     const int bitn = __ffs(dmask) - 1;
                     dmask &= dmask - 1;
-                    const int hl = (bitn >> 2) * 128 + q4 * 32 + lane;
-                    const int grp = ((bitn >> 1) & 1) * 8 + cq * 2 + (bitn & 1);  // 16-pixel group within the chunk
+                    const int j = (int)((jlist >> (4 * (bitn >> 2))) & 15u);
+                    const int mb = j / nbn, nb = j - mb * nbn;
+                    const int hl = mb * 128 + q4 * 32 + lane;
+                    const int grp = nb * 4 + (bitn & 3);  // 16-pixel group within the chunk
                     if (q < ws.tcq_slice_cap) {
                         slice[q] = t2_entry(chunk, hbase + hl, grp, vi);
                     } else {  // slice full (pathological inputs): the reference's own decision for the whole group, in line
@@ -256,9 +253,9 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                         const float2 hv = ws.hyp[cur_row + hl];
                         const int n = e.z & 0x7fff;
                         int c = 0;
-                        for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j) {
-                            const float2 dir = ws.pix_dir[(long long)vi * ws.cap + e.y + j];
-                            const uint32_t xy = ws.pix_xy[e.y + j];
+                        for (int jj = grp * K3_GROUP; jj < min(n, (grp + 1) * K3_GROUP); ++jj) {
+                            const float2 dir = ws.pix_dir[(long long)vi * ws.cap + e.y + jj];
+                            const uint32_t xy = ws.pix_xy[e.y + jj];
                             c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
                                                 hv.x, hv.y, d.thresh) ? 1 : 0;
                             ++amb_local;
@@ -279,7 +276,8 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
         if (warp == T2_MMA_WARP) {
             // ================= MMA issuer: one thread =================
             if (lane == 0) {
-                const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(256 >> 3) << 17) | ((128u >> 4) << 24);
+                // kind::tf32: D = f32 (bit 4), A = B = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+                const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T2_TILE_COLS >> 3) << 17) | ((128u >> 4) << 24);
                 uint32_t t = 0, s = 0, ph = 0;
                 for (;;) {
                     t2_stage &T = S.st[s];
@@ -291,13 +289,13 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                     for (int mb = 0; mb < mbn; ++mb) {
                         const uint64_t da = tc_desc(tc_saddr(&R.A[0][mb * 128]), sizeof(R.A[0]), 128);
                         for (int nb = 0; nb < nbn; ++nb, ++t) {
-                            const uint32_t buf = t & 1u;
-                            if (t >= 2) t2_wait(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u, 103);
+                            const uint32_t buf = t & 3u;
+                            if (t >= 4) t2_wait(&S.bar_empty[buf], ((t >> 2) - 1u) & 1u, 103);
                             tc_fence_after();
-                            const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * 256]), sizeof(T.B[0]), 128);
+                            const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * T2_TILE_COLS]), sizeof(T.B[0]), 128);
                             asm volatile(
                                 "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * 256u),
+                                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * (uint32_t)T2_TILE_COLS),
                                 "l"(da), "l"(db), "r"(idesc), "r"(0));
                             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                                              tc_saddr(&S.bar_full[buf])) : "memory");
@@ -367,7 +365,7 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                 const int vi = (int)(rg / npass), hbase = (int)(rg % npass) * TC_PASS_H;
                 const int hcount = min(TC_PASS_H, d.hn - hbase);
                 const int n = eA.z & 0x7fff;
-                const int nbn = (n + TC_TILE_PX - 1) / TC_TILE_PX, mbn = (hcount + 127) / 128;
+                const int nbn = (n + T2_TILE_PX - 1) / T2_TILE_PX, mbn = (hcount + 127) / 128;
                 const uint32_t rowseq = rg * nimg + ((uint32_t)eA.z >> 16) - seq0;
                 const int rowbuf = (int)(rowseq % T2_NROW);
                 const bool new_row = k == 0 || ((eA.z >> 15) & 1);
@@ -400,7 +398,7 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                 // ---- pixel constants in the image's frame, TF32-split, as B rows ----
                 int ext = 0, uext = 0;
                 const int ucx = (int)((uint32_t)eA.w & 0xffffu) - ox, ucy = (int)((uint32_t)eA.w >> 16) - oy;  // the unit's centre
-                for (int j = lane; j < nbn * TC_TILE_PX; j += 32) {
+                for (int j = lane; j < nbn * T2_TILE_PX; j += 32) {
                     float px = 0.f, py = 0.f, pz = -1e30f, qx = 0.f, qy = 0.f, qz = -1e30f;  // m = -2e30: never an inlier, never in the band
                     if (j < n) {
                         const float4 pq = W.pq[j];
