@@ -20,7 +20,7 @@ OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libpvvote.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 SOURCES = ["pvv_compact.cu", "pvv_vote.cu", "pvv_finalize.cu", "pvv_primitives.cu", "pvv_pnp.cu", "pvv_capi.cu", "pvv_host.cu"]
-HEADERS = ["pvv_common.cuh", "pvv_internal.cuh", "pvv_vote_tc.cuh", "../../include/pvvote.h"]
+HEADERS = ["pvv_common.cuh", "pvv_internal.cuh", "pvv_vote_tc.cuh", "pvv_vote_tc2.cuh", "../../include/pvvote.h"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

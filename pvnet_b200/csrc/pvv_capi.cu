@@ -104,7 +104,7 @@ layout make_layout(const pvv_job *j)
         long long entries = 64 * units;
         entries = entries < (1LL << 17) ? (1LL << 17) : entries > (1LL << 22) ? (1LL << 22) : entries;
         L.tcq_slice_cap = (int)(entries / PVV_TCQ_SLICES);
-        L.o_tcq = take(sizeof(uint2) * (size_t)L.tcq_slice_cap * PVV_TCQ_SLICES);
+        L.o_tcq = take(sizeof(uint4) * (size_t)L.tcq_slice_cap * PVV_TCQ_SLICES);
     }
     L.total_bytes = o;
     return L;
@@ -133,7 +133,7 @@ pvv_ws carve(const layout &L, void *base)
     ws.fin_part = (double *)(p + L.o_part);
     ws.img_rank = (int *)(p + L.o_rank);
     ws.img_org = (uint32_t *)(p + L.o_org);
-    ws.tcq = (uint2 *)(p + L.o_tcq);
+    ws.tcq = (uint4 *)(p + L.o_tcq);
     ws.tcq_cnt = (int *)(p + L.o_tcq_cnt);
     ws.tcq_slices = PVV_TCQ_SLICES;
     ws.tcq_slice_cap = L.tcq_slice_cap;

@@ -19,7 +19,7 @@ struct pvv_ws {
                                   //               (.x .y .z by K1c, .w by K1d): K3 decodes a work item with one load
     int *img_rank;                // [b]  rank of the image among the images that vote (tn > 0)
     uint32_t *img_org;            // [b]  x|y<<16 of the image's median foreground pixel: origin of its frame in the tensor-pipe K3
-    uint2 *tcq;                   // tensor-pipe K3: flagged (hypothesis, 16-pixel group) entries, one slice per CTA of k_count_tc2
+    uint4 *tcq;                   // tensor-pipe K3: flagged (hypothesis, 16-pixel group) entries, one slice per CTA of k_count_tc2
     int *tcq_cnt;                 // [tcq_slices] entries pushed per slice (may exceed tcq_slice_cap: the excess was resolved in line)
     int tcq_slices, tcq_slice_cap;
     int *tile_cnt;                // [b][ntiles] foreground pixels per compaction tile

@@ -611,7 +611,10 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
 static int pvv_count_variant(const pvv_dims &d, int force_exact, int k3_variant, band_consts *bc)
 {
     if (force_exact || !pvv_band_for(d.thresh, bc)) return -1;
-    return k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
+    int v = k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
+    // the second-generation tensor-pipe kernel indexes hyp / counts with 32 bits in its queue entries
+    if (v == 10 && (long long)d.b * d.vn * ((d.hn + 3) / 4 * 4) >= (1LL << 31)) v = 7;
+    return v;
 }
 
 // K2.  When the tensor-pipe kernel will count, its per-pixel constants pre-pass rides in the same launch (independent
@@ -674,7 +677,7 @@ static cudaError_t launch_count_tc2(const pvv_dims &d, const pvv_ws &ws, const b
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     if ((e = cudaLaunchKernelEx(&cfg, k_count_tc2<NB>, d, ws, bc)) != cudaSuccess) return e;
-    const int parts = 4;
+    const int parts = 16;
     pvv_launch_pdl(k_count_tc_deferred, dim3(ws.tcq_slices * parts), dim3(T2_DEF_THREADS), st, d, ws, bc, parts);
     ++*launches;
     return cudaGetLastError();

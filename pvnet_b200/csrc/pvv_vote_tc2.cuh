@@ -26,12 +26,21 @@
 //     atomic per hypothesis and row.
 #pragma once
 
+// development ablations (tools/t2_ablate.py, -DPVV_K3_ABLATE builds only): PVV_K3_ABLATE = bits << 16
+//   1 no vote   2 no TMEM loads   4 builders publish without building B   8 no MMA (plain arrive)   16 no queue pushes
+//   32 issuer does not wait for free accumulators   64 voters neither wait for tiles nor hand them back
+//   128 builders fetch no raw inputs   256 builders build no A rows
+#define T2A(bit) K3_ABL((bit) << 16)
+
 constexpr int T2_NS = 6;         // stage ring: B operand + header of units k .. k+5
 constexpr int T2_NROW = 3;       // row ring: a row buffer is rewritten 3 rows later
 constexpr int T2_VOTER_WARPS = 16;
 constexpr int T2_MMA_WARP = 16;
 constexpr int T2_TILE_PX = 64;                 // pixels per MMA tile
 constexpr int T2_TILE_COLS = 2 * T2_TILE_PX;   // N of one MMA = TMEM columns of one accumulator buffer: 4 buffers fill the SM's 512
+#ifndef T2_WAIT_MODE
+#define T2_WAIT_MODE 0    // 0: try_wait with a suspend-time hint, 1: try_wait (system time limit), 2: test_wait (pure poll)
+#endif
 constexpr uint32_t T2_SUSPEND_NS = 20000;   // try_wait suspend-time hint; the hardware wakes the warp when the phase completes
 
 // setmaxnreg moves registers inside the CTA's pool, which is what the CTA was LAUNCHED with (threads x launch registers),
@@ -47,7 +56,8 @@ template <int NB> struct t2_cfg {
 };
 
 struct t2_hdr {                   // written by the unit's builder (lane 0), read by the voters and the MMA issuer
-    int stop, n, mbn, nbn, hcount, rowbuf, rowseq, chunk, vi, hbase;
+    int stop, n, mbn, nbn, hcount, rowbuf, rowseq, pool0, vi, hbase;   // pool0: pool index of the chunk's first pixel
+    uint32_t corg;                // x | y << 16 of the chunk's middle pixel
     float ext;                    // largest |offset| (L1) of a pixel of the unit from the frame origin
     float ucx, ucy, uext;         // the unit's centre in the frame, largest |offset| of its pixels from that centre
     long long cnt_row;            // offset of (image, keypoint) row + pass in counts / hyp
@@ -76,6 +86,16 @@ template <int NB> struct t2_smem {
 // mbarrier wait that parks the warp: try_wait with a suspend-time hint returns when the phase completes or the hint
 // expires.  The watchdog counts this warp's own failed waits (not wall-clock time: a time-sliced context does not
 // advance it); 2^22 expired hints are seconds of continuous waiting where a legitimate wait lasts microseconds.
+#ifdef PVV_T2_PROF   // development: cycles each warp spends in each kind of wait, printed by CTA 0 at the end
+#define T2_PROF_DECL long long t2_prof_w[8] = {0, 0, 0, 0, 0, 0, 0, 0}; const long long t2_prof_t0 = clock64();
+#define T2_WAIT(bar, par, id) do { const long long t2_c0 = clock64(); t2_wait(bar, par, id); t2_prof_w[(id) & 7] += clock64() - t2_c0; } while (0)
+#define T2_PROF_PRINT(role) do { if (blockIdx.x == 3 && (threadIdx.x & 31) == 0) printf("prof %s warp %2d total %lld  w1(full) %lld w2(ready) %lld w3(empty) %lld w4(rowbuf) %lld w5(stage) %lld w6(raw) %lld w7 %lld\n", role, threadIdx.x >> 5, clock64() - t2_prof_t0, t2_prof_w[1], t2_prof_w[2], t2_prof_w[3], t2_prof_w[4], t2_prof_w[5], t2_prof_w[6], t2_prof_w[7]); } while (0)
+#else
+#define T2_PROF_DECL
+#define T2_WAIT(bar, par, id) t2_wait(bar, par, id)
+#define T2_PROF_PRINT(role)
+#endif
+
 __device__ __forceinline__ void t2_wait(uint32_t bar_saddr, uint32_t parity, int id = 0)
 {
     uint32_t done;
@@ -83,8 +103,16 @@ __device__ __forceinline__ void t2_wait(uint32_t bar_saddr, uint32_t parity, int
     uint32_t fails = 0;
 #endif
     for (;;) {
+#if T2_WAIT_MODE == 0
         asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
                      : "=r"(done) : "r"(bar_saddr), "r"(parity), "r"(T2_SUSPEND_NS) : "memory");
+#elif T2_WAIT_MODE == 1
+        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
+                     : "=r"(done) : "r"(bar_saddr), "r"(parity) : "memory");
+#else
+        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
+                     : "=r"(done) : "r"(bar_saddr), "r"(parity) : "memory");
+#endif
         if (done) return;
 #ifdef PVV_T2_DEBUG   // development: report which wait starved and carry on (the kernel then ends with wrong counts)
         if (++fails > (1u << 18)) {
@@ -99,6 +127,14 @@ __device__ __forceinline__ void t2_wait(uint32_t bar_saddr, uint32_t parity, int
 }
 __device__ __forceinline__ void t2_wait(unsigned long long *b, uint32_t parity, int id = 0) { t2_wait(tc_saddr(b), parity, id); }
 
+// one lane of a converged warp (elect.sync): the lane that issues tcgen05.mma / tcgen05.commit
+__device__ __forceinline__ bool tc_elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.b32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 // 1-D bulk copy global -> shared (TMA), completion counted in bytes on an mbarrier of this CTA
 __device__ __forceinline__ void t2_bulk_g2s(void *smem, const void *gmem, uint32_t bytes, unsigned long long *bar)
 {
@@ -111,10 +147,12 @@ __device__ __forceinline__ void t2_expect_tx(unsigned long long *bar, uint32_t b
 }
 __device__ __forceinline__ void t2_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// entry of the deferred queue: .x = voting chunk, .y = hypothesis (16 bits) | 16-pixel group << 16 | keypoint << 20
-__device__ __forceinline__ uint2 t2_entry(int chunk, int hyp, int grp, int vi)
+// Entry of the deferred queue, self-contained so that the kernel that resolves it has no dependent table look-ups:
+//   .x pool index of the group's first pixel   .y index of the hypothesis in hyp / counts
+//   .z pixels of the group that exist (0..16) | keypoint << 8   .w x | y << 16 of the chunk's middle pixel (phase-A frame)
+__device__ __forceinline__ uint4 t2_entry(int pool_px, long long hyp_idx, int nvalid, int vi, uint32_t org)
 {
-    return make_uint2((uint32_t)chunk, (uint32_t)hyp | ((uint32_t)grp << 16) | ((uint32_t)vi << 20));
+    return make_uint4((uint32_t)pool_px, (uint32_t)hyp_idx, (uint32_t)nvalid | ((uint32_t)vi << 8), org);
 }
 
 template <int NB>
@@ -152,117 +190,111 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
         // they work on four different tiles: a buffer is handed back by 4 warps (not 16), and between two tiles of a warp
         // lie three tiles of the others -- the MMA / commit / wake-up latency of the next tile is never exposed.
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_VOTER));
+        T2_PROF_DECL
         const int q4 = warp & 3, p = warp >> 2;
         uint32_t a_full = tc_saddr(&S.bar_full[p]), a_empty = tc_saddr(&S.bar_empty[p]);
         uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(p * T2_TILE_COLS);
         uint32_t lane0 = lane == 0;
         asm volatile("" : "+r"(a_full), "+r"(a_empty), "+r"(tmem_row), "+r"(lane0));  // kept in registers, not rematerialised
-        uint32_t tb = 0;           // index of the unit's first tile, in lock-step with the MMA issuer's count
-        int cnt[4] = {0, 0, 0, 0}; // inlier counts of this thread's 4 hypotheses (one per M-block), accumulated over the row
-        int cur_seq = -1, cur_hcount = 0, cur_mbn = 0;
-        long long cur_row = 0;
+        // Tile slots of a unit are numbered j = nb * S + mb (nb: 64-pixel quarter of the chunk, mb: 128-hypothesis M-block,
+        // S = 1, 2, 4, 4 for 1, 2, 3, 4 M-blocks; with 3 the slots mb = 3 stay empty) and slot t of the running count uses
+        // buffer t & 3.  S divides 4, so within a unit -- and, as long as the chunks are full, within a whole row -- a warp
+        // sees ONE M-block, i.e. one hypothesis per thread: its band half-width is computed once per unit, its inlier count
+        // is one register, the sign lanes are summed once per unit.
+        uint32_t tb = 0;           // slot count at the start of the unit, in lock-step with the MMA issuer's
+        uint32_t used = 0;         // tiles this warp has taken from its buffer (parity of the next `full` phase)
+        int cnt = 0;               // inlier count of this thread's hypothesis, accumulated over the units of a row
+        int cur_seq = -1, cur_mb = -1;
+        long long cur_idx = -1;    // counts index of that hypothesis (-1: none / beyond hcount)
         unsigned long long amb_local = 0;
-        uint2 *slice = ws.tcq + (size_t)blockIdx.x * ws.tcq_slice_cap;
+        uint4 *slice = ws.tcq + (size_t)blockIdx.x * ws.tcq_slice_cap;
 
-        auto flush = [&] {  // the row is over: one global add per hypothesis and phase
-#pragma unroll
-            for (int mb = 0; mb < 4; ++mb) {
-                const int hl = mb * 128 + q4 * 32 + lane;
-                if (mb < cur_mbn && hl < cur_hcount && cnt[mb]) atomicAdd(&ws.counts[cur_row + hl], cnt[mb]);
-                cnt[mb] = 0;
-            }
+        auto flush = [&] {  // the row (or the warp's M-block) is over: one global add per hypothesis
+            if (cnt && cur_idx >= 0) atomicAdd(&ws.counts[cur_idx], cnt);
+            cnt = 0;
         };
         auto landed = [&] { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); };
 
         uint32_t s = 0, ph = 0;
         for (;;) {
             t2_stage &T = S.st[s];
-            t2_wait(&S.bar_ready[s], ph, 2);
+            T2_WAIT(&S.bar_ready[s], ph, 2);
             if (T.h.stop) break;
             const int mbn = T.h.mbn, nbn = T.h.nbn, hcount = T.h.hcount;
-            if (T.h.rowseq != cur_seq) {
-                flush();
-                cur_seq = T.h.rowseq; cur_hcount = hcount; cur_mbn = mbn; cur_row = T.h.cnt_row;
-            }
-            const float ext = T.h.ext, ucx = T.h.ucx, ucy = T.h.ucy, uext = T.h.uext;
-            const t2_row &R = S.rows[T.h.rowbuf];
-            uint32_t dmask = 0u;   // bit 4k + g: flagged 16-pixel group g of the k-th tile this warp took from the unit
-            uint32_t jlist = 0u;   // nibble k: that tile's index mb * nbn + nb within the unit
-            int ktile = 0;
-            uint32_t v0[32], v1[32];
-            // this warp's tiles of the unit: j = mb * nbn + nb with tb + j = p (mod 4); one copy of the tile body
-            const int ntile = mbn * nbn;
-            const uint32_t inv = nbn == 4 ? 64u : nbn == 3 ? 86u : nbn == 2 ? 128u : 256u;   // (j * inv) >> 8 = j / nbn for j < 16
-#pragma unroll 1
-            for (int j = (int)(((uint32_t)p - tb) & 3u); j < ntile; j += 4) {
-                const uint32_t tt = tb + (uint32_t)j;
-                const int mb = (int)(((uint32_t)j * inv) >> 8);
+            const int sh = mbn >= 3 ? 2 : mbn - 1;           // log2(S)
+            const int m0 = (int)(((uint32_t)p - tb) & 3u);   // this warp's first slot of the unit
+            const int mb = m0 & ((1 << sh) - 1);
+            const int nslots = nbn << sh;
+            tb += (uint32_t)nslots;
+            if (mb < mbn) {
                 const int hl = mb * 128 + q4 * 32 + lane;
+                if (T.h.rowseq != cur_seq || mb != cur_mb) {
+                    flush();
+                    cur_seq = T.h.rowseq; cur_mb = mb;
+                    cur_idx = hl < hcount ? T.h.cnt_row + hl : -1;
+                }
+                const t2_row &R = S.rows[T.h.rowbuf];
                 const float4 hh = R.H[hl];
-                const float mu = __fadd_rn(__fadd_rn(fabsf(__fsub_rn(hh.x, ucx)), fabsf(__fsub_rn(hh.y, ucy))), uext);
-                const float Tt = __fmaf_rn(bc.erel, mu, __fmaf_rn(bc.kabs_tc, __fadd_rn(hh.z, ext), bc.abs_floor));
-                int neg = 0;
-                uint32_t dm = 0u;
-                t2_wait(a_full, (tt >> 2) & 1u, 1);
-                tc_fence_after();
-                tc_ld32(tmem_row, v0);
-                tc_ld32(tmem_row + 32u, v1);
-                landed();
-                tc_group(v0, Tt, neg, dm, 1u);
-                tc_ld32(tmem_row + 64u, v0);
-                tc_group(v1, Tt, neg, dm, 2u);
-                tc_ld32(tmem_row + 96u, v1);
-                landed();
-                tc_fence_before();          // the whole tile is in registers: its TMEM buffer is free
-                if (lane0) tc_bar_arrive(a_empty);
-                tc_group(v0, Tt, neg, dm, 4u);
-                tc_group(v1, Tt, neg, dm, 8u);
-                if (hl < hcount) {
-                    const int c = K3_GROUP * (4 - __popc(dm)) - sign_lanes_total(neg);
-                    cnt[0] += mb == 0 ? c : 0; cnt[1] += mb == 1 ? c : 0; cnt[2] += mb == 2 ? c : 0; cnt[3] += mb == 3 ? c : 0;
+                const float mu = __fadd_rn(__fadd_rn(fabsf(__fsub_rn(hh.x, T.h.ucx)), fabsf(__fsub_rn(hh.y, T.h.ucy))), T.h.uext);
+                const float Tt = __fmaf_rn(bc.erel, mu, __fmaf_rn(bc.kabs_tc, __fadd_rn(hh.z, T.h.ext), bc.abs_floor));
+                int neg = 0, ktile = 0;
+                uint32_t dmask = 0u;   // bit 4k + g: flagged 16-pixel group g of the k-th tile this warp took from the unit
+                uint32_t v0[32], v1[32];
+#pragma unroll 1
+                for (int j = m0; j < nslots; j += 4, ++ktile) {
+                    uint32_t dm = 0u;
+                    if (!T2A(64)) T2_WAIT(a_full, used & 1u, 1);
+                    ++used;
+                    tc_fence_after();
+                    const bool ld = !T2A(2), vt = !T2A(1);
+                    if (ld) { tc_ld32(tmem_row, v0); tc_ld32(tmem_row + 32u, v1); landed(); }
+                    if (vt) tc_group(v0, Tt, neg, dm, 1u);
+                    if (ld) tc_ld32(tmem_row + 64u, v0);
+                    if (vt) tc_group(v1, Tt, neg, dm, 2u);
+                    if (ld) { tc_ld32(tmem_row + 96u, v1); landed(); }
+                    tc_fence_before();          // the whole tile is in registers: its TMEM buffer is free
+                    if (lane0 && !T2A(64)) tc_bar_arrive(a_empty);
+                    if (vt) { tc_group(v0, Tt, neg, dm, 4u); tc_group(v1, Tt, neg, dm, 8u); }
+                    else neg += v0[0] ^ v1[31];
                     dmask |= dm << (4 * ktile);
                 }
-                jlist |= (uint32_t)j << (4 * ktile);
-                ++ktile;
-            }
-            tb += (uint32_t)(mbn * nbn);
-            // queue the flagged (hypothesis, group) pairs for k_count_tc_deferred: one reservation per warp and unit
-            const int mine = __popc(dmask);
-            if (__any_sync(0xffffffffu, mine)) {
-                int incl = mine;
+                if (T2A(16) || cur_idx < 0) dmask = 0u;
+                if (cur_idx >= 0) cnt += K3_GROUP * (4 * ktile - __popc(dmask)) - sign_lanes_total(neg);
+                // queue the flagged (hypothesis, group) pairs for k_count_tc_deferred: one reservation per warp and unit
+                const int mine = __popc(dmask);
+                if (__any_sync(0xffffffffu, mine)) {
+                    int incl = mine;
 #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int up = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += up;
-                }
-                int base = 0;
-                if (lane == 31) base = atomicAdd(&S.qn, incl);
-                int q = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
-                const int chunk = T.h.chunk, vi = T.h.vi, hbase = T.h.hbase;
-                while (dmask) {
-                    const int bitn = __ffs(dmask) - 1;
-                    dmask &= dmask - 1;
-                    const int j = (int)((jlist >> (4 * (bitn >> 2))) & 15u);
-                    const int mb = j / nbn, nb = j - mb * nbn;
-                    const int hl = mb * 128 + q4 * 32 + lane;
-                    const int grp = nb * 4 + (bitn & 3);  // 16-pixel group within the chunk
-                    if (q < ws.tcq_slice_cap) {
-                        slice[q] = t2_entry(chunk, hbase + hl, grp, vi);
-                    } else {  // slice full (pathological inputs): the reference's own decision for the whole group, in line
-                        const int4 e = __ldg(&ws.chunk_tab[chunk]);
-                        const float2 hv = ws.hyp[cur_row + hl];
-                        const int n = e.z & 0x7fff;
-                        int c = 0;
-                        for (int jj = grp * K3_GROUP; jj < min(n, (grp + 1) * K3_GROUP); ++jj) {
-                            const float2 dir = ws.pix_dir[(long long)vi * ws.cap + e.y + jj];
-                            const uint32_t xy = ws.pix_xy[e.y + jj];
-                            c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
-                                                hv.x, hv.y, d.thresh) ? 1 : 0;
-                            ++amb_local;
-                        }
-                        if (c) atomicAdd(&ws.counts[cur_row + hl], c);
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += up;
                     }
-                    ++q;
+                    int base = 0;
+                    if (lane == 31) base = atomicAdd(&S.qn, incl);
+                    int q = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
+                    const int pool0 = T.h.pool0, vi = T.h.vi, n = T.h.n;
+                    const uint32_t corg = T.h.corg;
+                    const int nb0 = m0 >> sh, nbstep = 4 >> sh;
+                    while (dmask) {
+                        const int bitn = __ffs(dmask) - 1;
+                        dmask &= dmask - 1;
+                        const int grp = (nb0 + (bitn >> 2) * nbstep) * 4 + (bitn & 3);  // 16-pixel group within the chunk
+                        if (q < ws.tcq_slice_cap) {
+                            slice[q] = t2_entry(pool0 + grp * K3_GROUP, cur_idx, max(0, min(K3_GROUP, n - grp * K3_GROUP)), vi, corg);
+                        } else {  // slice full (pathological inputs): the reference's own decision for the whole group, in line
+                            const float2 hv = ws.hyp[cur_idx];
+                            int c = 0;
+                            for (int jj = grp * K3_GROUP; jj < min(n, (grp + 1) * K3_GROUP); ++jj) {
+                                const float2 dir = ws.pix_dir[(long long)vi * ws.cap + pool0 + jj];
+                                const uint32_t xy = ws.pix_xy[pool0 + jj];
+                                c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
+                                                    hv.x, hv.y, d.thresh) ? 1 : 0;
+                                ++amb_local;
+                            }
+                            cnt += c;
+                        }
+                        ++q;
+                    }
                 }
             }
             __syncwarp();
@@ -270,40 +302,57 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
             if (++s == T2_NS) { s = 0; ph ^= 1u; }
         }
         flush();
+        T2_PROF_PRINT("voter  ");
         if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
     } else {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_OTHER));
+        T2_PROF_DECL
         if (warp == T2_MMA_WARP) {
-            // ================= MMA issuer: one thread =================
-            if (lane == 0) {
-                // kind::tf32: D = f32 (bit 4), A = B = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
-                const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T2_TILE_COLS >> 3) << 17) | ((128u >> 4) << 24);
-                uint32_t t = 0, s = 0, ph = 0;
-                for (;;) {
-                    t2_stage &T = S.st[s];
-                    t2_wait(&S.bar_ready[s], ph, 102);
-                    if (T.h.stop) break;
-                    const int mbn = T.h.mbn, nbn = T.h.nbn;
-                    const t2_row &R = S.rows[T.h.rowbuf];
-                    tc_fence_after();
-                    for (int mb = 0; mb < mbn; ++mb) {
-                        const uint64_t da = tc_desc(tc_saddr(&R.A[0][mb * 128]), sizeof(R.A[0]), 128);
-                        for (int nb = 0; nb < nbn; ++nb, ++t) {
-                            const uint32_t buf = t & 3u;
-                            if (t >= 4) t2_wait(&S.bar_empty[buf], ((t >> 2) - 1u) & 1u, 103);
-                            tc_fence_after();
-                            const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * T2_TILE_COLS]), sizeof(T.B[0]), 128);
+            // ================= MMA issuer: one warp, warp-uniform control flow, one elected lane issues =================
+            // (A single diverged thread made the compiler shuttle every operand of the uniform-datapath instructions through
+            // R2UR / ELECT / BRA.U.ANY sequences: ~50 dependent instructions per tile, and with one tile per ~570 cycles the
+            // issuer -- not the voters -- bounded the kernel.  Warp-uniform loops keep the descriptors in uniform registers.)
+            // kind::tf32: D = f32 (bit 4), A = B = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T2_TILE_COLS >> 3) << 17) | ((128u >> 4) << 24);
+            const uint32_t full0 = tc_saddr(&S.bar_full[0]), empty0 = tc_saddr(&S.bar_empty[0]);
+            uint32_t t = 0, s = 0, ph = 0;
+            uint32_t cpar = 0u;   // bit b: parity of the number of tiles issued into buffer b; bit 4 + b: buffer b has been used
+            for (;;) {
+                t2_stage &T = S.st[s];
+                T2_WAIT(&S.bar_ready[s], ph, 2);
+                if (T.h.stop) break;
+                const int mbn = T.h.mbn, nbn = T.h.nbn;
+                const int sn = mbn >= 3 ? 4 : mbn;   // slots per 64-pixel quarter (see the voters)
+                const t2_row &R = S.rows[T.h.rowbuf];
+                tc_fence_after();
+                // descriptors advance linearly: 128 rows x 16 B = 2048 B = 128 units of 16 B in the start-address field
+                const uint64_t da0 = tc_desc(tc_saddr(&R.A[0][0]), sizeof(R.A[0]), 128);
+                uint64_t db = tc_desc(tc_saddr(&T.B[0][0]), sizeof(T.B[0]), 128);
+                for (int nb = 0; nb < nbn; ++nb, db += 128) {
+                    uint64_t da = da0;
+                    for (int mb = 0; mb < sn; ++mb, ++t, da += 128) {
+                        if (mb >= mbn) continue;   // empty slot (3 M-blocks)
+                        const uint32_t buf = t & 3u;
+                        // the n-th tile of a buffer (n >= 1) needs the release of its (n-1)-th: phase n - 1 of `empty`
+                        if (((cpar >> (4 + buf)) & 1u) && !T2A(32) && !T2A(64)) T2_WAIT(empty0 + 8u * buf, ((cpar >> buf) & 1u) ^ 1u, 3);
+                        cpar = (cpar ^ (1u << buf)) | (16u << buf);
+                        tc_fence_after();
+                        if (T2A(8)) {
+                            if (lane == 0) tc_bar_arrive(full0 + 8u * buf);
+                        } else if (tc_elect_one()) {
                             asm volatile(
                                 "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * (uint32_t)T2_TILE_COLS),
                                 "l"(da), "l"(db), "r"(idesc), "r"(0));
                             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                             tc_saddr(&S.bar_full[buf])) : "memory");
+                                             full0 + 8u * buf) : "memory");
                         }
+                        __syncwarp();
                     }
-                    if (++s == T2_NS) { s = 0; ph ^= 1u; }
                 }
+                if (++s == T2_NS) { s = 0; ph ^= 1u; }
             }
+            T2_PROF_PRINT("issuer ");
             __syncwarp();
         } else {
             // ================= builders: warp b owns units b, b + NB, ... of this CTA's range =================
@@ -330,7 +379,7 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
             };
             // raw inputs of unit k (entry e) -> raw slot `slot` of this builder: two bulk copies, lane 0
             auto fetch_raw = [&](uint32_t k, const int4 &e, int slot) {
-                if (e.x < 0 || lane != 0) return;
+                if (e.x < 0 || lane != 0 || T2A(128)) return;
                 uint32_t ci, rg;
                 locate(k, ci, rg);
                 const int vi = (int)(rg / npass), n = e.z & 0x7fff;
@@ -374,9 +423,9 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
 
                 if (new_row) {
                     // the row buffer's previous occupant (3 rows back) ended with a unit <= k - 3: the voters (in order) are past it
-                    if (k >= 3) t2_wait(&S.bar_done[(k - 3) % T2_NS], ((k - 3) / T2_NS) & 1u, 4);
+                    if (k >= 3) T2_WAIT(&S.bar_done[(k - 3) % T2_NS], ((k - 3) / T2_NS) & 1u, 4);
                     t2_row &R = S.rows[rowbuf];
-                    for (int hl = lane; hl < mbn * 128; hl += 32) {
+                    for (int hl = lane; hl < mbn * 128 && !T2A(256); hl += 32) {
                         const float2 hv = hl < hcount ? ws.hyp[hrow + hl] : make_float2(0.f, 0.f);
                         float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy);
                         float mm = __fadd_rn(fabsf(hx), fabsf(hy));
@@ -391,14 +440,14 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                     }
                 }
                 // stage s is free once the voters are done with unit k - NS
-                if (k >= T2_NS) t2_wait(&S.bar_done[s], (kd - 1u) & 1u, 5);
-                t2_wait(&S.bar_raw[bw][slot], (it >> 1) & 1u, 6);   // raw inputs of unit k have landed
+                if (k >= T2_NS) T2_WAIT(&S.bar_done[s], (kd - 1u) & 1u, 5);
+                if (!T2A(128)) T2_WAIT(&S.bar_raw[bw][slot], (it >> 1) & 1u, 6);   // raw inputs of unit k have landed
                 t2_stage &T = S.st[s];
                 const t2_raw &W = S.raw[bw][slot];
                 // ---- pixel constants in the image's frame, TF32-split, as B rows ----
                 int ext = 0, uext = 0;
                 const int ucx = (int)((uint32_t)eA.w & 0xffffu) - ox, ucy = (int)((uint32_t)eA.w >> 16) - oy;  // the unit's centre
-                for (int j = lane; j < nbn * T2_TILE_PX; j += 32) {
+                for (int j = lane; j < nbn * T2_TILE_PX && !T2A(4); j += 32) {
                     float px = 0.f, py = 0.f, pz = -1e30f, qx = 0.f, qy = 0.f, qz = -1e30f;  // m = -2e30: never an inlier, never in the band
                     if (j < n) {
                         const float4 pq = W.pq[j];
@@ -426,7 +475,7 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                 if (lane == 0) {
                     t2_hdr &h = T.h;
                     h.stop = 0; h.n = n; h.mbn = mbn; h.nbn = nbn; h.hcount = hcount; h.rowbuf = rowbuf; h.rowseq = (int)rowseq;
-                    h.chunk = (int)ci; h.vi = vi; h.hbase = hbase;
+                    h.pool0 = eA.y; h.vi = vi; h.hbase = hbase; h.corg = (uint32_t)eA.w;
                     h.ext = (float)ext; h.ucx = (float)ucx; h.ucy = (float)ucy; h.uext = (float)uext;
                     h.cnt_row = hrow;
                 }
@@ -438,9 +487,10 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
             // the builder that would own unit `nunits` publishes the stop marker in its stage
             if (nunits % NB == (uint32_t)bw) {
                 const uint32_t k = nunits, s = k % T2_NS;
-                if (k >= T2_NS) t2_wait(&S.bar_done[s], (k / T2_NS - 1u) & 1u, 7);
+                if (k >= T2_NS) T2_WAIT(&S.bar_done[s], (k / T2_NS - 1u) & 1u, 7);
                 if (lane == 0) { S.st[s].h.stop = 1; tc_bar_arrive(&S.bar_ready[s]); }
             }
+            T2_PROF_PRINT("builder");
             __syncwarp();
         }
     }
@@ -459,57 +509,58 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
 //            the pre-pass constants, r formed in fp32 (one rounded product, one fma).  |m| > T decides (bound: DESIGN.md 4a,
 //            T = krel * (|hx| + |hy| + extent of the lane's pixels) + floor, the FP32-pipe kernel's band);
 //   phase B  the tests inside that band get the reference's exact rounding sequence (pvv_exact_test), densely packed.
-// Grid: blockIdx.x = slice + tcq_slices * part; `parts` CTAs stride over the entries of one slice.
+// Grid: blockIdx.x = slice + tcq_slices * part; `parts` CTAs stride over the entries of one slice.  Everything a lane
+// needs is in the entry, so its loads (hypothesis, 8 x constants, 8 x coordinates) are issued together.
 constexpr int T2_DEF_THREADS = 256;
 __global__ void __launch_bounds__(T2_DEF_THREADS) k_count_tc_deferred(pvv_dims d, pvv_ws ws, band_consts bc, int parts)
 {
     constexpr int EPB = T2_DEF_THREADS / 2;               // entries per CTA and step
-    __shared__ uint32_t s_q2[EPB * K3_GROUP];              // phase B: (local entry << 8) | pixel within the chunk
+    __shared__ uint32_t s_q2[EPB * K3_GROUP];              // phase B: (local entry << 8) | pixel within the group
     __shared__ int s_q2n;
     pvv_pdl_enter();
     const int tid = threadIdx.x;
     const int slice = blockIdx.x % ws.tcq_slices, part = blockIdx.x / ws.tcq_slices;
     const int total = min(ws.tcq_cnt[slice], ws.tcq_slice_cap);
-    const uint2 *q = ws.tcq + (size_t)slice * ws.tcq_slice_cap;
+    const uint4 *q = ws.tcq + (size_t)slice * ws.tcq_slice_cap;
     unsigned long long amb_local = 0;
     for (int base = part * EPB; base < total; base += parts * EPB) {
         if (tid == 0) s_q2n = 0;
         __syncthreads();
         const int le = tid >> 1, ei = base + le;
         if (ei < total) {
-            const uint2 en = q[ei];
-            const int hyp = (int)(en.y & 0xffffu), grp = (int)((en.y >> 16) & 0xfu), vi = (int)(en.y >> 20);
-            const int4 e = __ldg(&ws.chunk_tab[en.x]);
-            const int n = e.z & 0x7fff;
-            const long long row = ((long long)e.x * d.vn + vi) * ws.hn_pad;
-            const float2 hv = ws.hyp[row + hyp];
-            const int ox = (int)((uint32_t)e.w & 0xffffu), oy = (int)((uint32_t)e.w >> 16);
+            const uint4 en = q[ei];
+            const int nvalid = (int)(en.z & 0xffu), vi = (int)(en.z >> 8);
+            const int j0 = (tid & 1) * (K3_GROUP / 2);
+            const float4 *pq = ws.pix_pq + (long long)vi * ws.cap + en.x;
+            const uint32_t *pxy = ws.pix_xy + en.x;
+            float4 c[K3_GROUP / 2];
+            uint32_t xy[K3_GROUP / 2];
+#pragma unroll
+            for (int u = 0; u < K3_GROUP / 2; ++u) {   // all loads first
+                const bool ok = j0 + u < nvalid;
+                c[u] = ok ? pq[j0 + u] : make_float4(0.f, 0.f, 0.f, 0.f);
+                xy[u] = ok ? pxy[j0 + u] : 0u;
+            }
+            const float2 hv = ws.hyp[en.y];
+            const int ox = (int)(en.w & 0xffffu), oy = (int)(en.w >> 16);
             float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy);
-            float mm = __fadd_rn(fabsf(hx), fabsf(hy));
+            const float mm = __fadd_rn(fabsf(hx), fabsf(hy));
             const bool far = !(mm < 1e15f);
             if (far) { hx = 0.f; hy = 0.f; }
-            const int j0 = grp * K3_GROUP + (tid & 1) * (K3_GROUP / 2);
-            const float4 *pq = ws.pix_pq + (long long)vi * ws.cap + e.y;
-            const uint32_t *pxy = ws.pix_xy + e.y;
             float m[K3_GROUP / 2];
             int ext = 0;
 #pragma unroll
             for (int u = 0; u < K3_GROUP / 2; ++u) {
-                const int j = j0 + u;
                 m[u] = -1e30f;   // padded pixel / pixel the reference never counts: not an inlier, not in the band
-                if (j < n) {
-                    const float4 c = pq[j];
-                    const uint32_t xy = pxy[j];
-                    if (c.x != 0.f || c.y != 0.f) {
-                        const int ix = (int)(xy & 0xffffu) - ox, iy = (int)(xy >> 16) - oy;
-                        const float fx = (float)ix, fy = (float)iy;
-                        const float ra = -__fmaf_rn(fx, c.x, __fmul_rn(fy, c.y));
-                        const float rc = -__fmaf_rn(fx, c.z, __fmul_rn(fy, c.w));
-                        const float a = __fmaf_rn(hx, c.x, __fmaf_rn(hy, c.y, ra));
-                        const float tc = __fmaf_rn(hx, c.z, __fmaf_rn(hy, c.w, rc));
-                        m[u] = __fsub_rn(a, fabsf(tc));
-                        ext = max(ext, abs(ix) + abs(iy));
-                    }
+                if (c[u].x != 0.f || c[u].y != 0.f) {
+                    const int ix = (int)(xy[u] & 0xffffu) - ox, iy = (int)(xy[u] >> 16) - oy;
+                    const float fx = (float)ix, fy = (float)iy;
+                    const float ra = -__fmaf_rn(fx, c[u].x, __fmul_rn(fy, c[u].y));
+                    const float rc = -__fmaf_rn(fx, c[u].z, __fmul_rn(fy, c[u].w));
+                    const float a = __fmaf_rn(hx, c[u].x, __fmaf_rn(hy, c[u].y, ra));
+                    const float tc = __fmaf_rn(hx, c[u].z, __fmaf_rn(hy, c[u].w, rc));
+                    m[u] = __fsub_rn(a, fabsf(tc));
+                    ext = max(ext, abs(ix) + abs(iy));
                 }
             }
             const float T = far ? __int_as_float(0x7f800000) : __fmaf_rn(bc.krel, __fadd_rn(mm, (float)ext), bc.abs_floor);
@@ -518,26 +569,23 @@ __global__ void __launch_bounds__(T2_DEF_THREADS) k_count_tc_deferred(pvv_dims d
             for (int u = 0; u < K3_GROUP / 2; ++u) {
                 if (fabsf(m[u]) > T) {
                     sure += m[u] > 0.f;
-                } else if (j0 + u < n) {   // (padded pixels only get here when the band is infinite)
+                } else if (j0 + u < nvalid) {   // (padded pixels only get here when the band is infinite)
                     s_q2[atomicAdd(&s_q2n, 1)] = ((uint32_t)le << 8) | (uint32_t)(j0 + u);
                 }
             }
-            if (sure) atomicAdd(&ws.counts[row + hyp], sure);
+            if (sure) atomicAdd(&ws.counts[en.y], sure);
         }
         __syncthreads();
         const int q2 = s_q2n;
         for (int idx = tid; idx < q2; idx += T2_DEF_THREADS) {
             const uint32_t ent = s_q2[idx];
-            const uint2 en = q[base + (int)(ent >> 8)];
-            const int j = (int)(ent & 0xffu);
-            const int hyp = (int)(en.y & 0xffffu), vi = (int)(en.y >> 20);
-            const int4 e = __ldg(&ws.chunk_tab[en.x]);
-            const long long row = ((long long)e.x * d.vn + vi) * ws.hn_pad;
-            const float2 hv = ws.hyp[row + hyp];
-            const float2 dir = ws.pix_dir[(long long)vi * ws.cap + e.y + j];
-            const uint32_t xy = ws.pix_xy[e.y + j];
+            const uint4 en = q[base + (int)(ent >> 8)];
+            const int j = (int)(ent & 0xffu), vi = (int)(en.z >> 8);
+            const float2 hv = ws.hyp[en.y];
+            const float2 dir = ws.pix_dir[(long long)vi * ws.cap + en.x + j];
+            const uint32_t xy = ws.pix_xy[en.x + j];
             if (pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16), hv.x, hv.y, d.thresh))
-                atomicAdd(&ws.counts[row + hyp], 1);
+                atomicAdd(&ws.counts[en.y], 1);
             ++amb_local;
         }
         __syncthreads();
