@@ -704,7 +704,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         const bool few = variant == 9 || (variant == 7 && d.thresh <= 0.995f);
         e = few ? launch_count_tc<3>(d, ws, bc, sms, st) : launch_count_tc<7>(d, ws, bc, sms, st);
     }
-    else if (variant == 10) e = launch_count_tc2<3>(d, ws, bc, sms, st, launches);
+    else if (variant == 10) e = launch_count_tc2<4>(d, ws, bc, sms, st, launches);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);

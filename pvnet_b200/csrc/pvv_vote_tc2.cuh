@@ -29,13 +29,13 @@
 // development ablations (tools/t2_ablate.py, -DPVV_K3_ABLATE builds only): PVV_K3_ABLATE = bits << 16
 //   1 no vote   2 no TMEM loads   4 builders publish without building B   8 no MMA (plain arrive)   16 no queue pushes
 //   32 issuer does not wait for free accumulators   64 voters neither wait for tiles nor hand them back
-//   128 builders fetch no raw inputs   256 builders build no A rows
+//   128 builders fetch no raw inputs   256 builders build no A rows   512 no tcgen05 fences in the tile loops
 #define T2A(bit) K3_ABL((bit) << 16)
 
 constexpr int T2_NS = 6;         // stage ring: B operand + header of units k .. k+5
 constexpr int T2_NROW = 3;       // row ring: a row buffer is rewritten 3 rows later
 constexpr int T2_VOTER_WARPS = 16;
-constexpr int T2_MMA_WARP = 16;
+constexpr int T2_MMA_WARP = 16;                // first builder warp: owns the TMEM allocation (there is no dedicated MMA warp)
 constexpr int T2_TILE_PX = 64;                 // pixels per MMA tile
 constexpr int T2_TILE_COLS = 2 * T2_TILE_PX;   // N of one MMA = TMEM columns of one accumulator buffer: 4 buffers fill the SM's 512
 #ifndef T2_WAIT_MODE
@@ -46,13 +46,13 @@ constexpr uint32_t T2_SUSPEND_NS = 20000;   // try_wait suspend-time hint; the h
 // setmaxnreg moves registers inside the CTA's pool, which is what the CTA was LAUNCHED with (threads x launch registers),
 // not the SM's whole file (measured on the B200: with a split that needed more, exactly the voters that found the 1024
 // registers left over per sub-partition started and the rest waited forever).  ptxas caps the launch count at
-// floor(65536 / threads / 8) * 8, so for NB = 3: 640 threads x 96 = 61440 = 512 x 104 + 128 x 64.
-// NB + 1 must be a multiple of 4: setmaxnreg is executed by whole warpgroups.
+// floor(65536 / threads / 8) * 8, so for NB = 4: 640 threads x 96 = 61440 = 512 x 104 + 128 x 64.
+// NB must be a multiple of 4: setmaxnreg is executed by whole warpgroups.
 template <int NB> struct t2_cfg {
-    static_assert(NB == 3, "register split worked out for 3 builder warps");
-    static constexpr int threads = (T2_VOTER_WARPS + 1 + NB) * 32;
+    static_assert(NB == 4, "register split worked out for 4 builder warps");
+    static constexpr int threads = (T2_VOTER_WARPS + NB) * 32;
     static constexpr int regs_launch = 96, regs_voter = 104, regs_other = 64;
-    static_assert(T2_VOTER_WARPS * 32 * regs_voter + (1 + NB) * 32 * regs_other == threads * regs_launch, "setmaxnreg pool");
+    static_assert(T2_VOTER_WARPS * 32 * regs_voter + NB * 32 * regs_other == threads * regs_launch, "setmaxnreg pool");
 };
 
 struct t2_hdr {                   // written by the unit's builder (lane 0), read by the voters and the MMA issuer
@@ -192,6 +192,12 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_VOTER));
         T2_PROF_DECL
         const int q4 = warp & 3, p = warp >> 2;
+        // The MMAs of buffer p are issued by team p itself: its leader warp (the one with q4 == p, so the four leaders sit on
+        // four different schedulers) waits until its three siblings have pulled the tile, then issues the team's next tile.
+        // A single in-order issuer warp took ~250 cycles per tile (try_wait + issue + commit are a serial latency chain), as
+        // long as the four teams vote on a round of four tiles: it, not the vote, bounded the kernel.  Here that latency
+        // belongs to one team and is hidden by the other three teams of the scheduler.
+        const bool leader = q4 == p;
         uint32_t a_full = tc_saddr(&S.bar_full[p]), a_empty = tc_saddr(&S.bar_empty[p]);
         uint32_t tmem_row = tmem + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(p * T2_TILE_COLS);
         uint32_t lane0 = lane == 0;
@@ -215,11 +221,59 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
         };
         auto landed = [&] { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); };
 
+        // issue cursor of the leader: walks the same (unit, slot) sequence as the vote loop, one tile ahead
+        // kind::tf32: D = f32 (bit 4), A = B = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T2_TILE_COLS >> 3) << 17) | ((128u >> 4) << 24);
+        uint32_t is = 0, iph = 0, itb = 0, n_iss = 0, iunit = 0, vunit = 0;
+        int ij = -1;           // next slot of this team in the unit the cursor is in (-1: not positioned yet)
+        bool idone = false;
+        // Issues the team's next tile if none is in flight.  Called before the loop, at the top of every unit and after every
+        // release.  The cursor never runs more than 2 units ahead of the vote loop: the builder of unit k waits, when k opens a
+        // row, until the voters are done with unit k - 3 (row ring), so units beyond vunit + 2 may depend on this very warp's
+        // progress.  A team without tiles (3 M-blocks) just trails along.
+        auto issue_next = [&] {
+            while (!idone && n_iss == used && iunit <= vunit + 2) {
+                t2_stage &U = S.st[is];
+                T2_WAIT(&S.bar_ready[is], iph, 4);
+                if (U.h.stop) { idone = true; break; }
+                const int umbn = U.h.mbn, ush = umbn >= 3 ? 2 : umbn - 1, unslots = U.h.nbn << ush;
+                const int um0 = (int)(((uint32_t)p - itb) & 3u), umb = um0 & ((1 << ush) - 1);
+                if (ij < 0) ij = um0;
+                if (umb < umbn && ij < unslots) {
+                    // the n-th tile of the buffer (n >= 1) needs the release of its (n-1)-th by all four warps of the team
+                    if (n_iss && !T2A(64)) T2_WAIT(a_empty, (n_iss - 1u) & 1u, 3);
+                    ++n_iss;
+                    if (!T2A(512)) tc_fence_after();
+                    // descriptors advance linearly: 128 rows x 16 B = 2048 B = 128 units of 16 B in the start-address field
+                    const uint64_t da = tc_desc(tc_saddr(&S.rows[U.h.rowbuf].A[0][0]), sizeof(S.rows[0].A[0]), 128) + (uint64_t)(umb * 128);
+                    const uint64_t db = tc_desc(tc_saddr(&U.B[0][0]), sizeof(U.B[0]), 128) + (uint64_t)((ij >> ush) * 128);
+                    if (T2A(8)) {
+                        if (lane == 0) tc_bar_arrive(a_full);
+                    } else if (tc_elect_one()) {
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + (uint32_t)(p * T2_TILE_COLS)),
+                            "l"(da), "l"(db), "r"(idesc), "r"(0));
+                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(a_full) : "memory");
+                    }
+                    __syncwarp();
+                    ij += 4;
+                    break;
+                }
+                itb += (uint32_t)unslots;   // no (further) slot of this team in the unit: on to the next one
+                ij = -1;
+                ++iunit;
+                if (++is == T2_NS) { is = 0; iph ^= 1u; }
+            }
+        };
+        if (leader) issue_next();
+
         uint32_t s = 0, ph = 0;
-        for (;;) {
+        for (;; ++vunit) {
             t2_stage &T = S.st[s];
             T2_WAIT(&S.bar_ready[s], ph, 2);
             if (T.h.stop) break;
+            if (leader) issue_next();
             const int mbn = T.h.mbn, nbn = T.h.nbn, hcount = T.h.hcount;
             const int sh = mbn >= 3 ? 2 : mbn - 1;           // log2(S)
             const int m0 = (int)(((uint32_t)p - tb) & 3u);   // this warp's first slot of the unit
@@ -245,16 +299,18 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
                     uint32_t dm = 0u;
                     if (!T2A(64)) T2_WAIT(a_full, used & 1u, 1);
                     ++used;
-                    tc_fence_after();
+                    if (!T2A(512)) tc_fence_after();
                     const bool ld = !T2A(2), vt = !T2A(1);
                     if (ld) { tc_ld32(tmem_row, v0); tc_ld32(tmem_row + 32u, v1); landed(); }
                     if (vt) tc_group(v0, Tt, neg, dm, 1u);
                     if (ld) tc_ld32(tmem_row + 64u, v0);
                     if (vt) tc_group(v1, Tt, neg, dm, 2u);
                     if (ld) { tc_ld32(tmem_row + 96u, v1); landed(); }
-                    tc_fence_before();          // the whole tile is in registers: its TMEM buffer is free
+                    if (!T2A(512)) tc_fence_before();          // the whole tile is in registers: its TMEM buffer is free
                     if (lane0 && !T2A(64)) tc_bar_arrive(a_empty);
-                    if (vt) { tc_group(v0, Tt, neg, dm, 4u); tc_group(v1, Tt, neg, dm, 8u); }
+                    if (vt) tc_group(v0, Tt, neg, dm, 4u);
+                    if (leader) issue_next();   // the siblings have released the buffer by now (same tile, other schedulers)
+                    if (vt) tc_group(v1, Tt, neg, dm, 8u);
                     else neg += v0[0] ^ v1[31];
                     dmask |= dm << (4 * ktile);
                 }
@@ -307,56 +363,9 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
     } else {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_OTHER));
         T2_PROF_DECL
-        if (warp == T2_MMA_WARP) {
-            // ================= MMA issuer: one warp, warp-uniform control flow, one elected lane issues =================
-            // (A single diverged thread made the compiler shuttle every operand of the uniform-datapath instructions through
-            // R2UR / ELECT / BRA.U.ANY sequences: ~50 dependent instructions per tile, and with one tile per ~570 cycles the
-            // issuer -- not the voters -- bounded the kernel.  Warp-uniform loops keep the descriptors in uniform registers.)
-            // kind::tf32: D = f32 (bit 4), A = B = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T2_TILE_COLS >> 3) << 17) | ((128u >> 4) << 24);
-            const uint32_t full0 = tc_saddr(&S.bar_full[0]), empty0 = tc_saddr(&S.bar_empty[0]);
-            uint32_t t = 0, s = 0, ph = 0;
-            uint32_t cpar = 0u;   // bit b: parity of the number of tiles issued into buffer b; bit 4 + b: buffer b has been used
-            for (;;) {
-                t2_stage &T = S.st[s];
-                T2_WAIT(&S.bar_ready[s], ph, 2);
-                if (T.h.stop) break;
-                const int mbn = T.h.mbn, nbn = T.h.nbn;
-                const int sn = mbn >= 3 ? 4 : mbn;   // slots per 64-pixel quarter (see the voters)
-                const t2_row &R = S.rows[T.h.rowbuf];
-                tc_fence_after();
-                // descriptors advance linearly: 128 rows x 16 B = 2048 B = 128 units of 16 B in the start-address field
-                const uint64_t da0 = tc_desc(tc_saddr(&R.A[0][0]), sizeof(R.A[0]), 128);
-                uint64_t db = tc_desc(tc_saddr(&T.B[0][0]), sizeof(T.B[0]), 128);
-                for (int nb = 0; nb < nbn; ++nb, db += 128) {
-                    uint64_t da = da0;
-                    for (int mb = 0; mb < sn; ++mb, ++t, da += 128) {
-                        if (mb >= mbn) continue;   // empty slot (3 M-blocks)
-                        const uint32_t buf = t & 3u;
-                        // the n-th tile of a buffer (n >= 1) needs the release of its (n-1)-th: phase n - 1 of `empty`
-                        if (((cpar >> (4 + buf)) & 1u) && !T2A(32) && !T2A(64)) T2_WAIT(empty0 + 8u * buf, ((cpar >> buf) & 1u) ^ 1u, 3);
-                        cpar = (cpar ^ (1u << buf)) | (16u << buf);
-                        tc_fence_after();
-                        if (T2A(8)) {
-                            if (lane == 0) tc_bar_arrive(full0 + 8u * buf);
-                        } else if (tc_elect_one()) {
-                            asm volatile(
-                                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * (uint32_t)T2_TILE_COLS),
-                                "l"(da), "l"(db), "r"(idesc), "r"(0));
-                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                             full0 + 8u * buf) : "memory");
-                        }
-                        __syncwarp();
-                    }
-                }
-                if (++s == T2_NS) { s = 0; ph ^= 1u; }
-            }
-            T2_PROF_PRINT("issuer ");
-            __syncwarp();
-        } else {
+        {
             // ================= builders: warp b owns units b, b + NB, ... of this CTA's range =================
-            const int bw = warp - (T2_MMA_WARP + 1);
+            const int bw = warp - T2_VOTER_WARPS;
             // This CTA's contiguous range of units, in (keypoint, pass, chunk) order: unit k = global unit u_lo + k
             const uint32_t npass = (uint32_t)(d.hn + TC_PASS_H - 1) / TC_PASS_H;
             const uint32_t nchunks = (uint32_t)ws.chunk_start[d.b];
