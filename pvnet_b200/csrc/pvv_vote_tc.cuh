@@ -168,6 +168,14 @@ __device__ __forceinline__ void tc_bar_arrive(uint32_t bar_saddr)
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 
+// one lane of a converged warp (elect.sync): the lane that issues tcgen05.mma / tcgen05.commit
+__device__ __forceinline__ bool tc_elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.b32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes)
 {
     // K-major, SWIZZLE_NONE, descriptor version 1 (sm_100): start >> 4 | LBO >> 4 << 16 | SBO >> 4 << 32 | 1 << 46
@@ -415,9 +423,13 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
     } else {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TC_REGS_OTHER));
         if (warp == TC_MMA_WARP) {
-            // ================= MMA issuer: one thread =================
-            if (lane == 0) {
+            // ================= MMA issuer: one warp, warp-uniform control flow, one elected lane issues =================
+            // (Round 1 ran this loop in a single diverged thread: the compiler then shuttles every operand of the uniform-
+            // datapath instructions through R2UR / ELECT / BRA.U.ANY sequences, ~50 dependent instructions per tile on the
+            // critical path of a two-deep accumulator ring.  With warp-uniform loops the descriptors live in uniform registers.)
+            {
                 const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(256 >> 3) << 17) | ((128u >> 4) << 24);
+                const uint32_t full0 = tc_saddr(&S.bar_full[0]), empty0 = tc_saddr(&S.bar_empty[0]);
                 uint32_t t = 0;
                 for (uint32_t k = 0;; ++k) {
                     const uint32_t s = k % TC_STAGES;
@@ -427,19 +439,24 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     const int mbn = T.mbn, nbn = T.nbn;
                     const tc_row &R = S.rows[T.row];
                     tc_fence_after();
-                    for (int mb = 0; mb < mbn && !K3_ABL(32); ++mb) {
-                        const uint64_t da = tc_desc(tc_saddr(&R.A[0][mb * 128]), sizeof(R.A[0]), 128);
-                        for (int nb = 0; nb < nbn; ++nb, ++t) {
+                    // descriptors advance linearly: 128 (256) rows x 16 B = 128 (256) units of 16 B in the start-address field
+                    uint64_t da = tc_desc(tc_saddr(&R.A[0][0]), sizeof(R.A[0]), 128);
+                    const uint64_t db0 = tc_desc(tc_saddr(&T.B[0][0]), sizeof(T.B[0]), 128);
+                    for (int mb = 0; mb < mbn && !K3_ABL(32); ++mb, da += 128) {
+                        uint64_t db = db0;
+                        for (int nb = 0; nb < nbn; ++nb, ++t, db += 256) {
                             const uint32_t buf = t & 1u;
-                            if (t >= 2) tc_bar_wait<TC_SLEEP_MMA>(&S.bar_empty[buf], ((t >> 1) - 1u) & 1u);
+                            if (t >= 2) tc_bar_wait<TC_SLEEP_MMA>(empty0 + 8u * buf, ((t >> 1) - 1u) & 1u);
                             tc_fence_after();
-                            const uint64_t db = tc_desc(tc_saddr(&T.B[0][nb * 256]), sizeof(T.B[0]), 128);
-                            asm volatile(
-                                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * 256u),
-                                "l"(da), "l"(db), "r"(idesc), "r"(0));
-                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                             tc_saddr(&S.bar_full[buf])) : "memory");
+                            if (tc_elect_one()) {
+                                asm volatile(
+                                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                    "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem + buf * 256u),
+                                    "l"(da), "l"(db), "r"(idesc), "r"(0));
+                                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                                 full0 + 8u * buf) : "memory");
+                            }
+                            __syncwarp();
                         }
                     }
                 }

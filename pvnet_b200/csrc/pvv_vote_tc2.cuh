@@ -127,14 +127,6 @@ __device__ __forceinline__ void t2_wait(uint32_t bar_saddr, uint32_t parity, int
 }
 __device__ __forceinline__ void t2_wait(unsigned long long *b, uint32_t parity, int id = 0) { t2_wait(tc_saddr(b), parity, id); }
 
-// one lane of a converged warp (elect.sync): the lane that issues tcgen05.mma / tcgen05.commit
-__device__ __forceinline__ bool tc_elect_one()
-{
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.b32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
-
 // 1-D bulk copy global -> shared (TMA), completion counted in bytes on an mbarrier of this CTA
 __device__ __forceinline__ void t2_bulk_g2s(void *smem, const void *gmem, uint32_t bytes, unsigned long long *bar)
 {
