@@ -138,6 +138,22 @@ int64_t pvv_default_pool_capacity(const pvv_job *job);
 int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, const pvv_debug *dbg);
 
 /*
+ * pvv_v3 without any device allocation by the caller or the library.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs, outputs, arithmetic and status codes as pvv_v3, but job->workspace /
+ * job->workspace_bytes are IGNORED: the scratch lives in a file-scope static __device__ array of
+ * pvv_static_workspace_bytes() = 32 MiB inside the library (every GPU that loads libpvvote.so holds it until the process
+ * exits).  A job whose pvv_workspace_bytes() exceeds that is rejected with PVV_ERR_WORKSPACE and nothing is launched
+ * (32 MiB covers e.g. 2 images of 480x640, 9 keypoints, 512 hypotheses; check with pvv_workspace_bytes()).
+ * The call makes no cudaMalloc / cudaFree / allocating library call.  All calls on one device share the one array, which
+ * keeps the previous call's contents (what must start at zero is cleared on job->stream at the start of every call):
+ * two calls that overlap on the same GPU -- different streams, threads or processes' graphs replayed concurrently --
+ * RACE; serialise them (one stream, or events).
+ */
+size_t pvv_static_workspace_bytes(void);
+int pvv_v3_noalloc(const pvv_job *job, float confidence, int max_iter, float *out_kp);
+
+/*
  * ransac_voting_layer_v5 (ransac_voting_gpu.py:769-864) = v3 + a per-keypoint confidence: the refined keypoints are
  * re-voted at the fixed threshold 0.999 (:854-856) and out_conf [b,vn] float32 = inlier count / tn (0 for skipped images).
  */

@@ -41,7 +41,7 @@ class Debug(C.Structure):
 
 # every symbol include/pvvote.h declares (tests check the library exports exactly these)
 SYMBOLS = [
-    "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_v5", "pvv_hypotheses", "pvv_motion", "pvv_cov", "pvv_workspace_bytes_host",
+    "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_v3_noalloc", "pvv_static_workspace_bytes", "pvv_v5", "pvv_hypotheses", "pvv_motion", "pvv_cov", "pvv_workspace_bytes_host",
     "pvv_v3_host", "pvv_cov_host", "pvv_generate_hypothesis", "pvv_voting_for_hypothesis", "pvv_vote_counts",
     "pvv_generate_hypothesis_vanishing_point", "pvv_voting_for_hypothesis_vanishing_point",
     "pvv_uncertainty_pnp", "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_probe_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
@@ -69,6 +69,9 @@ def lib():
     L.pvv_default_pool_capacity.restype = C.c_int64
     L.pvv_v3.argtypes = [P(Job), F, I, V, P(Debug)]
     L.pvv_v5.argtypes = [P(Job), F, I, V, V, P(Debug)]
+    L.pvv_v3_noalloc.argtypes = [P(Job), F, I, V]
+    L.pvv_static_workspace_bytes.argtypes = []
+    L.pvv_static_workspace_bytes.restype = C.c_size_t
     L.pvv_hypotheses.argtypes = [P(Job), V, V, P(Debug)]
     L.pvv_motion.argtypes = [P(Job), V]
     L.pvv_cov.argtypes = [P(Job), V, V, P(Debug)]

@@ -5,6 +5,11 @@
 
 #include "pvv_internal.cuh"
 
+// Scratch of pvv_v3_noalloc: a file-scope device array (no cudaMalloc anywhere on that path).  In host code this name is a
+// host-side stand-in, NOT a device address: its device address is taken once per device with cudaGetSymbolAddress.
+#define PVV_STATIC_WS_BYTES (32u << 20)
+static __device__ __align__(256) unsigned char g_pvv_static_ws[PVV_STATIC_WS_BYTES];
+
 namespace {
 
 thread_local int t_last_launches = 0;
@@ -253,6 +258,32 @@ int pvv_v3(const pvv_job *job, float confidence, int max_iter, float *out_kp, co
 {
     (void)confidence; (void)max_iter;  // unobservable in the reference: every round re-votes the same idxs (:553-582)
     return run_v3(job, out_kp, nullptr, dbg);
+}
+
+size_t pvv_static_workspace_bytes(void) { return (size_t)PVV_STATIC_WS_BYTES; }
+
+int pvv_v3_noalloc(const pvv_job *job, float confidence, int max_iter, float *out_kp)
+{
+    (void)confidence; (void)max_iter;
+    if (!job || !out_kp) return PVV_ERR_INVALID;
+    // device address of the static scratch: looked up once per device, with that device current (the caller's)
+    constexpr int kMaxDev = 64;
+    static void *s_ptr[kMaxDev];   // written once per device with the same value by whoever gets there first: benign
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail_cuda(e);
+    if (dev < 0 || dev >= kMaxDev) return PVV_ERR_UNSUPPORTED;
+    void *ptr = __atomic_load_n(&s_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!ptr) {
+        if ((e = cudaGetSymbolAddress(&ptr, g_pvv_static_ws)) != cudaSuccess || !ptr) return fail_cuda(e);
+        __atomic_store_n(&s_ptr[dev], ptr, __ATOMIC_RELEASE);
+    }
+    pvv_job j = *job;
+    j.workspace = ptr;
+    j.workspace_bytes = (size_t)PVV_STATIC_WS_BYTES;
+    if (j.b <= 0 || j.h <= 0 || j.w <= 0 || j.vn <= 0 || j.hn_total <= 0) return PVV_ERR_INVALID;
+    if (pvv_workspace_bytes(&j) > (size_t)PVV_STATIC_WS_BYTES) return PVV_ERR_WORKSPACE;   // beyond the static maximum
+    return run_v3(&j, out_kp, nullptr, nullptr);
 }
 
 int pvv_v5(const pvv_job *job, float confidence, int max_iter, float *out_kp, float *out_conf, const pvv_debug *dbg)
