@@ -7,6 +7,10 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
+#include <thread>
+#include <vector>
+
 #include "pvv_internal.cuh"
 
 namespace {
@@ -34,8 +38,72 @@ bool is_pinned(const void *p, void **dev_ptr)
     return false;
 }
 
+// ---- host-side narrowing of wide masks --------------------------------------------------------------------------
+// torch.argmax hands the layer an int64 mask (tools/train_linemod.py:254): 8 bytes per pixel of which 7 are zero, 79 % of
+// the bytes a host-buffer call of configs[1] used to push over PCIe.  A few host threads narrow it to one byte per pixel
+// (the value the foreground rule looks at: the low byte for `.byte()`, 0/1 for `== 1`) into a pinned staging buffer,
+// sub-batch by sub-batch, while the previous sub-batch is already crossing the bus and being voted on.
+template <typename T>
+void narrow_range(const T *src, uint8_t *dst, size_t n, int fg_rule)
+{
+    if (fg_rule == PVV_FG_EQ1) { for (size_t i = 0; i < n; ++i) dst[i] = src[i] == (T)1 ? 1 : 0; }
+    else { for (size_t i = 0; i < n; ++i) dst[i] = (uint8_t)(long long)src[i]; }   // float: truncation toward zero, like .byte()
+}
+
+// int64 (what torch.argmax produces): eight pixels per step, the low bytes (or the == 1 flags) gathered into one 64-bit
+// store -- ~3 scalar operations per pixel, so a core narrows at memory speed without any ISA-specific code
+template <>
+void narrow_range<long long>(const long long *src, uint8_t *dst, size_t n, int fg_rule)
+{
+    const uint64_t *w = (const uint64_t *)src;
+    size_t i = 0;
+    if (fg_rule == PVV_FG_EQ1) {
+        for (; i + 8 <= n; i += 8) {
+            uint64_t o = 0;
+            for (int k = 0; k < 8; ++k) o |= (uint64_t)(w[i + k] == 1u) << (8 * k);
+            memcpy(dst + i, &o, 8);
+        }
+        for (; i < n; ++i) dst[i] = w[i] == 1u ? 1 : 0;
+    } else {
+        for (; i + 8 <= n; i += 8) {
+            uint64_t o = 0;
+            for (int k = 0; k < 8; ++k) o |= (w[i + k] & 0xffu) << (8 * k);
+            memcpy(dst + i, &o, 8);
+        }
+        for (; i < n; ++i) dst[i] = (uint8_t)w[i];
+    }
+}
+
+void narrow_dispatch(const void *src, int dtype, uint8_t *dst, size_t i0, size_t n, int fg_rule)
+{
+    switch (dtype) {
+        case PVV_MASK_I64: narrow_range((const long long *)src + i0, dst + i0, n, fg_rule); break;
+        case PVV_MASK_I32: narrow_range((const int32_t *)src + i0, dst + i0, n, fg_rule); break;
+        default: narrow_range((const float *)src + i0, dst + i0, n, fg_rule); break;
+    }
+}
+
+// pinned staging buffer, one per host thread that calls the host entry points (grown on demand, kept for the thread's
+// life: cudaHostAlloc costs milliseconds, a call costs one)
+struct pinned_stage {
+    void *p = nullptr;
+    size_t n = 0;
+    ~pinned_stage() { if (p) cudaFreeHost(p); }
+    void *get(size_t bytes)
+    {
+        if (bytes > n) {
+            if (p) cudaFreeHost(p);
+            p = nullptr; n = 0;
+            if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); p = nullptr; return nullptr; }
+            n = bytes;
+        }
+        return p;
+    }
+};
+thread_local pinned_stage t_stage;
+
 struct host_plan {
-    size_t dev_ws, o_mask, o_vertex, o_idxs, o_sel, o_mean, o_out, o_tn, o_status, total;
+    size_t dev_ws, sub_ws, o_mask, o_vertex, o_idxs, o_sel, o_mean, o_out, o_tn, o_status, total;
     long long mask_span, vertex_span;
     bool vertex_zero_copy;
     void *vertex_dev;
@@ -53,6 +121,14 @@ int plan_host(const pvv_job *j, host_plan *P)
     P->vertex_dev = nullptr;
     P->vertex_zero_copy = is_pinned(j->vertex, &P->vertex_dev);
     size_t o = align_up(pvv_workspace_bytes(j), 256);
+    {   // the narrowing path votes on up to 4 sub-batches on two streams at once: each needs a workspace of its own
+        const int nsub = j->b >= 8 ? 4 : j->b >= 2 ? 2 : 1;
+        pvv_job sj = *j;
+        sj.b = (j->b + nsub - 1) / nsub;
+        sj.pool_capacity = 0;                       // sub-batches of a narrowed call use the default pool bound
+        P->sub_ws = align_up(pvv_workspace_bytes(&sj), 256);
+        if ((size_t)nsub * P->sub_ws > o) o = (size_t)nsub * P->sub_ws;
+    }
     P->dev_ws = o;
     auto take = [&](size_t bytes) { const size_t at = o; o = align_up(o + bytes, 256); return at; };
     P->o_mask = take((size_t)P->mask_span * mask_elem(j->mask_dtype));
@@ -69,11 +145,13 @@ int plan_host(const pvv_job *j, host_plan *P)
 
 // One sub-batch [i0, i1) of the job on the compute stream; device-side inputs already point at the full arrays.
 int run_sub(const pvv_job &dj, int i0, int i1, bool cov, float confidence, int max_iter, const float *mean_dev,
-            float *out_dev, int *tn_dev, int32_t *status_dev)
+            float *out_dev, int *tn_dev, int32_t *status_dev, cudaStream_t stream = nullptr, void *sub_ws = nullptr,
+            size_t sub_ws_bytes = 0)
 {
     pvv_job sj = dj;
     sj.b = i1 - i0;
     sj.status = status_dev;
+    if (sub_ws) { sj.stream = stream; sj.workspace = sub_ws; sj.workspace_bytes = sub_ws_bytes; }
     sj.mask = (const char *)dj.mask + (size_t)i0 * dj.mask_strides[0] * mask_elem(dj.mask_dtype);
     sj.vertex = dj.vertex + (long long)i0 * dj.vertex_strides[0];
     if (dj.idxs) sj.idxs = dj.idxs + (size_t)i0 * dj.hn_total * dj.vn * 2;
@@ -112,7 +190,19 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     const bool mask_pinned = is_pinned(j->mask, &pin_dummy);
     // the mask is copied per sub-batch only when images are laid out one after the other (stride[0] covers an image)
     const bool separable = j->mask_strides[0] >= (int64_t)(j->h - 1) * j->mask_strides[1] + (int64_t)(j->w - 1) * j->mask_strides[2] + 1;
-    const int nsub = (mask_pinned && P.vertex_zero_copy && separable && j->b >= 8) ? 4 : 1;
+    int nsub = (mask_pinned && P.vertex_zero_copy && separable && j->b >= 8) ? 4 : 1;
+    // wide, contiguous masks are narrowed to one byte per pixel by host threads (pinned or pageable alike)
+    const size_t npx = (size_t)j->h * j->w;
+    const bool contiguous = j->mask_strides[2] == 1 && j->mask_strides[1] == j->w && j->mask_strides[0] == (int64_t)npx;
+    uint8_t *stage = nullptr;
+    if (esz > 1 && contiguous && P.vertex_zero_copy && npx * j->b >= (size_t)1 << 18) stage = (uint8_t *)t_stage.get(npx * j->b);
+    const bool narrow = stage != nullptr;
+    if (narrow) {
+        nsub = j->b >= 8 ? 4 : j->b >= 2 ? 2 : 1;
+        dj.mask_dtype = PVV_MASK_U8;           // the staged bytes already are what the foreground rule looks at
+        dj.mask_strides[0] = (int64_t)npx; dj.mask_strides[1] = j->w; dj.mask_strides[2] = 1;
+        h2d += (int64_t)(npx * j->b) - (int64_t)mbytes;
+    }
 
     if (P.vertex_zero_copy) {
         dj.vertex = (const float *)P.vertex_dev;
@@ -146,7 +236,79 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     if ((e = cudaMemsetAsync(status_dev, 0, sizeof(int32_t) * 4, st))) return PVV_ERR_CUDA;
     const size_t out_bytes = sizeof(float) * (size_t)j->b * j->vn * (cov ? 4 : 2);
 
-    if (nsub == 1) {
+    if (narrow) {
+        // workers narrow 64 K-pixel pieces in order; the calling thread hands every finished sub-batch to the copy stream
+        // and enqueues its voting on the caller's stream, so host narrowing, PCIe and the SMs overlap
+        const size_t piece = (size_t)1 << 16;
+        size_t sub_lo[5];
+        for (int s = 0; s <= nsub; ++s) sub_lo[s] = (size_t)((long long)j->b * s / nsub) * npx;
+        size_t piece_base[5];
+        piece_base[0] = 0;
+        for (int s = 0; s < nsub; ++s) piece_base[s + 1] = piece_base[s] + (sub_lo[s + 1] - sub_lo[s] + piece - 1) / piece;
+        std::atomic<size_t> next(0);
+        std::atomic<size_t> done[4];
+        for (int s = 0; s < 4; ++s) done[s].store(0);
+        const int fg_rule = j->fg_rule, dtype = j->mask_dtype;
+        const void *src = j->mask;
+        auto work = [&] {
+            for (;;) {
+                const size_t c = next.fetch_add(1);
+                if (c >= piece_base[nsub]) return;
+                int s = 0;
+                while (c >= piece_base[s + 1]) ++s;
+                const size_t i0 = sub_lo[s] + (c - piece_base[s]) * piece;
+                const size_t n = i0 + piece <= sub_lo[s + 1] ? piece : sub_lo[s + 1] - i0;
+                narrow_dispatch(src, dtype, stage, i0, n, fg_rule);
+                done[s].fetch_add(1, std::memory_order_release);
+            }
+        };
+        unsigned hw = std::thread::hardware_concurrency();
+#ifndef PVV_HOST_THREADS_DIV
+#define PVV_HOST_THREADS_DIV 2   // measured on the 16-thread host of a B200 box: 8 workers beat 12 and 4 (profiles/r02_e2e_host_threads.log)
+#endif
+        int nthreads = (int)(hw / PVV_HOST_THREADS_DIV);
+        nthreads = nthreads < 1 ? 1 : nthreads > 16 ? 16 : nthreads;
+        if ((size_t)nthreads > piece_base[nsub]) nthreads = (int)piece_base[nsub];
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; ++t) pool.emplace_back(work);
+        // one copy stream and two voting streams: the compaction of sub-batch s + 1 gathers its foreground vectors over PCIe
+        // (bus-bound) while sub-batch s is being voted on (SM-bound); every sub-batch has its own workspace
+        cudaStream_t cs = nullptr, ks[2] = {nullptr, nullptr};
+        cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        bool ok = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&ks[0], cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&ks[1], cudaStreamNonBlocking) == cudaSuccess;
+        for (int i = 0; ok && i < 7; ++i) ok = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) == cudaSuccess;
+        // everything the caller's stream did before (input copies above, earlier use of the workspace) comes first
+        ok = ok && cudaEventRecord(ev[4], st) == cudaSuccess && cudaStreamWaitEvent(cs, ev[4], 0) == cudaSuccess &&
+             cudaStreamWaitEvent(ks[0], ev[4], 0) == cudaSuccess && cudaStreamWaitEvent(ks[1], ev[4], 0) == cudaSuccess;
+        r = PVV_OK;
+        for (int s = 0; s < nsub; ++s) {
+            const size_t want = piece_base[s + 1] - piece_base[s];
+            while (done[s].load(std::memory_order_acquire) < want) std::this_thread::yield();
+            if (!ok || r != PVV_OK) continue;   // keep draining the workers; nothing more is enqueued
+            const int i0 = (int)((long long)j->b * s / nsub), i1 = (int)((long long)j->b * (s + 1) / nsub);
+            cudaStream_t k = ks[s & 1];
+            ok = cudaMemcpyAsync(base + P.o_mask + sub_lo[s], stage + sub_lo[s], sub_lo[s + 1] - sub_lo[s], cudaMemcpyHostToDevice, cs) ==
+                     cudaSuccess &&
+                 cudaEventRecord(ev[s], cs) == cudaSuccess && cudaStreamWaitEvent(k, ev[s], 0) == cudaSuccess;
+            if (ok) {
+                pvv_job sub = dj;
+                sub.pool_capacity = 0;
+                r = run_sub(sub, i0, i1, cov, confidence, max_iter, mean_dev, out_dev, tn_dev, status_dev + s, k,
+                            base + (size_t)s * P.sub_ws, P.sub_ws);
+            }
+        }
+        for (auto &t : pool) t.join();
+        // the caller's stream continues after both voting streams
+        for (int i = 0; ok && i < 2; ++i)
+            ok = cudaEventRecord(ev[5 + i], ks[i]) == cudaSuccess && cudaStreamWaitEvent(st, ev[5 + i], 0) == cudaSuccess;
+        for (int i = 0; i < 7; ++i) if (ev[i]) cudaEventDestroy(ev[i]);
+        if (cs) cudaStreamDestroy(cs);
+        for (int i = 0; i < 2; ++i) if (ks[i]) cudaStreamDestroy(ks[i]);
+        if (r != PVV_OK) return r;
+        if (!ok) { cudaGetLastError(); return PVV_ERR_CUDA; }
+    } else if (nsub == 1) {
         if ((e = cudaMemcpyAsync(base + P.o_mask, j->mask, mbytes, cudaMemcpyHostToDevice, st))) return PVV_ERR_CUDA;
         r = run_sub(dj, 0, j->b, cov, confidence, max_iter, mean_dev, out_dev, tn_dev, status_dev);
         if (r != PVV_OK) return r;

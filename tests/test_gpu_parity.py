@@ -281,7 +281,23 @@ def test_host_buffers_match_device_path():
         assert not out.is_cuda and torch.equal(out, dev_out.cpu())
         h2d, d2h = out.transfer_bytes
         full = tv_h.numel() * 4
-        assert (h2d < mask.nbytes + 0.2 * full) if pin else (h2d >= mask.nbytes + full)
+        assert (h2d < mask.nbytes + 0.2 * full) if pin else (h2d >= mask.size + full)
+    # wide masks are narrowed to one byte per pixel by host threads (pinned vertex): every dtype and both foreground rules
+    lab = mask.copy()
+    lab[0][lab[0] == 1] = 2            # foreground for .byte(), background for == 1
+    lab[1][:100] = 256                 # wraps to background under .byte()
+    dev_lab = pv.ransac_voting_layer_v3(torch.from_numpy(lab).to(DEV), torch.from_numpy(vertex).to(DEV), 128, 0.99, seed=7)
+    cov_lab = pv.estimate_voting_distribution_with_mean(torch.from_numpy(lab).to(DEV), torch.from_numpy(vertex).to(DEV), dev_lab,
+                                                        64, 128, seed=7)[1]
+    tv_pin = synth.as_net_output(vertex, pin=True)
+    for dt in (torch.int64, torch.int32, torch.float32, torch.uint8):
+        hl = torch.from_numpy(lab).to(dt) if dt != torch.uint8 else torch.from_numpy((lab & 0xff).astype(np.uint8))
+        out = pv.ransac_voting_layer_v3(hl, tv_pin, 128, 0.99, seed=7)
+        assert torch.equal(out, dev_lab.cpu()), dt
+        if dt != torch.uint8:
+            assert out.transfer_bytes[0] < lab.size * 1 + 0.2 * tv_pin.numel() * 4, dt     # one byte per pixel crossed the bus
+            c = pv.estimate_voting_distribution_with_mean(hl, tv_pin, dev_lab.cpu(), 64, 128, seed=7)[1]
+            assert torch.equal(c, cov_lab.cpu()), dt
     cov_d = pv.estimate_voting_distribution_with_mean(tm_h.to(DEV), torch.from_numpy(vertex).to(DEV), dev_out, 64, 128, seed=7)[1]
     cov_h = pv.estimate_voting_distribution_with_mean(tm_h, torch.from_numpy(vertex), dev_out.cpu(), 64, 128, seed=7)[1]
     assert torch.equal(cov_h, cov_d.cpu())
