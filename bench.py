@@ -51,6 +51,9 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU work in the bounded cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="configs1", choices=["configs1", "configs3"],
+                    help="configs1: the headline line (default, what the driver runs); configs3: Occlusion-LINEMOD shape, "
+                         "16 images x 8 instance masks per GPU, v3 + covariance, packed [b,vn,6] gather (reported beside it)")
     return ap.parse_args()
 
 
@@ -244,6 +247,83 @@ def ref_cuda_leg(pv, tm, tv, tn_total):
     return res
 
 
+def run_configs3(args):
+    """BASELINE configs[3]: Occlusion-LINEMOD-shaped batch, 8 object instances per 480x640 image, 128 images over 8 GPUs =
+    16 images x 8 instance masks = 128 mask/vertex entries per rank (each instance has its own vertex field, as the network
+    emits one per object), v3(512, 0.99) + estimate_voting_distribution_with_mean (16 x 256 hypotheses) per entry, and ONE
+    packed [b,vn,6] all-gather of keypoints + covariances per step (pvnet_b200.distributed; the reference analogue is
+    UncertaintyEvalWrapper under DataParallel, tools/train_linemod.py:135-143,222-223).  Weak scaling: fixed work per rank."""
+    import torch
+    import torch.distributed as dist
+    from pvnet_b200 import distributed as pd
+    from pvnet_b200 import synth
+
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    imgs, inst = 16, 8
+    b = imgs * inst
+    uniq = 32
+    masks = np.zeros((uniq, H, W), np.int64)
+    verts = np.zeros((uniq, H, W, VN, 2), np.float32)
+    for e in range(uniq):
+        r = np.random.default_rng(7000 + 1000 * rank + e)
+        masks[e] = synth.blob_mask(r, float(r.uniform(0.002, 0.008)))
+        verts[e] = synth.unit_field(masks[e], synth.keypoints_in_bbox(r, masks[e], VN), SIGMA, r)
+    reps = b // uniq
+    tm = torch.from_numpy(masks).to(dev).repeat(reps, 1, 1)
+    full = synth.as_net_output(verts, device=dev)._base.repeat(reps, 1, 1, 1)         # [b, 2 + 2vn, h, w], network layout
+    tv = full[:, 2:].permute(0, 2, 3, 1).view(b, H, W, VN, 2)
+    tn_total = int((masks != 0).sum()) * reps
+    gather = pd.AsyncGather(world * b, (VN, 6), dev)
+
+    def step(i):
+        return pd.ransac_voting_layer_v3_sharded(tm, tv, HN, world * b, seed=i, inlier_thresh=0.99, with_cov=True, gather=gather)
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    gather.drain()
+    torch.cuda.synchronize()
+    windows = []
+    for wdw in range(N_WINDOWS):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+        e0.record()
+        for i in range(args.steps):
+            step(i)
+        gather.drain()
+        e1.record()
+        torch.cuda.synchronize()
+        wms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([wms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            wms = float(t.item())
+        windows.append(wms)
+    ms = float(np.median(windows))
+    res = gather.wait((gather.n - 1) % 2)
+    finite = bool(torch.isfinite(res).all())
+    if rank == 0:
+        tests = float(tn_total) * VN * (HN + 4096)
+        _emit({"metric": "voting images/sec (Occlusion-LINEMOD shape: 8 instance masks per 480x640 image, 9 kp, v3 512 hyp + covariance 4096 hyp)",
+               "value": world * imgs * args.steps / (ms * 1e-3), "unit": "images/s", "n_gpus": world, "steps": args.steps,
+               "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": "configs[3]: 16 images x 8 instance masks per GPU (128 entries of 480x640), 9 kp, v3(512, 0.99) + "
+                                      "distribution(16 x 256, 0.99), packed [b,vn,6] all-gather", "images_per_gpu": imgs,
+                          "instances_per_image": inst, "global_images": world * imgs, "fg_pixels_per_rank": tn_total,
+                          "parallelism": f"dp{world} by image, asynchronous packed gather"},
+               "instances_per_s": world * b * args.steps / (ms * 1e-3), "hyp_pixel_tests_per_s": world * tests * args.steps / (ms * 1e-3),
+               "timed_windows_ms": windows, "result_finite": finite, "gathered_shape": list(res.shape)})
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -270,14 +350,17 @@ def run_ours(args):
         sets.append((m, v))
     tn_total = int((mask != 0).sum())
     tests_per_step = float(tn_total) * VN * HN
-    gathered = torch.empty((world * b, VN, 2), dtype=torch.float32, device=dev) if world > 1 else None
+    # N > 1: the product's own sharded entry point (pvnet_b200.distributed): every rank votes on its 32 images (draws keyed
+    # by the global image id) and the packed results are gathered on every rank by an asynchronous all-gather into two
+    # rotating buffers, so the gather of step i overlaps the compaction of step i + 1 (it used to sit on the voting stream)
+    from pvnet_b200 import distributed as pd
+    gather = pd.AsyncGather(world * b, (VN, 2), dev) if world > 1 else None
 
     def step(i):
         m, v = sets[i % N_SETS]
-        out = pv.ransac_voting_layer_v3(m, v, HN, THRESH, seed=i, image_id_base=rank * b)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, out)
-        return out
+            return pd.ransac_voting_layer_v3_sharded(m, v, HN, world * b, seed=i, inlier_thresh=THRESH, gather=gather)
+        return pv.ransac_voting_layer_v3(m, v, HN, THRESH, seed=i, image_id_base=rank * b)
 
     sampler = ClockSampler(local)
     for i in range(max(args.warmup, 3)):
@@ -300,6 +383,8 @@ def run_ours(args):
         e0.record()
         for i in range(args.steps):
             step(wdw * args.steps + i)
+        if gather is not None:
+            gather.drain()     # the last gathers complete inside the timed window (the stream waits, the host does not)
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -396,7 +481,7 @@ def run_ours(args):
         for i in range(n_e2e):
             o = pv.ransac_voting_layer_v3(hm, hv, HN, THRESH, seed=i, image_id_base=rank * b)
             if world > 1:
-                dist.all_gather_into_tensor(gathered, o.to(dev))
+                gather.wait(gather.submit(o.to(dev)))
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if world > 1:
@@ -451,5 +536,7 @@ if __name__ == "__main__":
     _quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "configs3":
+        run_configs3(a)
     else:
         run_ours(a)

@@ -69,7 +69,21 @@ def _worker(rank, world, port, global_b, q):
         with pytest.raises(ValueError):
             pd.ransac_voting_layer_v3_sharded(torch.from_numpy(mask[:1]), torch.from_numpy(vertex[:1]), HN, global_b + 4,
                                               vote_fn=_vote_fn([]))
-        q.put((rank, kp.numpy(), cov.numpy(), kp_only.numpy(), calls, (lo, hi)))
+        # the asynchronous gather (bench.py's N > 1 path): three steps through two rotating receive buffers
+        async_ok = None
+        if global_b % world == 0:
+            g = pd.AsyncGather(global_b, (VN, 6), torch.device("cpu"))
+            slots = [pd.ransac_voting_layer_v3_sharded(torch.from_numpy(mask[lo:hi]), torch.from_numpy(vertex[lo:hi]), HN,
+                                                       global_b, seed=3, with_cov=True, vote_fn=_vote_fn([]),
+                                                       cov_fn=_cov_fn([]), gather=g) for _ in range(3)]
+            assert slots == [0, 1, 0]
+            g.drain()
+            full = g.wait(slots[-1])
+            async_ok = bool(torch.equal(full[:, :, :2], kp) and torch.equal(full[:, :, 2:].reshape(global_b, VN, 2, 2), cov)
+                            and torch.equal(g.wait(1), full))
+            with pytest.raises(ValueError):
+                pd.AsyncGather(global_b + 1, (VN, 2), torch.device("cpu"))
+        q.put((rank, kp.numpy(), cov.numpy(), kp_only.numpy(), calls, (lo, hi), async_ok))
     finally:
         dist.destroy_process_group()
 
@@ -93,7 +107,8 @@ def test_two_ranks_equal_single_process(global_b):
     kp1 = _vote_fn(calls)(torch.from_numpy(mask), torch.from_numpy(vertex), HN, seed=3, image_id_base=0)
     _, cov1 = _cov_fn(calls)(torch.from_numpy(mask), torch.from_numpy(vertex), kp1, seed=4, image_id_base=0)
     covered = []
-    for rank, kp, cov, kp_only, rcalls, (lo, hi) in res:
+    for rank, kp, cov, kp_only, rcalls, (lo, hi), async_ok in res:
+        assert async_ok is (True if global_b % world == 0 else None)
         assert kp.shape == (global_b, VN, 2) and cov.shape == (global_b, VN, 2, 2)
         assert np.array_equal(kp, kp1.numpy())            # every rank holds the full, rank-count-invariant result
         assert np.array_equal(cov, cov1.numpy())
