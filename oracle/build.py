@@ -89,9 +89,41 @@ def build_ref(force: bool = False) -> str | None:
     return REF_SO
 
 
+REF_PNP_SRC = "/root/reference/lib/utils/extend_utils/src/uncertainty_pnp.cpp"
+REF_PNP_INC = "/root/reference/lib/utils/extend_utils/include"
+REF_PNP_SO = os.path.join(REF_OUT, "ref_pnp_functor.so")
+
+
+def build_ref_pnp(force: bool = False) -> str | None:
+    """The reference's uncertainty-PnP COST functor (uncertainty_pnp.cpp:7-33) compiled against the vendored header-only
+    ceres/jet.h + ceres/rotation.h + Eigen, behind oracle/ref_pnp_driver.cpp.  The struct is cut out of the reference
+    source at build time into oracle/_ref/pnp_functor.inc (never committed): everything from `struct
+    ReprojectionErrorArray {` up to the factory comment, plus the member declarations -- the AutoDiffCostFunction factory is
+    left out because <ceres/ceres.h> needs glog headers, which this image does not have.  Returns None when
+    /root/reference is absent (GPU box: the prebuilt file is used)."""
+    if not os.path.isfile(REF_PNP_SRC):
+        return REF_PNP_SO if os.path.exists(REF_PNP_SO) else None
+    drv = os.path.join(HERE, "ref_pnp_driver.cpp")
+    if not force and _newer(REF_PNP_SO, [REF_PNP_SRC, drv]):
+        return REF_PNP_SO
+    os.makedirs(REF_OUT, exist_ok=True)
+    lines = open(REF_PNP_SRC).read().split("\n")
+    a = next(i for i, l in enumerate(lines) if l.startswith("struct ReprojectionErrorArray"))
+    b = next(i for i, l in enumerate(lines) if "// Factory to hide" in l)
+    c = next(i for i, l in enumerate(lines) if i > b and l.strip().startswith("double x2d,y2d;"))
+    d = next(i for i, l in enumerate(lines) if i > c and l.strip() == "};")
+    with open(os.path.join(REF_OUT, "pnp_functor.inc"), "w") as f:
+        f.write("// generated by oracle/build.py from %s lines %d-%d and %d-%d; not committed\n" % (REF_PNP_SRC, a + 1, b, c + 1, d + 1))
+        f.write("\n".join(lines[a:b] + lines[c:d + 1]) + "\n")
+    _run(["g++", "-O2", "-w", "-std=c++14", "-fPIC", "-shared", "-I", REF_PNP_INC, "-I", os.path.join(REF_PNP_INC, "eigen3"),
+          "-I", REF_OUT, drv, "-o", REF_PNP_SO])
+    return REF_PNP_SO
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     if what in ("oracle", "all"):
         print(build_oracle(force=True))
     if what in ("ref", "all"):
         print(build_ref(force=True))
+        print(build_ref_pnp(force=True))

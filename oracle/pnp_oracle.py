@@ -86,3 +86,31 @@ def uncertainty_pnp(points_2d, weights_2d, points_3d, camera_matrix, return_info
 def evaluate_uncertainty_pose(mean_pts2d, covar, points_3d, K):
     """The pose part of Evaluator.evaluate_uncertainty (evaluation_utils.py:164-183)."""
     return uncertainty_pnp(mean_pts2d, weights_from_covariance(covar), points_3d, K)
+
+
+# ---- the reference's own cost functor (oracle/_ref/ref_pnp_functor.so, built by oracle/build.py:build_ref_pnp) ----------
+_REF_PNP = None
+
+
+def ref_cost_available() -> bool:
+    import os
+    return os.path.exists(os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "ref_pnp_functor.so"))
+
+
+def ref_cost(rt, pts2d, pts3d, w, K):
+    """Residuals [2*pn] and Jacobian [2*pn, 6] of the REFERENCE's ReprojectionErrorArray (uncertainty_pnp.cpp:7-33) at the
+    pose rt = (angle-axis, translation), differentiated by the reference's own ceres::Jet."""
+    import ctypes
+    import os
+    global _REF_PNP
+    if _REF_PNP is None:
+        _REF_PNP = ctypes.CDLL(os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "ref_pnp_functor.so"))
+        dp = ctypes.POINTER(ctypes.c_double)
+        _REF_PNP.ref_pnp_cost.argtypes = [dp, dp, dp, dp, dp, ctypes.c_int, dp, dp]
+    c = lambda a: np.ascontiguousarray(a, np.float64)
+    pts2d, pts3d, w, K, rt = c(pts2d), c(pts3d), c(w), c(K), c(rt)
+    pn = pts2d.shape[0]
+    res, jac = np.zeros(2 * pn), np.zeros((2 * pn, 6))
+    p = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+    _REF_PNP.ref_pnp_cost(p(pts2d), p(pts3d), p(w), p(K), p(rt), pn, p(res), p(jac))
+    return res, jac

@@ -638,6 +638,35 @@ def test_uncertainty_pnp_vs_oracle():
     np.testing.assert_allclose(got, po.uncertainty_pnp(x[9].astype(np.float64), w, Xs[9], K), atol=1e-6)
 
 
+def test_uncertainty_pnp_is_stationary_for_the_reference_cost():
+    """N2: the pose the GPU solver returns minimises the REFERENCE's own cost -- the gradient J^T r of
+    ReprojectionErrorArray (uncertainty_pnp.cpp:7-33, compiled from the reference source with its own ceres::Jet, oracle/_ref)
+    vanishes there, and no pose the restatement finds has a lower reference cost (1e-9 relative)."""
+    import cv2
+    from oracle import pnp_oracle as po
+    from pvnet_b200 import uncertainty_pnp as up
+    if not po.ref_cost_available():
+        pytest.skip("oracle/_ref/ref_pnp_functor.so not built")
+    rng = np.random.default_rng(77)
+    b, pn = 12, 9
+    cases = [synth.pnp_case(rng, pn, noise=1.5) for _ in range(b)]
+    K = cases[0][0]
+    Xs = np.stack([c[1] for c in cases])
+    x = np.stack([c[3] for c in cases])
+    cov = np.stack([c[4] for c in cases]).astype(np.float64)
+    poses = up.uncertainty_pnp_batch(torch.from_numpy(x).to(DEV), torch.from_numpy(cov).to(DEV), Xs, K).cpu().numpy()
+    for i in range(b):
+        w = po.weights_from_covariance(cov[i])
+        rt = np.concatenate([cv2.Rodrigues(poses[i][:, :3])[0].reshape(3), poses[i][:, 3]])
+        r, j = po.ref_cost(rt, x[i], Xs[i], w, K)
+        g = j.T @ r
+        assert np.abs(g).max() <= 1e-6 * max(1.0, np.abs(j).max() * np.abs(r).max()), (i, g)
+        want = po.uncertainty_pnp(x[i], w, Xs[i], K)
+        rt_w = np.concatenate([cv2.Rodrigues(want[:, :3])[0].reshape(3), want[:, 3]])
+        rw, _ = po.ref_cost(rt_w, x[i], Xs[i], w, K)
+        assert float(r @ r) <= float(rw @ rw) * (1 + 1e-9) + 1e-12
+
+
 def test_voting_to_pose_pipeline():
     """mask + vertex field -> v3 keypoints -> covariances -> uncertainty PnP, all on the device: the recovered pose
     reprojects the object's keypoints onto the voted ones."""
