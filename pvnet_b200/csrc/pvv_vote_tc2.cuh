@@ -504,77 +504,65 @@ __global__ void __launch_bounds__(t2_cfg<NB>::threads, 1) k_count_tc2(pvv_dims d
 
 // ---- K3c: the deferred passes of the tensor-pipe kernel, as a kernel of their own ---------------------------------
 // One queue entry = one flagged (hypothesis, 16-pixel group): the tensor-pipe value of at least one of its tests was
-// inside the tensor-pipe band, so k_count_tc2 counted NONE of its 16 tests.  Two lanes per entry (8 pixels each):
+// inside the tensor-pipe band, so k_count_tc2 counted NONE of its 16 tests.  SIXTEEN lanes per entry, one pixel each, so a
+// warp's loads are two contiguous 256-byte runs (the first version gave every lane 8 pixels: 32 different cache lines per
+// load instruction, and the kernel was bound by the load unit at 170 us):
 //   phase A  the FP32 filter in the chunk's own frame (origin = the chunk's middle pixel, the frame of the FP32-pipe
 //            kernel): a = fma(hx, nx, fma(hy, ny, ra)), tau c = fma(hx, tau ny, fma(hy, -tau nx, rc)), m = a - |tau c| on
 //            the pre-pass constants, r formed in fp32 (one rounded product, one fma).  |m| > T decides (bound: DESIGN.md 4a,
-//            T = krel * (|hx| + |hy| + extent of the lane's pixels) + floor, the FP32-pipe kernel's band);
+//            T = krel * (|hx| + |hy| + extent of the group's pixels) + floor, the FP32-pipe kernel's band);
 //   phase B  the tests inside that band get the reference's exact rounding sequence (pvv_exact_test), densely packed.
-// Grid: blockIdx.x = slice + tcq_slices * part; `parts` CTAs stride over the entries of one slice.  Everything a lane
-// needs is in the entry, so its loads (hypothesis, 8 x constants, 8 x coordinates) are issued together.
+// Grid: blockIdx.x = slice + tcq_slices * part; `parts` CTAs stride over the entries of one slice.
 constexpr int T2_DEF_THREADS = 256;
 __global__ void __launch_bounds__(T2_DEF_THREADS) k_count_tc_deferred(pvv_dims d, pvv_ws ws, band_consts bc, int parts)
 {
-    constexpr int EPB = T2_DEF_THREADS / 2;               // entries per CTA and step
-    __shared__ uint32_t s_q2[EPB * K3_GROUP];              // phase B: (local entry << 8) | pixel within the group
+    constexpr int EPB = T2_DEF_THREADS / K3_GROUP;         // entries per CTA and step
+    __shared__ uint32_t s_q2[T2_DEF_THREADS];              // phase B: (local entry << 8) | pixel within the group
     __shared__ int s_q2n;
     pvv_pdl_enter();
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, px = tid & (K3_GROUP - 1), le = tid / K3_GROUP;
     const int slice = blockIdx.x % ws.tcq_slices, part = blockIdx.x / ws.tcq_slices;
     const int total = min(ws.tcq_cnt[slice], ws.tcq_slice_cap);
     const uint4 *q = ws.tcq + (size_t)slice * ws.tcq_slice_cap;
+    const uint32_t half_mask = 0xffffu << (16 * ((tid >> 4) & 1));   // the 16 lanes of this entry within the warp
     unsigned long long amb_local = 0;
     for (int base = part * EPB; base < total; base += parts * EPB) {
         if (tid == 0) s_q2n = 0;
         __syncthreads();
-        const int le = tid >> 1, ei = base + le;
-        if (ei < total) {
+        const int ei = base + le;
+        if (ei < total) {   // uniform over the 16 lanes of an entry
             const uint4 en = q[ei];
             const int nvalid = (int)(en.z & 0xffu), vi = (int)(en.z >> 8);
-            const int j0 = (tid & 1) * (K3_GROUP / 2);
-            const float4 *pq = ws.pix_pq + (long long)vi * ws.cap + en.x;
-            const uint32_t *pxy = ws.pix_xy + en.x;
-            float4 c[K3_GROUP / 2];
-            uint32_t xy[K3_GROUP / 2];
-#pragma unroll
-            for (int u = 0; u < K3_GROUP / 2; ++u) {   // all loads first
-                const bool ok = j0 + u < nvalid;
-                c[u] = ok ? pq[j0 + u] : make_float4(0.f, 0.f, 0.f, 0.f);
-                xy[u] = ok ? pxy[j0 + u] : 0u;
-            }
+            const bool ok = px < nvalid;
+            const float4 c = ok ? ws.pix_pq[(long long)vi * ws.cap + en.x + px] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const uint32_t xy = ok ? ws.pix_xy[en.x + px] : 0u;
             const float2 hv = ws.hyp[en.y];
             const int ox = (int)(en.w & 0xffffu), oy = (int)(en.w >> 16);
             float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy);
             const float mm = __fadd_rn(fabsf(hx), fabsf(hy));
             const bool far = !(mm < 1e15f);
             if (far) { hx = 0.f; hy = 0.f; }
-            float m[K3_GROUP / 2];
+            float m = -1e30f;   // padded pixel / pixel the reference never counts: not an inlier, not in the band
             int ext = 0;
-#pragma unroll
-            for (int u = 0; u < K3_GROUP / 2; ++u) {
-                m[u] = -1e30f;   // padded pixel / pixel the reference never counts: not an inlier, not in the band
-                if (c[u].x != 0.f || c[u].y != 0.f) {
-                    const int ix = (int)(xy[u] & 0xffffu) - ox, iy = (int)(xy[u] >> 16) - oy;
-                    const float fx = (float)ix, fy = (float)iy;
-                    const float ra = -__fmaf_rn(fx, c[u].x, __fmul_rn(fy, c[u].y));
-                    const float rc = -__fmaf_rn(fx, c[u].z, __fmul_rn(fy, c[u].w));
-                    const float a = __fmaf_rn(hx, c[u].x, __fmaf_rn(hy, c[u].y, ra));
-                    const float tc = __fmaf_rn(hx, c[u].z, __fmaf_rn(hy, c[u].w, rc));
-                    m[u] = __fsub_rn(a, fabsf(tc));
-                    ext = max(ext, abs(ix) + abs(iy));
-                }
+            if (c.x != 0.f || c.y != 0.f) {
+                const int ix = (int)(xy & 0xffffu) - ox, iy = (int)(xy >> 16) - oy;
+                const float fx = (float)ix, fy = (float)iy;
+                const float ra = -__fmaf_rn(fx, c.x, __fmul_rn(fy, c.y));
+                const float rc = -__fmaf_rn(fx, c.z, __fmul_rn(fy, c.w));
+                const float a = __fmaf_rn(hx, c.x, __fmaf_rn(hy, c.y, ra));
+                const float tc = __fmaf_rn(hx, c.z, __fmaf_rn(hy, c.w, rc));
+                m = __fsub_rn(a, fabsf(tc));
+                ext = abs(ix) + abs(iy);
             }
+            // the group's extent: maximum over its 16 lanes
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) ext = max(ext, __shfl_xor_sync(half_mask, ext, o, 16));
             const float T = far ? __int_as_float(0x7f800000) : __fmaf_rn(bc.krel, __fadd_rn(mm, (float)ext), bc.abs_floor);
-            int sure = 0;
-#pragma unroll
-            for (int u = 0; u < K3_GROUP / 2; ++u) {
-                if (fabsf(m[u]) > T) {
-                    sure += m[u] > 0.f;
-                } else if (j0 + u < nvalid) {   // (padded pixels only get here when the band is infinite)
-                    s_q2[atomicAdd(&s_q2n, 1)] = ((uint32_t)le << 8) | (uint32_t)(j0 + u);
-                }
-            }
-            if (sure) atomicAdd(&ws.counts[en.y], sure);
+            const bool decided = fabsf(m) > T;
+            const uint32_t sure = __ballot_sync(half_mask, decided && m > 0.f) & half_mask;
+            if (px == 0 && sure) atomicAdd(&ws.counts[en.y], __popc(sure));
+            if (!decided && ok)     // (padded pixels only get here when the band is infinite)
+                s_q2[atomicAdd(&s_q2n, 1)] = ((uint32_t)le << 8) | (uint32_t)px;
         }
         __syncthreads();
         const int q2 = s_q2n;
