@@ -41,7 +41,7 @@ class Debug(C.Structure):
 
 # every symbol include/pvvote.h declares (tests check the library exports exactly these)
 SYMBOLS = [
-    "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_v3_noalloc", "pvv_static_workspace_bytes", "pvv_v5", "pvv_hypotheses", "pvv_motion", "pvv_cov", "pvv_workspace_bytes_host",
+    "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_v3_noalloc", "pvv_static_workspace_bytes", "pvv_v5", "pvv_hypotheses", "pvv_motion", "pvv_cov", "pvv_workspace_bytes_host", "pvv_set_host_workers",
     "pvv_v3_host", "pvv_cov_host", "pvv_generate_hypothesis", "pvv_voting_for_hypothesis", "pvv_vote_counts",
     "pvv_generate_hypothesis_vanishing_point", "pvv_voting_for_hypothesis_vanishing_point",
     "pvv_uncertainty_pnp", "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_probe_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
@@ -90,6 +90,13 @@ def lib():
     L.pvv_probe_tflops.argtypes = [I, I, V]
     L.pvv_probe_tflops.restype = C.c_double
     L.pvv_version.restype = C.c_char_p
+    L.pvv_set_host_workers.argtypes = [I]
+    # several ranks on one host (torchrun sets LOCAL_WORLD_SIZE): divide the host cores between them; with fewer than 6
+    # workers per rank narrowing the mask on the host is slower than copying it wide (profiles/r02_e2e_host_threads.log)
+    ranks = int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1)
+    if ranks > 1:
+        per_rank = ((os.cpu_count() or 2) // 2) // ranks
+        L.pvv_set_host_workers(per_rank if per_rank >= 6 else 0)
     _lib = L
     return L
 

@@ -102,6 +102,8 @@ struct pinned_stage {
 };
 thread_local pinned_stage t_stage;
 
+std::atomic<int> g_host_workers(-1);   // pvv_set_host_workers: < 0 auto, 0 narrowing off, > 0 that many
+
 struct host_plan {
     size_t dev_ws, sub_ws, o_mask, o_vertex, o_idxs, o_sel, o_mean, o_out, o_tn, o_status, total;
     long long mask_span, vertex_span;
@@ -195,7 +197,9 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     const size_t npx = (size_t)j->h * j->w;
     const bool contiguous = j->mask_strides[2] == 1 && j->mask_strides[1] == j->w && j->mask_strides[0] == (int64_t)npx;
     uint8_t *stage = nullptr;
-    if (esz > 1 && contiguous && P.vertex_zero_copy && npx * j->b >= (size_t)1 << 18) stage = (uint8_t *)t_stage.get(npx * j->b);
+    const int workers_cfg = g_host_workers.load(std::memory_order_relaxed);
+    if (workers_cfg != 0 && esz > 1 && contiguous && P.vertex_zero_copy && npx * j->b >= (size_t)1 << 18)
+        stage = (uint8_t *)t_stage.get(npx * j->b);
     const bool narrow = stage != nullptr;
     if (narrow) {
         nsub = j->b >= 8 ? 4 : j->b >= 2 ? 2 : 1;
@@ -266,7 +270,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
 #ifndef PVV_HOST_THREADS_DIV
 #define PVV_HOST_THREADS_DIV 2   // measured on the 16-thread host of a B200 box: 8 workers beat 12 and 4 (profiles/r02_e2e_host_threads.log)
 #endif
-        int nthreads = (int)(hw / PVV_HOST_THREADS_DIV);
+        int nthreads = workers_cfg > 0 ? workers_cfg : (int)(hw / PVV_HOST_THREADS_DIV);
         nthreads = nthreads < 1 ? 1 : nthreads > 16 ? 16 : nthreads;
         if ((size_t)nthreads > piece_base[nsub]) nthreads = (int)piece_base[nsub];
         std::vector<std::thread> pool;
@@ -432,6 +436,8 @@ __global__ void __launch_bounds__(256) k_ffma2_probe(float *out, int iters, floa
 }  // namespace
 
 extern "C" {
+
+int pvv_set_host_workers(int n) { return g_host_workers.exchange(n < -1 ? -1 : n); }
 
 size_t pvv_workspace_bytes_host(const pvv_job *job)
 {

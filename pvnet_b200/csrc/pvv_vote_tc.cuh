@@ -28,7 +28,7 @@
 //   * 1 MMA warp: one elected thread issues the tcgen05.mma of tile i+2 as soon as the voters have pulled tile i into
 //     registers (mbarriers full / empty; tcgen05.commit); operands are canonical K-major, non-swizzled core matrices
 //     (8 rows x 16 B; LBO = byte stride between the two K halves, SBO = between 8-row groups: verified by tc_probe.cu);
-//   * 7 producer warps (48 registers): stage the raw inputs of unit k+1 with cp.async, build the B rows of unit k
+//   * 7 producer warps (48 registers): stage the raw inputs of unit k+1 with 1-D bulk copies (TMA), build the B rows of unit k
 //     (pixel constants from the pre-pass that rides in K2's launch, translated into the row's frame and split), build the A rows
 //     once per row, and run the deferred passes (phase A / B) of unit k-2 -- the voters never leave their loop.
 // Units are dealt as contiguous ranges in (keypoint, pass, chunk) order, so a CTA changes row ~3 times per launch.
@@ -108,6 +108,7 @@ struct tc_smem {
     tc_raw raw[TC_RAWS];
     uint32_t q2[K3_QCAP];             // phase B entries: (pixel << 16) | hypothesis within the pass
     unsigned long long bar_ab[TC_STAGES], bar_done[TC_STAGES], bar_full[2], bar_empty[2];
+    unsigned long long bar_in[TC_RAWS];   // raw inputs of unit k have landed in raw[k % TC_RAWS] (bulk copies: complete_tx)
     long long off[8];                 // ring: pool offset of the image of unit k (slot k & 7), fetched two iterations ahead
     int4 ent[8];                      // ring: chunk-table entry of unit k, fetched three iterations ahead (x = -1: no unit)
     uint32_t tmem;
@@ -164,6 +165,16 @@ __device__ __forceinline__ void tc_bar_wait(unsigned long long *b, uint32_t pari
 __device__ __forceinline__ void tc_bar_arrive(uint32_t bar_saddr)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_saddr) : "memory");
+}
+// 1-D bulk copy global -> shared (TMA), completion counted in bytes on an mbarrier of this CTA
+__device__ __forceinline__ void tc_bulk_g2s(void *smem, const void *gmem, uint32_t bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(tc_saddr(smem)), "l"(gmem), "r"(bytes), "r"(tc_saddr(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_expect_tx(unsigned long long *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc_saddr(bar)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -276,6 +287,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
 
     if (tid == 0) {
         for (int i = 0; i < TC_STAGES; ++i) { tc_bar_init(&S.bar_ab[i], TC_PROD_WARPS); tc_bar_init(&S.bar_done[i], TC_VOTER_WARPS); }
+        for (int i = 0; i < TC_RAWS; ++i) tc_bar_init(&S.bar_in[i], 1);
         tc_bar_init(&S.bar_full[0], 1); tc_bar_init(&S.bar_full[1], 1);
         tc_bar_init(&S.bar_empty[0], TC_VOTER_WARPS); tc_bar_init(&S.bar_empty[1], TC_VOTER_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -564,24 +576,30 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 const int img = S.ent[kk & 7u].x;
                 if (img >= 0) cp_async8(&S.off[kk & 7u], ws.img_off + img);
             };
+            // Raw inputs of a unit = three contiguous runs of the pooled SoA buffers (constants, directions, coordinates; a
+            // fourth for the hypotheses when the unit opens a row): ONE thread issues them as 1-D bulk copies (TMA:
+            // cp.async.bulk, completion counted in bytes on bar_in) instead of 768 cp.async spread over the producers.
+            // Sources are 16-byte aligned because every image starts on a 16-pixel boundary of the pool (PVV_POOL_ALIGN); sizes
+            // are rounded up to 16 bytes (the pool and a hypothesis row have that slack).
             auto stage_inputs = [&](uint32_t rg1, uint32_t k1, const int4 &e, long long off, bool new_row, int rowbuf) {
-                if (e.x >= 0 && !K3_ABL(1024)) {
+                (void)off;
+                if (e.x >= 0 && !K3_ABL(1024) && ptid == 0) {
                     const int vi = (int)rg1 / npass, hbase = ((int)rg1 % npass) * TC_PASS_H;
-                    const long long pix = e.y;   // a pool index (off is no longer needed)
-                    (void)off;
+                    const long long pix = e.y;   // a pool index
+                    const int n = e.z & 0x7fff;
                     tc_raw &W = S.raw[k1 % TC_RAWS];
-                    for (int j = ptid; j < (e.z & 0x7fff); j += TC_PRODS) {
-                        cp_async16(&W.pq[j], ws.pix_pq + (long long)vi * ws.cap + pix + j);
-                        cp_async8(&W.dir[j], ws.pix_dir + (long long)vi * ws.cap + pix + j);
-                        cp_async4(&W.xy[j], ws.pix_xy + pix + j);
-                    }
-                    if (new_row) {
-                        const long long hrow = ((long long)e.x * d.vn + vi) * ws.hn_pad + hbase;
-                        const int hcount = min(TC_PASS_H, d.hn - hbase);
-                        for (int hl = ptid; hl < hcount; hl += TC_PRODS) cp_async8(&S.rows[rowbuf].raw[hl], ws.hyp + hrow + hl);
-                    }
+                    unsigned long long *bar = &S.bar_in[k1 % TC_RAWS];
+                    const uint32_t b_pq = (uint32_t)n * 16u, b_dir = (uint32_t)((n + 1) & ~1) * 8u, b_xy = (uint32_t)((n + 3) & ~3) * 4u;
+                    const int hcount = min(TC_PASS_H, d.hn - hbase);
+                    const uint32_t b_h = new_row ? (uint32_t)((hcount + 1) & ~1) * 8u : 0u;
+                    tc_expect_tx(bar, b_pq + b_dir + b_xy + b_h);
+                    tc_bulk_g2s(W.pq, ws.pix_pq + (long long)vi * ws.cap + pix, b_pq, bar);
+                    tc_bulk_g2s(W.dir, ws.pix_dir + (long long)vi * ws.cap + pix, b_dir, bar);
+                    tc_bulk_g2s(W.xy, ws.pix_xy + pix, b_xy, bar);
+                    if (new_row)
+                        tc_bulk_g2s(S.rows[rowbuf].raw, ws.hyp + ((long long)e.x * d.vn + vi) * ws.hn_pad + hbase, b_h, bar);
                 }
-                cp_async_commit();
+                cp_async_commit();   // (the look-ahead ring of thread 0 still uses cp.async)
             };
             if (ptid == 0) {
                 for (uint32_t i = 0; i < 3; ++i) fetch_entry(i, i);
@@ -601,7 +619,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 const uint32_t s = k % TC_STAGES;
                 tc_stage &T = S.st[s];  // free: the deferred passes of unit k - 3 ended in the previous iteration
                 cp_async_wait_all();
-                pbar();  // unit k's inputs are staged; everything of the previous iteration is complete
+                pbar();  // the look-ahead ring is up to date; everything of the previous iteration is complete
                 e0 = S.ent[k & 7u];
                 const int4 e1 = S.ent[(k + 1) & 7u];
                 if (e0.x < 0) {
@@ -610,6 +628,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
                     break;
                 }
+                if (!K3_ABL(1024)) tc_bar_wait<TC_SLEEP_VOTER>(&S.bar_in[k % TC_RAWS], (k / TC_RAWS) & 1u);   // unit k's raw inputs landed
                 if (ptid == 0) { fetch_entry(3, k + 3); fetch_off(k + 2); }   // committed with the staging group below
                 const long long off1 = S.off[(k + 1) & 7u];
                 uint32_t ci1, rg1;

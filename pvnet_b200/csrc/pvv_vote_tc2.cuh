@@ -127,16 +127,9 @@ __device__ __forceinline__ void t2_wait(uint32_t bar_saddr, uint32_t parity, int
 }
 __device__ __forceinline__ void t2_wait(unsigned long long *b, uint32_t parity, int id = 0) { t2_wait(tc_saddr(b), parity, id); }
 
-// 1-D bulk copy global -> shared (TMA), completion counted in bytes on an mbarrier of this CTA
-__device__ __forceinline__ void t2_bulk_g2s(void *smem, const void *gmem, uint32_t bytes, unsigned long long *bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(tc_saddr(smem)), "l"(gmem), "r"(bytes), "r"(tc_saddr(bar)) : "memory");
-}
-__device__ __forceinline__ void t2_expect_tx(unsigned long long *bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc_saddr(bar)), "r"(bytes) : "memory");
-}
+// (the bulk-copy helpers are pvv_vote_tc.cuh's)
+__device__ __forceinline__ void t2_bulk_g2s(void *smem, const void *gmem, uint32_t bytes, unsigned long long *bar) { tc_bulk_g2s(smem, gmem, bytes, bar); }
+__device__ __forceinline__ void t2_expect_tx(unsigned long long *bar, uint32_t bytes) { tc_expect_tx(bar, bytes); }
 __device__ __forceinline__ void t2_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Entry of the deferred queue, self-contained so that the kernel that resolves it has no dependent table look-ups:
