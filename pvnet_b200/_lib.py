@@ -91,12 +91,12 @@ def lib():
     L.pvv_probe_tflops.restype = C.c_double
     L.pvv_version.restype = C.c_char_p
     L.pvv_set_host_workers.argtypes = [I]
-    # several ranks on one host (torchrun sets LOCAL_WORLD_SIZE): divide the host cores between them; with fewer than 6
+    # several ranks on one host (torchrun sets LOCAL_WORLD_SIZE): divide the host cores between them; with fewer than 8
     # workers per rank narrowing the mask on the host is slower than copying it wide (profiles/r02_e2e_host_threads.log)
     ranks = int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1)
     if ranks > 1:
         per_rank = ((os.cpu_count() or 2) // 2) // ranks
-        L.pvv_set_host_workers(per_rank if per_rank >= 6 else 0)
+        L.pvv_set_host_workers(per_rank if per_rank >= 8 else 0)
     _lib = L
     return L
 
