@@ -142,6 +142,7 @@ pvv_ws carve(const layout &L, void *base)
     ws.tcq_cnt = (int *)(p + L.o_tcq_cnt);
     ws.tcq_slices = PVV_TCQ_SLICES;
     ws.tcq_slice_cap = L.tcq_slice_cap;
+    ws.want_rank = 0;
     ws.idxs_used = nullptr;
     ws.cap = L.cap;
     ws.ntiles = L.ntiles;
@@ -197,6 +198,7 @@ int run_front(const pvv_job *j, const pvv_debug *dbg, pvv_dims *d_out, pvv_ws *w
     cudaStream_t st = (cudaStream_t)j->stream;
     pvv_ws ws = carve(L, j->workspace);
     if (dbg) ws.idxs_used = dbg->idxs;
+    ws.want_rank = dbg && dbg->k3_variant == 11 ? 1 : 0;   // the experimental k_count_tc2 (variant 10) is the only reader
     const pvv_dims d = make_dims(j);
     cudaError_t e = cudaMemsetAsync(j->workspace, 0, L.zero_bytes, st);
     if (e) return fail_cuda(e);

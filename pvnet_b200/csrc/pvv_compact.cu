@@ -187,6 +187,7 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
     if (threadIdx.x == 0) {
         ws.tn[img] = carry;
         ws.img_flags[img] = flags;
+        if (carry) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_NEED_LO], (unsigned long long)pvv_pool_span(carry));
         __threadfence();
         s_last = atomicAdd(&ws.counters[PVV_CTR_TICKET], 1u) == gridDim.x - 1;
     }
@@ -197,17 +198,8 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
     // Pool overflow (a user-set pool_capacity that is too small, or an injected `selection` that keeps far more than
     // max_num pixels): images are admitted greedily in batch order; one that does not fit is dropped (zero keypoints,
     // PVV_IMG_OVERFLOW) and takes no room, so every later image that still fits is kept.  Sequential, but b is small and
-    // this only runs when the batch as a whole does not fit.
-    __shared__ long long s_need;
-    if (threadIdx.x == 0) s_need = 0;
-    __syncthreads();
-    {
-        long long need = 0;
-        for (int i = threadIdx.x; i < d.b; i += kThreads) need += pvv_pool_span(((volatile int *)ws.tn)[i]);
-        if (need) atomicAdd((unsigned long long *)&s_need, (unsigned long long)need);
-    }
-    __syncthreads();
-    if (s_need > ws.cap) {
+    // this only runs when the batch as a whole does not fit (every image's block added its span to PVV_CTR_NEED).
+    if (*(volatile unsigned long long *)&ws.counters[PVV_CTR_NEED_LO] > (unsigned long long)ws.cap) {
         if (threadIdx.x == 0) {
             long long used = 0;
             for (int i = 0; i < d.b; ++i) {
@@ -238,8 +230,8 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
         const int c = (n + PVV_CHUNK_PX - 1) / PVV_CHUNK_PX;
         int total_c;
         const int ex_c = block_excl_scan(c, &total_c);
-        int total_r;
-        const int ex_r = block_excl_scan(n > 0 ? 1 : 0, &total_r);   // rank of the image among those that vote
+        int total_r = 0, ex_r = 0;
+        if (ws.want_rank) ex_r = block_excl_scan(n > 0 ? 1 : 0, &total_r);   // rank of the image among those that vote (k_count_tc2)
         if (i < d.b) {
             ws.img_off[i] = my_off;
             ws.chunk_start[i] = chunk + ex_c;

@@ -22,6 +22,7 @@ struct pvv_ws {
     uint4 *tcq;                   // tensor-pipe K3: flagged (hypothesis, 16-pixel group) entries, one slice per CTA of k_count_tc2
     int *tcq_cnt;                 // [tcq_slices] entries pushed per slice (may exceed tcq_slice_cap: the excess was resolved in line)
     int tcq_slices, tcq_slice_cap;
+    int want_rank;                // 1: K1c also ranks the images that vote (img_rank, PVV_CTR_NIMG): only k_count_tc2 reads them
     int *tile_cnt;                // [b][ntiles] foreground pixels per compaction tile
     int *tile_off;                // [b][ntiles] exclusive prefix of tile_cnt within the image
     uint32_t *fg_bits;            // [b][ntiles][32] foreground bitmask (bit i of word w = pixel 32w+i of the tile), after
@@ -38,7 +39,7 @@ struct pvv_ws {
 };
 
 enum { PVV_CTR_TICKET = 0, PVV_CTR_WORK = 1, PVV_CTR_STATUS = 2, PVV_CTR_AMB_LO = 4, PVV_CTR_AMB_HI = 5,
-       PVV_CTR_NIMG = 6 /* images that vote (tn > 0) */ };
+       PVV_CTR_NIMG = 6 /* images that vote (tn > 0) */, PVV_CTR_NEED_LO = 8 /* + 9: pool pixels the batch needs (u64) */ };
 #define PVV_TCQ_SLICES 148   // = CTAs of the tensor-pipe counting kernel (one per SM of a B200)
 enum { PVV_IMG_SKIPPED = 1, PVV_IMG_SUBSAMPLED = 2, PVV_IMG_OVERFLOW = 4 };
 

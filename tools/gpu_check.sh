@@ -17,6 +17,6 @@ timeout 300 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu1.log 2>&1
 echo "ncu launches exit $?"
 timeout 300 $CMD > $OUT/${TAG}_plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_count -s 3 -c 2 -f -o $OUT/${TAG}_k_count $CMD > $OUT/${TAG}_ncu2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_count_tc -s 3 -c 1 -f -o $OUT/${TAG}_k_count $CMD > $OUT/${TAG}_ncu2.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT
