@@ -19,8 +19,10 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libpvvote.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-SOURCES = ["pvv_compact.cu", "pvv_vote.cu", "pvv_finalize.cu", "pvv_primitives.cu", "pvv_pnp.cu", "pvv_capi.cu", "pvv_host.cu"]
-HEADERS = ["pvv_common.cuh", "pvv_internal.cuh", "pvv_vote_tc.cuh", "pvv_vote_tc2.cuh", "../../include/pvvote.h"]
+SOURCES = ["pvv_compact.cu", "pvv_vote.cu", "pvv_finalize.cu", "pvv_primitives.cu", "pvv_pnp.cu", "pvv_capi.cu", "pvv_host.cu",
+           "pvv_host_simd.cpp"]
+HEADERS = ["pvv_common.cuh", "pvv_internal.cuh", "pvv_vote_tc.cuh", "pvv_vote_tc2.cuh", "pvv_host_simd.h",
+           "../../include/pvvote.h"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 
@@ -34,7 +36,7 @@ def _stale(dst, srcs):
 
 def _compile(src):
     s = os.path.join(CSRC, src)
-    o = os.path.join(OBJ, src.replace(".cu", ".o"))
+    o = os.path.join(OBJ, os.path.splitext(src)[0] + ".o")   # nvcc hands a .cpp to the host compiler as it is
     deps = [s] + [os.path.join(CSRC, h) for h in HEADERS]
     if not _stale(o, deps):
         return o, ""

@@ -10,6 +10,23 @@
 #define PVV_CHUNK_PX 256   // pixels per voting work item (K3)
 #define PVV_POOL_ALIGN 16  // every image starts on a multiple of this many pixels in the pool: the SoA rows of a voting
                            // chunk (4 / 8 / 16 bytes per pixel) are then 16-byte aligned sources for bulk copies (TMA)
+// Checked build (-DPVV_CHECKED, tools/build_variant.sh checked -DPVV_CHECKED): bounds asserts on pool / chunk-table / queue /
+// tensor-memory indices.  A failed check prints the site and traps (the call returns PVV_ERR_CUDA).  Off in the shipped
+// library: the macro expands to nothing.  This replaces a compute-sanitizer run, which the GPU pool does not allow.
+#ifdef PVV_CHECKED
+#include <stdio.h>
+#define PVV_CHECK(cond)                                                                                              \
+    do {                                                                                                             \
+        if (!(cond)) {                                                                                               \
+            printf("PVV_CHECK failed: %s  (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, \
+                   (int)threadIdx.x);                                                                                \
+            __trap();                                                                                                \
+        }                                                                                                            \
+    } while (0)
+#else
+#define PVV_CHECK(cond) ((void)0)
+#endif
+
 #ifndef PVV_FIN_SPLIT
 #define PVV_FIN_SPLIT 4     // CTAs sharing the pixels of one (image, keypoint) in K4
 #endif

@@ -7,10 +7,17 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <stdio.h>
 #include <thread>
 #include <vector>
 
+#include "pvv_host_simd.h"
 #include "pvv_internal.cuh"
 
 namespace {
@@ -42,44 +49,15 @@ bool is_pinned(const void *p, void **dev_ptr)
 // torch.argmax hands the layer an int64 mask (tools/train_linemod.py:254): 8 bytes per pixel of which 7 are zero, 79 % of
 // the bytes a host-buffer call of configs[1] used to push over PCIe.  A few host threads narrow it to one byte per pixel
 // (the value the foreground rule looks at: the low byte for `.byte()`, 0/1 for `== 1`) into a pinned staging buffer,
-// sub-batch by sub-batch, while the previous sub-batch is already crossing the bus and being voted on.
-template <typename T>
-void narrow_range(const T *src, uint8_t *dst, size_t n, int fg_rule)
-{
-    if (fg_rule == PVV_FG_EQ1) { for (size_t i = 0; i < n; ++i) dst[i] = src[i] == (T)1 ? 1 : 0; }
-    else { for (size_t i = 0; i < n; ++i) dst[i] = (uint8_t)(long long)src[i]; }   // float: truncation toward zero, like .byte()
-}
-
-// int64 (what torch.argmax produces): eight pixels per step, the low bytes (or the == 1 flags) gathered into one 64-bit
-// store -- ~3 scalar operations per pixel, so a core narrows at memory speed without any ISA-specific code
-template <>
-void narrow_range<long long>(const long long *src, uint8_t *dst, size_t n, int fg_rule)
-{
-    const uint64_t *w = (const uint64_t *)src;
-    size_t i = 0;
-    if (fg_rule == PVV_FG_EQ1) {
-        for (; i + 8 <= n; i += 8) {
-            uint64_t o = 0;
-            for (int k = 0; k < 8; ++k) o |= (uint64_t)(w[i + k] == 1u) << (8 * k);
-            memcpy(dst + i, &o, 8);
-        }
-        for (; i < n; ++i) dst[i] = w[i] == 1u ? 1 : 0;
-    } else {
-        for (; i + 8 <= n; i += 8) {
-            uint64_t o = 0;
-            for (int k = 0; k < 8; ++k) o |= (w[i + k] & 0xffu) << (8 * k);
-            memcpy(dst + i, &o, 8);
-        }
-        for (; i < n; ++i) dst[i] = (uint8_t)w[i];
-    }
-}
-
+// sub-batch by sub-batch, while the previous sub-batch is already crossing the bus and being voted on.  The loops are in
+// pvv_host_simd.cpp (AVX-512 where the CPU has it: 132 GB/s with 8 threads against 65 GB/s scalar).
 void narrow_dispatch(const void *src, int dtype, uint8_t *dst, size_t i0, size_t n, int fg_rule)
 {
+    const int eq1 = fg_rule == PVV_FG_EQ1;
     switch (dtype) {
-        case PVV_MASK_I64: narrow_range((const long long *)src + i0, dst + i0, n, fg_rule); break;
-        case PVV_MASK_I32: narrow_range((const int32_t *)src + i0, dst + i0, n, fg_rule); break;
-        default: narrow_range((const float *)src + i0, dst + i0, n, fg_rule); break;
+        case PVV_MASK_I64: pvv_narrow_i64((const int64_t *)src + i0, dst + i0, n, eq1); break;
+        case PVV_MASK_I32: pvv_narrow_i32((const int32_t *)src + i0, dst + i0, n, eq1); break;
+        default: pvv_narrow_f32((const float *)src + i0, dst + i0, n, eq1); break;
     }
 }
 
@@ -102,12 +80,68 @@ struct pinned_stage {
 };
 thread_local pinned_stage t_stage;
 
+// -DPVV_HOST_TRACE: timeline of a host-buffer call on stderr (development builds only, tools/build_variant.sh)
+#ifdef PVV_HOST_TRACE
+#define PVV_HOST_MAX_SUB_TR 8
+struct host_trace {
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    cudaEvent_t g0 = nullptr, gc[PVV_HOST_MAX_SUB_TR] = {}, gk[PVV_HOST_MAX_SUB_TR] = {}, gb[PVV_HOST_MAX_SUB_TR] = {}, gm[PVV_HOST_MAX_SUB_TR] = {};
+    double g0_us = 0;
+    void gpu_start(cudaStream_t st)
+    {
+        cudaEventCreate(&g0);
+        for (auto &e : gc) cudaEventCreate(&e);
+        for (auto &e : gk) cudaEventCreate(&e);
+        for (auto &e : gb) cudaEventCreate(&e);
+        for (auto &e : gm) cudaEventCreate(&e);
+        cudaEventRecord(g0, st);
+        g0_us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+    }
+    void gpu_report(int nsub)
+    {
+        for (int s = 0; s < nsub; ++s) {
+            float a = 0, b = 0, c = 0, m = 0;
+            cudaEventElapsedTime(&a, g0, gc[s]);
+            cudaEventElapsedTime(&b, g0, gk[s]);
+            cudaEventElapsedTime(&c, g0, gb[s]);
+            cudaEventElapsedTime(&m, g0, gm[s]);
+            fprintf(stderr, "[pvv gpu ] sub-batch %d: copies start %8.1f  mask done %8.1f  spans pulled %8.1f us   voted %8.1f us   (host clock; start event at %.1f)\n", s,
+                    g0_us + c * 1e3, g0_us + m * 1e3, g0_us + a * 1e3, g0_us + b * 1e3, g0_us);
+        }
+    }
+    void mark(const char *what, int i = -1)
+    {
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+        fprintf(stderr, "[pvv host] %8.1f us  %s %d\n", us, what, i);
+    }
+};
+#define HOST_TRACE(tr, ...) (tr).mark(__VA_ARGS__)
+#else
+struct host_trace {};
+#define HOST_TRACE(tr, ...) ((void)(tr))
+#endif
+
 std::atomic<int> g_host_workers(-1);   // pvv_set_host_workers: < 0 auto, 0 narrowing off, > 0 that many
+
+#ifndef PVV_HOST_NSUB
+#define PVV_HOST_NSUB 4        // sub-batches of a pipelined host call (batches of >= 8 images)
+#endif
+#define PVV_HOST_MAX_SUB 8
+static_assert(PVV_HOST_NSUB >= 1 && PVV_HOST_NSUB <= PVV_HOST_MAX_SUB, "sub-batch count");
+
+inline int host_nsub(int b) { return b >= 2 * PVV_HOST_NSUB ? PVV_HOST_NSUB : b >= 8 ? 4 : b >= 2 ? 2 : 1; }
+
+// Layouts of a pinned vertex tensor whose foreground row spans the pull kernel (k_pull_spans) stages in device memory,
+// instead of the scatter kernel gathering them pixel by pixel over PCIe:  PLANAR = x contiguous (the network's NCHW
+// output seen as [b,h,w,vn,2]: a span is a run of floats in each of the 2 vn planes);  INTERLEAVED = the 2 vn values of a
+// pixel contiguous and pixels of a row adjacent (a contiguous [b,h,w,vn,2] tensor: a span is ONE run of floats).
+enum { CROP_NONE = 0, CROP_PLANAR = 1, CROP_INTERLEAVED = 2 };
 
 struct host_plan {
     size_t dev_ws, sub_ws, o_mask, o_vertex, o_idxs, o_sel, o_mean, o_out, o_tn, o_status, total;
     long long mask_span, vertex_span;
     bool vertex_zero_copy;
+    int crop_kind;
     void *vertex_dev;
 };
 
@@ -122,9 +156,17 @@ int plan_host(const pvv_job *j, host_plan *P)
     if (P->mask_span < 0 || P->vertex_span < 0) return PVV_ERR_INVALID;
     P->vertex_dev = nullptr;
     P->vertex_zero_copy = is_pinned(j->vertex, &P->vertex_dev);
+    {
+        const int64_t *v = j->vertex_strides;
+        P->crop_kind = CROP_NONE;
+        if (P->vertex_zero_copy && v[2] == 1 && v[1] >= j->w && v[3] > 0 && v[4] > 0 && v[0] < (1LL << 31))
+            P->crop_kind = CROP_PLANAR;
+        else if (P->vertex_zero_copy && v[4] == 1 && v[3] == 2 && v[2] == 2 * (int64_t)j->vn && v[1] >= v[2] * j->w)
+            P->crop_kind = CROP_INTERLEAVED;
+    }
     size_t o = align_up(pvv_workspace_bytes(j), 256);
-    {   // the narrowing path votes on up to 4 sub-batches on two streams at once: each needs a workspace of its own
-        const int nsub = j->b >= 8 ? 4 : j->b >= 2 ? 2 : 1;
+    {   // the pipelined path votes on its sub-batches on two streams at once: each needs a workspace of its own
+        const int nsub = host_nsub(j->b);
         pvv_job sj = *j;
         sj.b = (j->b + nsub - 1) / nsub;
         sj.pool_capacity = 0;                       // sub-batches of a narrowed call use the default pool bound
@@ -134,16 +176,209 @@ int plan_host(const pvv_job *j, host_plan *P)
     P->dev_ws = o;
     auto take = [&](size_t bytes) { const size_t at = o; o = align_up(o + bytes, 256); return at; };
     P->o_mask = take((size_t)P->mask_span * mask_elem(j->mask_dtype));
-    P->o_vertex = take(P->vertex_zero_copy ? 0 : (size_t)P->vertex_span * sizeof(float));
+    // device image of the vertex tensor (same strides): all of it for pageable input; only the foreground row spans are
+    // filled for pinned input of a layout the pull kernel knows; nothing for pinned input of any other layout (zero-copy)
+    P->o_vertex = take(P->vertex_zero_copy && P->crop_kind == CROP_NONE ? 0 : (size_t)P->vertex_span * sizeof(float));
     P->o_idxs = take(j->idxs ? sizeof(int32_t) * (size_t)j->b * j->hn_total * j->vn * 2 : 0);
     P->o_sel = take(j->selection ? sizeof(float) * (size_t)j->b * j->h * j->w : 0);
     P->o_mean = take(sizeof(float) * (size_t)j->b * j->vn * 2);
     P->o_out = take(sizeof(float) * (size_t)j->b * j->vn * 4);
     P->o_tn = take(sizeof(int) * (size_t)j->b);
-    P->o_status = take(sizeof(int32_t) * 4);   // one PVV_FLAG_* word per sub-batch
+    P->o_status = take(sizeof(int32_t) * PVV_HOST_MAX_SUB);   // one PVV_FLAG_* word per sub-batch
     P->total = o;
     return PVV_OK;
 }
+
+// Host worker threads of the prepared path, kept per calling thread and parked on a condition variable between calls.
+class worker_pool {
+    std::mutex m;
+    std::condition_variable cv, cv_done;
+    std::vector<std::thread> th;
+    const std::function<void()> *job = nullptr;
+    unsigned long long gen = 0;
+    int active = 0, njob = 0;
+    bool stop = false;
+
+    void loop(int id)
+    {
+        unsigned long long seen = 0;
+        std::unique_lock<std::mutex> lk(m);
+        for (;;) {
+            cv.wait(lk, [&] { return stop || gen != seen; });
+            if (stop) return;
+            seen = gen;
+            if (id >= njob) continue;
+            const std::function<void()> *f = job;
+            lk.unlock();
+            (*f)();
+            lk.lock();
+            if (--active == 0) cv_done.notify_all();
+        }
+    }
+
+public:
+    // runs *f on n workers; the guard's wait() (or its destructor) returns when all of them are back
+    struct job_guard {
+        worker_pool &p;
+        bool waited = false;
+        job_guard(worker_pool &pool, int n, const std::function<void()> *f) : p(pool)
+        {
+            std::lock_guard<std::mutex> lk(p.m);
+            while ((int)p.th.size() < n) {
+                const int id = (int)p.th.size();
+                p.th.emplace_back([&pool, id] { pool.loop(id); });
+            }
+            p.job = f; p.njob = n; p.active = n; ++p.gen;
+            p.cv.notify_all();
+        }
+        void wait()
+        {
+            if (waited) return;
+            std::unique_lock<std::mutex> lk(p.m);
+            p.cv_done.wait(lk, [&] { return p.active == 0; });
+            waited = true;
+        }
+        ~job_guard() { wait(); }
+    };
+    ~worker_pool()
+    {
+        { std::lock_guard<std::mutex> lk(m); stop = true; }
+        cv.notify_all();
+        for (auto &t : th) t.join();
+    }
+};
+thread_local worker_pool t_pool;
+
+// Pull kernel: for every image row, the span [first, last] of its foreground pixels (found in the byte mask that has just
+// arrived in device memory), in all 2 vn (keypoint, component) planes, from the pinned host tensor (mapped into the device's
+// address space) to the same place in the device image of the tensor.  One warp per row; coalesced 4-byte loads, 12 per
+// lane in flight.  Measured (tools/crop_probe.cu, 32 images of configs[1]): 43 GB/s over PCIe for such spans, against
+// 38 GB/s for bounding-box copies by the copy engines (which also move 1.5x the bytes: boxes, not spans) and 13 - 20 GB/s
+// for the per-pixel gather in the scatter kernel.  One 64-thread CTA per SM with <= 32 registers and no shared memory:
+// the tensor-pipe counting kernel's CTA leaves 4096 registers and 2 KB of shared memory on its SM, room for exactly two of
+// these (one per voting stream), so the spans of sub-batch s + 1 cross the bus while sub-batch s is being voted on -- and a
+// counting kernel that arrives while they are resident still finds its 61440 registers.
+template <bool PLANAR, bool VEC4>
+__global__ void __launch_bounds__(64, 32) k_pull_spans(const uint8_t *__restrict__ mask, const float *__restrict__ src,
+                                                       float *__restrict__ dst, int b, int h, int w, int vn, long long vs0,
+                                                       long long vs1, long long vs2, long long vs3, long long vs4)
+{
+    const int lane = threadIdx.x & 31;
+    const int nwarps = (int)gridDim.x * 2;
+    for (int task = (int)blockIdx.x * 2 + (threadIdx.x >> 5); task < b * h; task += nwarps) {
+        const int img = task / h, y = task - img * h;
+        const uint8_t *row = mask + (size_t)task * w;
+        int first = 0x7fffffff, last = -1;
+        if ((w & 3) == 0) {   // rows start on 4-byte boundaries (the mask buffer is 256-byte aligned)
+            for (int x = lane * 4; x < w; x += 128) {
+                const uint32_t v = *reinterpret_cast<const uint32_t *>(row + x);
+                if (v) {
+                    first = min(first, x + ((__ffs((int)v) - 1) >> 3));
+                    last = max(last, x + 3 - (__clz((int)v) >> 3));
+                }
+            }
+        } else {
+            for (int x = lane; x < w; x += 32)
+                if (row[x]) { first = min(first, x); last = max(last, x); }
+        }
+        first = __reduce_min_sync(0xffffffffu, first);
+        last = __reduce_max_sync(0xffffffffu, last);
+        if (last < 0) continue;
+        const long long base = (long long)img * vs0 + (long long)y * vs1;
+        if (PLANAR) {
+            const float *sb = src + base;
+            float *db = dst + base;
+            const int planes = 2 * vn;
+            for (int p0 = 0; p0 < planes; p0 += 4) {
+                int po[4];   // plane offsets inside the image: 32 bits (the host checks the image stride)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int p = min(p0 + k, planes - 1);
+                    po[k] = (int)((long long)(p >> 1) * vs3 + (long long)(p & 1) * vs4);
+                }
+                if (VEC4) {
+                    // 16-byte loads (rows, planes and both tensors are 16-byte aligned, w % 4 == 0): a lane moves 4 pixels, a
+                    // warp 128 -- one round trip per plane for a typical span, four planes in flight; up to 3 pixels
+                    // either side of the span ride along (they stay inside the row)
+                    for (int xs = (first & ~3) + 4 * lane; xs <= last; xs += 128) {
+                        float4 v[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) v[k] = __ldg(reinterpret_cast<const float4 *>(sb + po[k] + xs));
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (p0 + k < planes) *reinterpret_cast<float4 *>(db + po[k] + xs) = v[k];
+                    }
+                    continue;
+                }
+                for (int xs = first & ~31; xs <= last; xs += 64) {
+                    const int xa = xs + lane, xb = xa + 32;
+                    const bool oka = xa >= first && xa <= last, okb = xb <= last;   // xb >= first always
+                    float va[4], vb[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        va[k] = oka ? __ldg(sb + po[k] + xa) : 0.f;
+                        vb[k] = okb ? __ldg(sb + po[k] + xb) : 0.f;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (p0 + k < planes) {
+                            if (oka) db[po[k] + xa] = va[k];
+                            if (okb) db[po[k] + xb] = vb[k];
+                        }
+                }
+            }
+        } else {
+            // one run of floats: [first * vs2, (last + 1) * vs2), vs2 = 2 vn
+            const long long r0 = base + (long long)first * vs2, r1 = base + (long long)(last + 1) * vs2;
+            for (long long o = (r0 & ~31LL) + lane; o < r1; o += 32 * 8) {
+                float v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { const long long q = o + 32 * k; v[k] = (q >= r0 && q < r1) ? __ldg(src + q) : 0.f; }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { const long long q = o + 32 * k; if (q >= r0 && q < r1) dst[q] = v[k]; }
+            }
+        }
+    }
+}
+
+// Streams and events of the pipelined path, kept per calling thread and device (creating three streams and eleven events
+// costs ~0.2 ms, a tenth of a call).  A host call synchronises before it returns, so they are idle between calls.
+struct host_streams {
+    int dev = -1, sms = 148;
+    cudaStream_t cs = nullptr, ks[2] = {nullptr, nullptr};
+    cudaEvent_t ev[PVV_HOST_MAX_SUB + 3] = {};
+    void drop()
+    {
+        for (auto &e : ev) { if (e) cudaEventDestroy(e); e = nullptr; }
+        if (cs) cudaStreamDestroy(cs);
+        for (auto &k : ks) { if (k) cudaStreamDestroy(k); k = nullptr; }
+        cs = nullptr; dev = -1;
+        cudaGetLastError();
+    }
+    bool get()
+    {
+        int d = -1;
+        if (cudaGetDevice(&d) != cudaSuccess) return false;
+        if (d == dev) return true;
+        drop();
+        bool ok = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&ks[0], cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&ks[1], cudaStreamNonBlocking) == cudaSuccess;
+        for (auto &e : ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) { drop(); return false; }
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d);
+        // the pull kernel uses no shared memory, but it has to run beside the tensor-pipe counting kernel, whose 224 KB need
+        // the SM's largest shared-memory carve-out: ask for the same one, or its CTAs wait until that kernel has left the SM
+        cudaFuncSetAttribute(k_pull_spans<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k_pull_spans<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k_pull_spans<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaGetLastError();
+        dev = d;
+        return true;
+    }
+    ~host_streams() { drop(); }
+};
+thread_local host_streams t_streams;
 
 // One sub-batch [i0, i1) of the job on the compute stream; device-side inputs already point at the full arrays.
 int run_sub(const pvv_job &dj, int i0, int i1, bool cov, float confidence, int max_iter, const float *mean_dev,
@@ -172,9 +407,11 @@ int run_sub(const pvv_job &dj, int i0, int i1, bool cov, float confidence, int m
 int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const float *mean_host, float *out_host,
              int64_t *h2d_bytes, int64_t *d2h_bytes)
 {
+    host_trace tr;
     host_plan P;
     int r = plan_host(j, &P);
     if (r != PVV_OK) return r;
+    HOST_TRACE(tr, "planned");
     if (!j->workspace || j->workspace_bytes < P.total || !out_host) return PVV_ERR_WORKSPACE;
     if (cov && !mean_host) return PVV_ERR_INVALID;
     if (j->mask_dtype == PVV_MASK_LOGITS_F32) return PVV_ERR_UNSUPPORTED;  // logits live on the device, next to the network
@@ -193,20 +430,25 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     // the mask is copied per sub-batch only when images are laid out one after the other (stride[0] covers an image)
     const bool separable = j->mask_strides[0] >= (int64_t)(j->h - 1) * j->mask_strides[1] + (int64_t)(j->w - 1) * j->mask_strides[2] + 1;
     int nsub = (mask_pinned && P.vertex_zero_copy && separable && j->b >= 8) ? 4 : 1;
-    // wide, contiguous masks are narrowed to one byte per pixel by host threads (pinned or pageable alike)
+    // Prepared path: host threads walk contiguous masks piece by piece -- wide masks are narrowed to one byte per pixel
+    // (pinned or pageable alike), and the foreground window of every image is measured -- so that only a byte per pixel and
+    // the windows of the vertex tensor cross the bus, as plain copies
     const size_t npx = (size_t)j->h * j->w;
     const bool contiguous = j->mask_strides[2] == 1 && j->mask_strides[1] == j->w && j->mask_strides[0] == (int64_t)npx;
-    uint8_t *stage = nullptr;
     const int workers_cfg = g_host_workers.load(std::memory_order_relaxed);
-    if (workers_cfg != 0 && esz > 1 && contiguous && P.vertex_zero_copy && npx * j->b >= (size_t)1 << 18)
-        stage = (uint8_t *)t_stage.get(npx * j->b);
+    const bool prepared = workers_cfg != 0 && contiguous && P.vertex_zero_copy && npx * j->b >= (size_t)1 << 18 &&
+                          (esz > 1 || (mask_pinned && P.crop_kind != CROP_NONE)) && j->w >= 8;
+    uint8_t *stage = nullptr;
+    if (prepared && esz > 1) stage = (uint8_t *)t_stage.get(npx * j->b);
     const bool narrow = stage != nullptr;
+    const bool prep = prepared && (narrow || esz == 1);
+    if (prep) nsub = host_nsub(j->b);
     if (narrow) {
-        nsub = j->b >= 8 ? 4 : j->b >= 2 ? 2 : 1;
         dj.mask_dtype = PVV_MASK_U8;           // the staged bytes already are what the foreground rule looks at
         dj.mask_strides[0] = (int64_t)npx; dj.mask_strides[1] = j->w; dj.mask_strides[2] = 1;
         h2d += (int64_t)(npx * j->b) - (int64_t)mbytes;
     }
+    std::vector<char> gathered(j->b, 1);   // images whose foreground vectors the scatter kernel pulls over the bus itself
 
     if (P.vertex_zero_copy) {
         dj.vertex = (const float *)P.vertex_dev;
@@ -237,32 +479,41 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     float *out_dev = (float *)(base + P.o_out);
     int *tn_dev = (int *)(base + P.o_tn);
     int32_t *status_dev = (int32_t *)(base + P.o_status);
-    if ((e = cudaMemsetAsync(status_dev, 0, sizeof(int32_t) * 4, st))) return PVV_ERR_CUDA;
+    if ((e = cudaMemsetAsync(status_dev, 0, sizeof(int32_t) * PVV_HOST_MAX_SUB, st))) return PVV_ERR_CUDA;
     const size_t out_bytes = sizeof(float) * (size_t)j->b * j->vn * (cov ? 4 : 2);
 
-    if (narrow) {
-        // workers narrow 64 K-pixel pieces in order; the calling thread hands every finished sub-batch to the copy stream
-        // and enqueues its voting on the caller's stream, so host narrowing, PCIe and the SMs overlap
-        const size_t piece = (size_t)1 << 16;
-        size_t sub_lo[5];
-        for (int s = 0; s <= nsub; ++s) sub_lo[s] = (size_t)((long long)j->b * s / nsub) * npx;
-        size_t piece_base[5];
-        piece_base[0] = 0;
-        for (int s = 0; s < nsub; ++s) piece_base[s + 1] = piece_base[s] + (sub_lo[s + 1] - sub_lo[s] + piece - 1) / piece;
+    if (prep) {
+        // Workers take pieces (runs of whole rows of one image, ~64 K pixels) in order: narrow, then measure the foreground
+        // window.  The calling thread hands every finished sub-batch to the copy stream (mask bytes, then the windows of the
+        // vertex tensor) and enqueues its voting, so host work, PCIe and the SMs overlap.
+        const int rpp = std::max(1, (int)(((size_t)1 << 16) / (size_t)j->w));    // rows per piece
+        const int ppi = (j->h + rpp - 1) / rpp;                                  // pieces per image
+        int img_lo[PVV_HOST_MAX_SUB + 1];
+        for (int s = 0; s <= nsub; ++s) img_lo[s] = (int)((long long)j->b * s / nsub);
+        struct piece_info { long long count, span; };
+        std::vector<piece_info> pieces((size_t)j->b * ppi);
+        const size_t npieces = pieces.size();
         std::atomic<size_t> next(0);
-        std::atomic<size_t> done[4];
-        for (int s = 0; s < 4; ++s) done[s].store(0);
-        const int fg_rule = j->fg_rule, dtype = j->mask_dtype;
+        std::atomic<size_t> done[PVV_HOST_MAX_SUB];
+        for (int s = 0; s < PVV_HOST_MAX_SUB; ++s) done[s].store(0);
+        const int fg_rule = j->fg_rule, dtype = j->mask_dtype, hh = j->h, ww = j->w;
         const void *src = j->mask;
         auto work = [&] {
             for (;;) {
                 const size_t c = next.fetch_add(1);
-                if (c >= piece_base[nsub]) return;
+                if (c >= npieces) return;
+                const int img = (int)(c / ppi), r0 = (int)(c % ppi) * rpp, rows = std::min(rpp, hh - r0);
+                const size_t i0 = (size_t)img * npx + (size_t)r0 * ww;
+                if (narrow) narrow_dispatch(src, dtype, stage, i0, (size_t)rows * ww, fg_rule);
+                piece_info &pi = pieces[c];
+                pi.span = 0;
+                pi.count = pvv_fg_extent((narrow ? stage : (const uint8_t *)src) + i0, ww, rows, &pi.span);
+                // the staged bytes are about to be read by a copy engine: write them back now, while this core is awake -- a
+                // copy engine reading lines that sit modified in the cache of a core that has since gone to sleep crawls
+                // (measured: 2.4 MB in 0.29 ms instead of 0.05 ms, and the kernels running at the time slow down with it)
+                if (narrow) pvv_writeback(stage + i0, (size_t)rows * ww);
                 int s = 0;
-                while (c >= piece_base[s + 1]) ++s;
-                const size_t i0 = sub_lo[s] + (c - piece_base[s]) * piece;
-                const size_t n = i0 + piece <= sub_lo[s + 1] ? piece : sub_lo[s + 1] - i0;
-                narrow_dispatch(src, dtype, stage, i0, n, fg_rule);
+                while (img >= img_lo[s + 1]) ++s;
                 done[s].fetch_add(1, std::memory_order_release);
             }
         };
@@ -272,44 +523,91 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
 #endif
         int nthreads = workers_cfg > 0 ? workers_cfg : (int)(hw / PVV_HOST_THREADS_DIV);
         nthreads = nthreads < 1 ? 1 : nthreads > 16 ? 16 : nthreads;
-        if ((size_t)nthreads > piece_base[nsub]) nthreads = (int)piece_base[nsub];
-        std::vector<std::thread> pool;
-        for (int t = 0; t < nthreads; ++t) pool.emplace_back(work);
-        // one copy stream and two voting streams: the compaction of sub-batch s + 1 gathers its foreground vectors over PCIe
-        // (bus-bound) while sub-batch s is being voted on (SM-bound); every sub-batch has its own workspace
-        cudaStream_t cs = nullptr, ks[2] = {nullptr, nullptr};
-        cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-        bool ok = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess &&
-                  cudaStreamCreateWithFlags(&ks[0], cudaStreamNonBlocking) == cudaSuccess &&
-                  cudaStreamCreateWithFlags(&ks[1], cudaStreamNonBlocking) == cudaSuccess;
-        for (int i = 0; ok && i < 7; ++i) ok = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) == cudaSuccess;
+        if ((size_t)nthreads > npieces) nthreads = (int)npieces;
+        HOST_TRACE(tr, "inputs enqueued");
+        // (the workers are parked threads of this calling thread: a thread that EXITS while the GPU is busy stalls the copy
+        // engines and the running kernels for 0.1 - 0.3 ms -- measured, tools/host_trace.py -- so none is created per call)
+        const std::function<void()> work_fn(work);
+        worker_pool::job_guard guard(t_pool, nthreads, &work_fn);
+        HOST_TRACE(tr, "workers started", nthreads);
+        // one copy stream and two voting streams (kept per calling thread): the compaction of sub-batch s + 1 runs while
+        // sub-batch s is being voted on; every sub-batch has its own workspace
+        host_streams &hs = t_streams;
+        bool ok = hs.get();
+        cudaStream_t cs = hs.cs, *ks = hs.ks;
+        cudaEvent_t *ev = hs.ev;   // [0, MAX_SUB): sub-batch copied; MAX_SUB: caller's stream; MAX_SUB + 1, + 2: voting streams
         // everything the caller's stream did before (input copies above, earlier use of the workspace) comes first
-        ok = ok && cudaEventRecord(ev[4], st) == cudaSuccess && cudaStreamWaitEvent(cs, ev[4], 0) == cudaSuccess &&
-             cudaStreamWaitEvent(ks[0], ev[4], 0) == cudaSuccess && cudaStreamWaitEvent(ks[1], ev[4], 0) == cudaSuccess;
+        ok = ok && cudaEventRecord(ev[PVV_HOST_MAX_SUB], st) == cudaSuccess && cudaStreamWaitEvent(cs, ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess &&
+             cudaStreamWaitEvent(ks[0], ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess && cudaStreamWaitEvent(ks[1], ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess;
         r = PVV_OK;
+        HOST_TRACE(tr, "streams ready");
+#ifdef PVV_HOST_TRACE
+        tr.gpu_start(st);
+#endif
+        const uint8_t *mask_bytes = narrow ? stage : (const uint8_t *)j->mask;
         for (int s = 0; s < nsub; ++s) {
-            const size_t want = piece_base[s + 1] - piece_base[s];
+            const int i0 = img_lo[s], i1 = img_lo[s + 1];
+            const size_t want = (size_t)(i1 - i0) * ppi;
             while (done[s].load(std::memory_order_acquire) < want) std::this_thread::yield();
+            HOST_TRACE(tr, "prepared sub-batch", s);
             if (!ok || r != PVV_OK) continue;   // keep draining the workers; nothing more is enqueued
-            const int i0 = (int)((long long)j->b * s / nsub), i1 = (int)((long long)j->b * (s + 1) / nsub);
             cudaStream_t k = ks[s & 1];
-            ok = cudaMemcpyAsync(base + P.o_mask + sub_lo[s], stage + sub_lo[s], sub_lo[s + 1] - sub_lo[s], cudaMemcpyHostToDevice, cs) ==
-                     cudaSuccess &&
-                 cudaEventRecord(ev[s], cs) == cudaSuccess && cudaStreamWaitEvent(k, ev[s], 0) == cudaSuccess;
-            if (ok) {
-                pvv_job sub = dj;
-                sub.pool_capacity = 0;
+#ifdef PVV_HOST_TRACE
+            cudaEventRecord(tr.gb[s], cs);
+#endif
+            ok = cudaMemcpyAsync(base + P.o_mask + (size_t)i0 * npx, mask_bytes + (size_t)i0 * npx, (size_t)(i1 - i0) * npx,
+                                 cudaMemcpyHostToDevice, cs) == cudaSuccess;
+            // foreground row spans of the sub-batch: staged by the pull kernel when that moves at most a few times the bytes
+            // of the pixels themselves (compact objects); otherwise the scatter kernel gathers the pixels in place (sparse
+            // foreground: spans would be whole rows)
+            pvv_job sub = dj;
+            sub.pool_capacity = 0;
+#ifdef PVV_HOST_TRACE
+            cudaEventRecord(tr.gm[s], cs);
+#endif
+            bool staged = false;
+            if (P.crop_kind != CROP_NONE) {
+                long long span_px = 0, fg_px = 0;
+                for (size_t c = (size_t)i0 * ppi; c < (size_t)i1 * ppi; ++c) { span_px += pieces[c].span; fg_px += pieces[c].count; }
+                staged = fg_px > 0 && span_px <= 3 * fg_px + 4096;
+                if (staged) h2d += span_px * j->vn * 8;
+            }
+            ok = ok && cudaEventRecord(ev[s], cs) == cudaSuccess && cudaStreamWaitEvent(k, ev[s], 0) == cudaSuccess;
+            if (ok && staged) {
+                const int64_t *v = j->vertex_strides;
+                float *dev_v = (float *)(base + P.o_vertex);
+                const uint8_t *dev_m = (const uint8_t *)(base + P.o_mask) + (size_t)i0 * npx;
+                const float *src_v = (const float *)P.vertex_dev + (long long)i0 * v[0];
+                const int grid = hs.sms;   // one CTA per SM: see k_pull_spans
+                const bool vec4 = ((v[0] | v[1] | v[3] | v[4] | ww) & 3) == 0 && (((uintptr_t)src_v | (uintptr_t)dev_v) & 15) == 0;
+                float *dst_v = dev_v + (long long)i0 * v[0];
+                if (P.crop_kind == CROP_PLANAR && vec4)
+                    k_pull_spans<true, true><<<grid, 64, 0, k>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
+                else if (P.crop_kind == CROP_PLANAR)
+                    k_pull_spans<true, false><<<grid, 64, 0, k>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
+                else
+                    k_pull_spans<false, false><<<grid, 64, 0, k>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
+                ok = cudaGetLastError() == cudaSuccess;
+                sub.vertex = dev_v;
+                for (int img = i0; img < i1; ++img) gathered[img] = 0;
+            }
+#ifdef PVV_HOST_TRACE
+            cudaEventRecord(tr.gc[s], k);
+#endif
+            if (ok)
                 r = run_sub(sub, i0, i1, cov, confidence, max_iter, mean_dev, out_dev, tn_dev, status_dev + s, k,
                             base + (size_t)s * P.sub_ws, P.sub_ws);
-            }
+#ifdef PVV_HOST_TRACE
+            cudaEventRecord(tr.gk[s], k);
+#endif
+            HOST_TRACE(tr, "enqueued sub-batch", s);
         }
-        for (auto &t : pool) t.join();
+        guard.wait();
+        HOST_TRACE(tr, "workers parked");
         // the caller's stream continues after both voting streams
         for (int i = 0; ok && i < 2; ++i)
-            ok = cudaEventRecord(ev[5 + i], ks[i]) == cudaSuccess && cudaStreamWaitEvent(st, ev[5 + i], 0) == cudaSuccess;
-        for (int i = 0; i < 7; ++i) if (ev[i]) cudaEventDestroy(ev[i]);
-        if (cs) cudaStreamDestroy(cs);
-        for (int i = 0; i < 2; ++i) if (ks[i]) cudaStreamDestroy(ks[i]);
+            ok = cudaEventRecord(ev[PVV_HOST_MAX_SUB + 1 + i], ks[i]) == cudaSuccess &&
+                 cudaStreamWaitEvent(st, ev[PVV_HOST_MAX_SUB + 1 + i], 0) == cudaSuccess;
         if (r != PVV_OK) return r;
         if (!ok) { cudaGetLastError(); return PVV_ERR_CUDA; }
     } else if (nsub == 1) {
@@ -346,7 +644,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     }
     if ((e = cudaMemcpyAsync(out_host, out_dev, out_bytes, cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
     d2h += (int64_t)out_bytes;
-    int32_t status_host[4] = {0, 0, 0, 0};
+    int32_t status_host[PVV_HOST_MAX_SUB] = {0};
     if ((e = cudaMemcpyAsync(status_host, status_dev, sizeof(status_host), cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
     d2h += (int64_t)sizeof(status_host);
     if (P.vertex_zero_copy && h2d_bytes) {
@@ -356,7 +654,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
         e = cudaMemcpyAsync(tn_host, tn_dev, sizeof(int) * j->b, cudaMemcpyDeviceToHost, st);
         if (!e) e = cudaStreamSynchronize(st);
         long long sum = 0;
-        for (int i = 0; i < j->b; ++i) sum += tn_host[i];
+        for (int i = 0; i < j->b; ++i) sum += gathered[i] ? tn_host[i] : 0;
         free(tn_host);
         if (e) return PVV_ERR_CUDA;
         h2d += sum * j->vn * 8;
@@ -364,10 +662,16 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     } else {
         if ((e = cudaStreamSynchronize(st))) return PVV_ERR_CUDA;
     }
+    HOST_TRACE(tr, "synchronised");
+#ifdef PVV_HOST_TRACE
+    if (tr.g0) tr.gpu_report(host_nsub(j->b));
+#endif
     if (h2d_bytes) *h2d_bytes = h2d;
     if (d2h_bytes) *d2h_bytes = d2h;
     // the call has synchronised: a pool overflow (user-set pool_capacity too small) is reported, not silent
-    if ((status_host[0] | status_host[1] | status_host[2] | status_host[3]) & PVV_FLAG_POOL_OVERFLOW) return PVV_ERR_POOL_OVERFLOW;
+    int32_t status_any = 0;
+    for (int s = 0; s < PVV_HOST_MAX_SUB; ++s) status_any |= status_host[s];
+    if (status_any & PVV_FLAG_POOL_OVERFLOW) return PVV_ERR_POOL_OVERFLOW;
     return PVV_OK;
 }
 

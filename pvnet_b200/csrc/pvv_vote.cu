@@ -286,20 +286,26 @@ __device__ __forceinline__ void cp_async8(void *smem, const void *gmem)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <int H, int THREADS, int MINB>
+// PSPLIT: warp groups that share the hypotheses of a pass and split the item's pixel groups between them.  HT = THREADS /
+// PSPLIT threads own H hypotheses each; with few hypotheses (hn <= 128: HT = 32) PSPLIT = 2 gives a CTA two warps on the
+// same shared-memory footprint (one-warp CTAs are limited to 11 per SM by their shared memory: 2.75 warps per scheduler).
+template <int H, int THREADS, int MINB, int PSPLIT = 1>
 __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, band_consts bc)
 {
+    constexpr int HT = THREADS / PSPLIT;
     static_assert(THREADS <= 256 && H <= 8 && PVV_CHUNK_PX / K3_GROUP <= 32, "entry packing");
+    static_assert(HT % 32 == 0 && HT * PSPLIT == THREADS, "a warp belongs to one pixel range");
     __shared__ __align__(16) float sP[K3_SP_FLOATS];
     __shared__ __align__(8) float2 sDir[2][PVV_CHUNK_PX];  // raw pixels, double-buffered (current / prefetched item)
     __shared__ uint32_t sXY[2][PVV_CHUNK_PX];
-    __shared__ float4 sH[H * THREADS];  // this pass's hypotheses in the chunk-local frame: {hx, hy, T, -}
+    __shared__ float4 sH[H * HT];  // this pass's hypotheses in the chunk-local frame: {hx, hy, T, -}
     __shared__ uint32_t s_q[K3_QCAP];   // phase A: (group << 16) | (k << 8) | thread
     __shared__ uint32_t s_q2[K3_QCAP];  // phase B: (pixel << 16) | (k << 8) | thread
     __shared__ int s_id[2], s_P[2], s_qn, s_q2n;
 
     pvv_pdl_enter();
     const int tid = threadIdx.x;
+    const int ht = tid % HT, pg = tid / HT;  // hypothesis thread, pixel range (warp-uniform)
     const int split = THREADS >= 128 ? k3_split_for(ws.chunk_start[d.b] * d.vn, (int)gridDim.x) : 1;
     const int total_items = ws.chunk_start[d.b] * d.vn * split;
     unsigned long long amb_local = 0;
@@ -385,7 +391,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
 
         // exact decision for one in-band test, correcting the provisional count (sign bit of m clear = counted)
         auto resolve = [&](int hbase, int t, int k, int j, float m) {
-            const int h = hbase + k * THREADS + t;
+            const int h = hbase + k * HT + t;
             const float2 hv = ws.hyp[row + h];
             const float2 dir = rDir[j];
             const uint32_t xy = rXY[j];
@@ -396,8 +402,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
             ++amb_local;
         };
 
-        for (int hbase = 0; hbase < d.hn; hbase += THREADS * H) {
-            const bool active = hbase + (tid & ~31) < d.hn;  // warp-uniform: does this warp own hypotheses in the pass
+        // pixel groups of this warp's range
+        const int gper = (ngroups + PSPLIT - 1) / PSPLIT;
+        const int g0 = min(ngroups, pg * gper), g1 = min(ngroups, g0 + gper);
+        for (int hbase = 0; hbase < d.hn; hbase += HT * H) {
+            const bool active = hbase + (ht & ~31) < d.hn;  // warp-uniform: does this warp own hypotheses in the pass
             if (hbase > 0) {
                 __syncthreads();  // the previous pass's deferred entries (s_q2, sH) are consumed
                 if (tid == 0) s_q2n = 0;
@@ -408,18 +417,18 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                 uint32_t dmask[H];
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
-                    const int h = hbase + k * THREADS + tid;
+                    const int h = hbase + k * HT + ht;
                     const float2 hv = h < d.hn ? ws.hyp[row + h] : make_float2(0.f, 0.f);
                     k3_local_hyp(hv.x, hv.y, ox, oy, P, bc, hx[k], hy[k], T[k]);
                     neg[k] = 0;
                     dmask[k] = 0u;
-                    sH[k * THREADS + tid] = make_float4(hx[k], hy[k], T[k], 0.f);  // for the deferred pass
+                    if (PSPLIT == 1 || pg == 0) sH[k * HT + ht] = make_float4(hx[k], hy[k], T[k], 0.f);  // for the deferred pass
                 }
                 // The hot loop has no branch and no divergence: a (slot, group) with any test inside the guard band
                 // only sets a bit in a per-thread mask.
-                uint32_t bit = 1u;
-                const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(sP);
-                for (int g = 0; g < ngroups; ++g, pp += K3_GSTRIDE, bit <<= 1) {
+                uint32_t bit = 1u << g0;
+                const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(sP) + g0 * K3_GSTRIDE;
+                for (int g = g0; g < g1; ++g, pp += K3_GSTRIDE, bit <<= 1) {
                     float mabs[H];
 #pragma unroll
                     for (int k = 0; k < H; ++k) mabs[k] = __int_as_float(0x7f800000);
@@ -461,8 +470,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                 }
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
-                    const int h = hbase + k * THREADS + tid;
-                    const int cnt = npad - sign_lanes_total(neg[k]);  // padded and never-inlier pixels have m < 0
+                    const int h = hbase + k * HT + ht;
+                    const int cnt = (g1 - g0) * K3_GROUP - sign_lanes_total(neg[k]);  // padded and never-inlier pixels have m < 0
                     if (h < d.hn && cnt && !K3_ABL(8)) atomicAdd(&ws.counts[row + h], cnt);
                 }
                 // queue this thread's flagged (slot, group) pairs for the dense passes below: one shared-memory atomic per
@@ -471,7 +480,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                 int mine = 0;
 #pragma unroll
                 for (int k = 0; k < H; ++k) {
-                    dm[k] = hbase + k * THREADS + tid < d.hn && !K3_ABL(1) ? dmask[k] : 0u;
+                    dm[k] = hbase + k * HT + ht < d.hn && !K3_ABL(1) ? dmask[k] : 0u;
                     mine += __popc(dm[k]);
                 }
                 if (__any_sync(0xffffffffu, mine)) {
@@ -491,12 +500,12 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                             const int grp = __ffs(m_k) - 1;
                             m_k &= m_k - 1;
                             if (q < K3_QCAP) {
-                                s_q[q] = ((uint32_t)grp << 16) | ((uint32_t)k << 8) | (uint32_t)tid;
+                                s_q[q] = ((uint32_t)grp << 16) | ((uint32_t)k << 8) | (uint32_t)ht;
                             } else {  // queue full (pathological inputs): resolve in line
-                                const float4 hl = sH[k * THREADS + tid];  // this thread's own entry
+                                const float4 hl = make_float4(hx[k], hy[k], T[k], 0.f);
                                 for (int j = grp * K3_GROUP; j < min(n, (grp + 1) * K3_GROUP); ++j) {
                                     const float m = k3_m(hl.x, hl.y, k3_load_px(sP, j));
-                                    if (!(fabsf(m) > hl.z)) resolve(hbase, tid, k, j, m);
+                                    if (!(fabsf(m) > hl.z)) resolve(hbase, ht, k, j, m);
                                 }
                             }
                             ++q;
@@ -513,7 +522,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                 const int t = (int)(ent & 0xffu), k = (int)((ent >> 8) & 0xffu), grp = (int)(ent >> 16);
                 constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
                 const int u0 = (idx % K3_SUB) * PAIRS;
-                const float4 hl = sH[k * THREADS + t];
+                const float4 hl = sH[k * HT + t];
                 const f32x2 hxx = pk(hl.x, hl.x), hyy = pk(hl.y, hl.y);
                 const ulonglong2 *pg = reinterpret_cast<const ulonglong2 *>(sP) + grp * K3_GSTRIDE + 3 * u0;
                 uint32_t inband = 0u;
@@ -542,7 +551,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
             for (int idx = tid; idx < q2; idx += THREADS) {
                 const uint32_t ent = s_q2[idx];
                 const int t = (int)(ent & 0xffu), k = (int)((ent >> 8) & 0xffu), j = (int)(ent >> 16);
-                const float4 hl = sH[k * THREADS + t];
+                const float4 hl = sH[k * HT + t];
                 resolve(hbase, t, k, j, k3_m(hl.x, hl.y, k3_load_px(sP, j)));
             }
         }
@@ -591,13 +600,13 @@ static bool pvv_band_for(float t, band_consts *bc)
     return true;
 }
 
-template <int H, int THREADS, int MINB>
+template <int H, int THREADS, int MINB, int PSPLIT = 1>
 static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const band_consts &bc, int sms, cudaStream_t st)
 {
     int per_sm = 8;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS, MINB>, THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count<H, THREADS, MINB, PSPLIT>, THREADS, 0);
     if (per_sm < 1) per_sm = 1;
-    pvv_launch_pdl(k_count<H, THREADS, MINB>, dim3(sms * per_sm), dim3(THREADS), st, d, ws, bc);
+    pvv_launch_pdl(k_count<H, THREADS, MINB, PSPLIT>, dim3(sms * per_sm), dim3(THREADS), st, d, ws, bc);
     return cudaGetLastError();
 }
 
@@ -705,6 +714,9 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         e = few ? launch_count_tc<3>(d, ws, bc, sms, st) : launch_count_tc<7>(d, ws, bc, sms, st);
     }
     else if (variant == 10) e = launch_count_tc2<4>(d, ws, bc, sms, st, launches);
+    else if (variant == 11) e = launch_count_t<4, 64, 10, 2>(d, ws, bc, sms, st);
+    else if (variant == 12) e = launch_count_t<4, 128, 5, 4>(d, ws, bc, sms, st);
+    else if (variant == 13) e = launch_count_t<4, 128, 5, 2>(d, ws, bc, sms, st);
     else if (variant == 1) e = launch_count_t<4, 64, 10>(d, ws, bc, sms, st);
     else if (variant == 2) e = launch_count_t<4, 32, 20>(d, ws, bc, sms, st);
     else if (variant == 3) e = launch_count_t<4, 128, 6>(d, ws, bc, sms, st);

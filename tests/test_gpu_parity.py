@@ -303,6 +303,39 @@ def test_host_buffers_match_device_path():
     assert torch.equal(cov_h, cov_d.cpu())
 
 
+def test_host_window_copies():
+    """Pinned host buffers: the foreground span of every image row is staged in device memory by the pull kernel (planar
+    = the network's layout, interleaved = a contiguous [b,h,w,vn,2] tensor); sparse foreground falls back to the in-place
+    gather.  Same bits as the device path in every case."""
+    b = 9
+    mask, vertex, _ = synth.make_batch(b, vn=9, frac=0.03, sigma=0.05, seed=91)
+    mask[4] = 0                                              # an image without foreground: no window, zero keypoints
+    mask[6, 5, 7] = 1                                        # a stray pixel far from the object: a span of its own
+    dm, dv = torch.from_numpy(mask).to(DEV), torch.from_numpy(vertex).to(DEV)
+    want = pv.ransac_voting_layer_v3(dm, dv, 128, 0.99, seed=3).cpu()
+    npx, fg = mask[0].size, int((mask != 0).sum())
+    full = vertex.size * 4
+    planar = synth.as_net_output(vertex, pin=True)
+    inter = torch.from_numpy(vertex).pin_memory()
+    for name, hv in (("planar", planar), ("interleaved", inter)):
+        for hm in (torch.from_numpy(mask).pin_memory(), torch.from_numpy(mask.astype(np.uint8)).pin_memory(),
+                   torch.from_numpy(mask.astype(np.int32))):
+            out = pv.ransac_voting_layer_v3(hm, hv, 128, 0.99, seed=3)
+            assert torch.equal(out, want), (name, hm.dtype)
+            h2d = out.transfer_bytes[0]
+            assert fg * 72 <= h2d - b * npx <= 2.5 * fg * 72, (name, hm.dtype, h2d)   # row spans, not the tensor
+    cov_want = pv.estimate_voting_distribution_with_mean(dm, dv, want.to(DEV), 32, 64, seed=3)[1].cpu()
+    cov = pv.estimate_voting_distribution_with_mean(torch.from_numpy(mask).pin_memory(), planar, want, 32, 64, seed=3)[1]
+    assert torch.equal(cov, cov_want)
+    # sparse foreground: windows would be the whole images -> gathered in place, a few bytes per foreground pixel
+    rng = np.random.default_rng(5)
+    sparse = (rng.random(mask.shape) < 0.01).astype(np.int64)
+    want_s = pv.ransac_voting_layer_v3(torch.from_numpy(sparse).to(DEV), dv, 128, 0.99, seed=3).cpu()
+    out = pv.ransac_voting_layer_v3(torch.from_numpy(sparse).pin_memory(), planar, 128, 0.99, seed=3)
+    assert torch.equal(out, want_s)
+    assert out.transfer_bytes[0] <= b * npx + int((sparse != 0).sum()) * 72 + 4096
+
+
 def test_shard_invariance_and_errors():
     """image_id_base keys the draw stream by GLOBAL image id: a shard reproduces its slice of the full batch."""
     mask, vertex, _ = synth.make_batch(4, vn=5, frac=0.05, sigma=0.05, seed=66, h=96, w=128)

@@ -25,10 +25,12 @@ from pvnet_b200 import ransac_voting_gpu as pv, synth
 dev = "cuda:0"
 mask, vertex, _ = synth.make_batch(32, vn=9, frac=0.03, sigma=0.05, seed=1234)
 tm, tv = torch.from_numpy(mask).to(dev), synth.as_net_output(vertex, device=dev)
+HN = int(os.environ.get("K3_HN", "512"))
+VAR = os.environ.get("K3_VAR")
 for thresh in (0.999,):
     for abl in [int(v) for v in (sys.argv[1:] or [0, 1, 4, 5, 8, 13, 2, 3, 15])]:
         os.environ["PVV_K3_ABLATE"] = str(abl)
         st = []
         for i in range(14):
-            pv.ransac_voting_layer_v3(tm, tv, 512, thresh, seed=0, stage_ms=st)
-        print(f"hotvar {HV} thresh {thresh} ablate {abl:2d}: count {float(np.median([s['count'] for s in st[3:]])):.4f} ms", flush=True)
+            pv.ransac_voting_layer_v3(tm, tv, HN, thresh, seed=0, stage_ms=st, k3_variant=int(VAR) if VAR else None)
+        print(f"hn {HN} variant {VAR} hotvar {HV} thresh {thresh} ablate {abl:2d}: count {float(np.median([s['count'] for s in st[3:]])):.4f} ms", flush=True)
