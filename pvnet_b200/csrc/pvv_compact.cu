@@ -135,6 +135,7 @@ template <int DT>
 static void launch_tile_count(const pvv_dims &d, const void *mask, const pvv_ws &ws, dim3 grid, cudaStream_t st)
 {
     const bool linear = d.ms[2] == 1 && d.ms[1] == d.w;
+    pvv_hint_carveout(linear ? (const void *)k_tile_count<DT, true> : (const void *)k_tile_count<DT, false>);
     if (linear) k_tile_count<DT, true><<<grid, kThreads, 0, st>>>(d, mask, ws);
     else k_tile_count<DT, false><<<grid, kThreads, 0, st>>>(d, mask, ws);
 }

@@ -254,10 +254,12 @@ thread_local worker_pool t_pool;
 // address space) to the same place in the device image of the tensor.  One warp per row; coalesced 4-byte loads, 12 per
 // lane in flight.  Measured (tools/crop_probe.cu, 32 images of configs[1]): 43 GB/s over PCIe for such spans, against
 // 38 GB/s for bounding-box copies by the copy engines (which also move 1.5x the bytes: boxes, not spans) and 13 - 20 GB/s
-// for the per-pixel gather in the scatter kernel.  One 64-thread CTA per SM with <= 32 registers and no shared memory:
-// the tensor-pipe counting kernel's CTA leaves 4096 registers and 2 KB of shared memory on its SM, room for exactly two of
-// these (one per voting stream), so the spans of sub-batch s + 1 cross the bus while sub-batch s is being voted on -- and a
-// counting kernel that arrives while they are resident still finds its 61440 registers.
+// for the per-pixel gather in the scatter kernel.  64-thread CTAs with <= 32 registers and no shared memory: the
+// tensor-pipe counting kernel's CTA leaves 4096 registers and 2 KB of shared memory on its SM, room for two of these, so the
+// spans of sub-batch s + 1 cross the bus while sub-batch s is being voted on -- and a counting kernel that arrives while
+// they are resident still finds its 61440 registers (all kernels ask for the same shared-memory carve-out: pvv_internal.cuh).
+// The overlap has a price: kernels that run beside a pull take about twice as long (the outstanding reads of host memory sit
+// in the L2's request queues for microseconds), so the pulls have a stream of their own and run one at a time.
 template <bool PLANAR, bool VEC4>
 __global__ void __launch_bounds__(64, 32) k_pull_spans(const uint8_t *__restrict__ mask, const float *__restrict__ src,
                                                        float *__restrict__ dst, int b, int h, int w, int vn, long long vs0,
@@ -345,14 +347,15 @@ __global__ void __launch_bounds__(64, 32) k_pull_spans(const uint8_t *__restrict
 // costs ~0.2 ms, a tenth of a call).  A host call synchronises before it returns, so they are idle between calls.
 struct host_streams {
     int dev = -1, sms = 148;
-    cudaStream_t cs = nullptr, ks[2] = {nullptr, nullptr};
-    cudaEvent_t ev[PVV_HOST_MAX_SUB + 3] = {};
+    cudaStream_t cs = nullptr, ps = nullptr, ks[2] = {nullptr, nullptr};   // copies, span pulls, voting (two in turn)
+    cudaEvent_t ev[2 * PVV_HOST_MAX_SUB + 3] = {};
     void drop()
     {
         for (auto &e : ev) { if (e) cudaEventDestroy(e); e = nullptr; }
         if (cs) cudaStreamDestroy(cs);
+        if (ps) cudaStreamDestroy(ps);
         for (auto &k : ks) { if (k) cudaStreamDestroy(k); k = nullptr; }
-        cs = nullptr; dev = -1;
+        cs = nullptr; ps = nullptr; dev = -1;
         cudaGetLastError();
     }
     bool get()
@@ -362,17 +365,12 @@ struct host_streams {
         if (d == dev) return true;
         drop();
         bool ok = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&ps, cudaStreamNonBlocking) == cudaSuccess &&
                   cudaStreamCreateWithFlags(&ks[0], cudaStreamNonBlocking) == cudaSuccess &&
                   cudaStreamCreateWithFlags(&ks[1], cudaStreamNonBlocking) == cudaSuccess;
         for (auto &e : ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
         if (!ok) { drop(); return false; }
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d);
-        // the pull kernel uses no shared memory, but it has to run beside the tensor-pipe counting kernel, whose 224 KB need
-        // the SM's largest shared-memory carve-out: ask for the same one, or its CTAs wait until that kernel has left the SM
-        cudaFuncSetAttribute(k_pull_spans<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        cudaFuncSetAttribute(k_pull_spans<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        cudaFuncSetAttribute(k_pull_spans<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        cudaGetLastError();
         dev = d;
         return true;
     }
@@ -534,11 +532,18 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
         // sub-batch s is being voted on; every sub-batch has its own workspace
         host_streams &hs = t_streams;
         bool ok = hs.get();
+        struct carveout_scope {   // every kernel launched by this thread until the end of the block: largest carve-out
+            carveout_scope() { pvv_carveout_wish() = cudaSharedmemCarveoutMaxShared; }
+            ~carveout_scope() { pvv_carveout_wish() = cudaSharedmemCarveoutDefault; }
+        } carveout;
         cudaStream_t cs = hs.cs, *ks = hs.ks;
-        cudaEvent_t *ev = hs.ev;   // [0, MAX_SUB): sub-batch copied; MAX_SUB: caller's stream; MAX_SUB + 1, + 2: voting streams
+        cudaEvent_t *ev = hs.ev;   // [0, MAX_SUB): sub-batch copied; MAX_SUB: caller's stream; MAX_SUB + 1, + 2: voting streams;
+                                   // [MAX_SUB + 3, 2 MAX_SUB + 3): spans of the sub-batch pulled
+        cudaStream_t ps = hs.ps;
         // everything the caller's stream did before (input copies above, earlier use of the workspace) comes first
         ok = ok && cudaEventRecord(ev[PVV_HOST_MAX_SUB], st) == cudaSuccess && cudaStreamWaitEvent(cs, ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess &&
-             cudaStreamWaitEvent(ks[0], ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess && cudaStreamWaitEvent(ks[1], ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess;
+             cudaStreamWaitEvent(ks[0], ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess && cudaStreamWaitEvent(ks[1], ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess &&
+             cudaStreamWaitEvent(ps, ev[PVV_HOST_MAX_SUB], 0) == cudaSuccess;
         r = PVV_OK;
         HOST_TRACE(tr, "streams ready");
 #ifdef PVV_HOST_TRACE
@@ -572,27 +577,35 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
                 staged = fg_px > 0 && span_px <= 3 * fg_px + 4096;
                 if (staged) h2d += span_px * j->vn * 8;
             }
-            ok = ok && cudaEventRecord(ev[s], cs) == cudaSuccess && cudaStreamWaitEvent(k, ev[s], 0) == cudaSuccess;
+            ok = ok && cudaEventRecord(ev[s], cs) == cudaSuccess && cudaStreamWaitEvent(staged ? ps : k, ev[s], 0) == cudaSuccess;
             if (ok && staged) {
                 const int64_t *v = j->vertex_strides;
                 float *dev_v = (float *)(base + P.o_vertex);
                 const uint8_t *dev_m = (const uint8_t *)(base + P.o_mask) + (size_t)i0 * npx;
                 const float *src_v = (const float *)P.vertex_dev + (long long)i0 * v[0];
-                const int grid = hs.sms;   // one CTA per SM: see k_pull_spans
+                // CTAs of two warps on half of the SMs: enough loads in flight to fill the bus (a quarter of the SMs is not),
+                // while the kernels of the sub-batch being voted on at the same time slow down less than with one CTA on
+                // every SM (measured, tools/host_trace.py: 74 CTAs 1.38 ms per call, 148 CTAs 1.45 ms, 32 CTAs 1.70 ms)
+                const int grid = std::max(1, hs.sms / 2);
+                pvv_hint_carveout((const void *)k_pull_spans<true, true>);      // see pvv_internal.cuh
+                pvv_hint_carveout((const void *)k_pull_spans<true, false>);
+                pvv_hint_carveout((const void *)k_pull_spans<false, false>);
                 const bool vec4 = ((v[0] | v[1] | v[3] | v[4] | ww) & 3) == 0 && (((uintptr_t)src_v | (uintptr_t)dev_v) & 15) == 0;
                 float *dst_v = dev_v + (long long)i0 * v[0];
                 if (P.crop_kind == CROP_PLANAR && vec4)
-                    k_pull_spans<true, true><<<grid, 64, 0, k>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
+                    k_pull_spans<true, true><<<grid, 64, 0, ps>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
                 else if (P.crop_kind == CROP_PLANAR)
-                    k_pull_spans<true, false><<<grid, 64, 0, k>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
+                    k_pull_spans<true, false><<<grid, 64, 0, ps>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
                 else
-                    k_pull_spans<false, false><<<grid, 64, 0, k>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
-                ok = cudaGetLastError() == cudaSuccess;
+                    k_pull_spans<false, false><<<grid, 64, 0, ps>>>(dev_m, src_v, dst_v, i1 - i0, hh, ww, j->vn, v[0], v[1], v[2], v[3], v[4]);
+                // the pulls have a stream of their own: one at a time (each saturates the bus), never queued behind a vote
+                ok = cudaGetLastError() == cudaSuccess && cudaEventRecord(ev[PVV_HOST_MAX_SUB + 3 + s], ps) == cudaSuccess &&
+                     cudaStreamWaitEvent(k, ev[PVV_HOST_MAX_SUB + 3 + s], 0) == cudaSuccess;
                 sub.vertex = dev_v;
                 for (int img = i0; img < i1; ++img) gathered[img] = 0;
             }
 #ifdef PVV_HOST_TRACE
-            cudaEventRecord(tr.gc[s], k);
+            cudaEventRecord(tr.gc[s], staged ? ps : k);
 #endif
             if (ok)
                 r = run_sub(sub, i0, i1, cov, confidence, max_iter, mean_dev, out_dev, tn_dev, status_dev + s, k,

@@ -69,9 +69,43 @@ __device__ __forceinline__ void pvv_pdl_enter()
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+// Shared-memory carve-out of the library's kernels.  The tensor-pipe counting kernel needs the SM's largest one (224 KB),
+// and an SM only changes its carve-out when it is empty: one resident CTA of a kernel that settled for a small carve-out
+// (the span-pull kernel of a host-buffer call lives for ~0.2 ms) keeps the counting kernel's CTA for that SM -- and with it
+// the whole persistent grid -- waiting (tools/coresidency_probe.cu).  Host-buffer calls, which run sub-batches side by
+// side, therefore ask for the largest carve-out in every kernel (-25 us per call, measured); device-buffer calls run one
+// chain at a time and keep the default, which is 7 us faster for them (more L1 for the compaction and pre-pass kernels).
+// The wish is per calling thread (pvv_host.cu sets it around its sub-batches); the attribute is set when it changes.
+inline int &pvv_carveout_wish()
+{
+    thread_local int wish = cudaSharedmemCarveoutDefault;
+    return wish;
+}
+inline void pvv_hint_carveout(const void *kern)
+{
+    struct seen_t { const void *fn; int dev, state; };
+    thread_local seen_t seen[48];
+    thread_local int nseen = 0;
+    const int wish = pvv_carveout_wish();
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    seen_t *slot = nullptr;
+    for (int i = 0; i < nseen; ++i)
+        if (seen[i].fn == kern && seen[i].dev == dev) { slot = &seen[i]; break; }
+    if (slot ? slot->state == wish : wish == cudaSharedmemCarveoutDefault && nseen < 48) {
+        if (!slot) { seen[nseen].fn = kern; seen[nseen].dev = dev; seen[nseen].state = wish; ++nseen; }
+        return;
+    }
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, wish);
+    cudaGetLastError();
+    if (slot) slot->state = wish;
+    else if (nseen < 48) { seen[nseen].fn = kern; seen[nseen].dev = dev; seen[nseen].state = wish; ++nseen; }
+}
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t pvv_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args)
 {
+    pvv_hint_carveout((const void *)kern);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;

@@ -13,6 +13,6 @@ ys, xs = np.nonzero(mask[0])
 print("image 0: fg", len(ys), "bbox", ys.min(), ys.max(), xs.min(), xs.max(), "bbox area / fg = %.2f" % ((ys.max() - ys.min() + 1) * (xs.max() - xs.min() + 1) / len(ys)), flush=True)
 for i in range(6):
     t0 = time.perf_counter()
-    pv.ransac_voting_layer_v3(hm, hv, 512, 0.999, seed=1)
+    pv.ransac_voting_layer_v3(hm, hv, int(os.environ.get('TRACE_HN', '512')), 0.999, seed=1)
     torch.cuda.synchronize()
     print("call %d: %.3f ms" % (i, (time.perf_counter() - t0) * 1e3), file=sys.stderr, flush=True)
