@@ -184,18 +184,25 @@ int pvv_cov(const pvv_job *job, const float *mean, float *out_cov, const pvv_deb
  * Host-buffer variants (the reference-facing call with HOST memory): mask / vertex / idxs / selection / mean are host
  * pointers, outputs are host pointers; copies are issued on job->stream and the call returns after the result has
  * landed (it synchronises the stream).  `workspace` is still device memory, sized by pvv_workspace_bytes_host().
- * Pinned (cudaHostAlloc / cudaHostRegister) inputs are read in place over PCIe: only the mask and the foreground
- * vertex vectors cross the bus.  Pageable inputs are staged with a full copy.
+ * Pinned (cudaHostAlloc / cudaHostRegister) inputs are read in place over PCIe: only one byte per mask pixel and the
+ * foreground of the vertex tensor cross the bus (contiguous masks are prepared by host worker threads -- see
+ * pvv_set_host_workers -- and the foreground row spans of a [b,h,w,vn,2] view of an NCHW tensor, or of a contiguous
+ * [b,h,w,vn,2] tensor, are staged in the workspace by a pull kernel; any other layout, and sparse foreground, is gathered
+ * pixel by pixel by the compaction kernel).  Pageable inputs are staged with a full copy.  The workspace of a pinned call
+ * holds a device image of the vertex tensor (same strides, only the foreground spans are written).
  * h2d_bytes / d2h_bytes (optional) receive the bytes that crossed the bus.
  */
 size_t pvv_workspace_bytes_host(const pvv_job *job);
 /*
- * Host worker threads the host-buffer entry points may use to narrow a wide (int64 / int32 / float32) contiguous mask to one
- * byte per pixel before it crosses PCIe (3x fewer bytes for the int64 mask torch.argmax produces).  n < 0 (default):
- * half the hardware threads, at most 16; n = 0: no narrowing, the mask is copied as it is; n > 0: that many.  Narrowing
- * only pays when a rank has the host cores to itself: measured on the B200 boxes, 8 workers give +20 % at 1 rank and lose
- * at 2 and 8 ranks per host, so a launcher that runs several ranks per box should divide the cores or pass 0 (the Python
- * mirror does that from LOCAL_WORLD_SIZE).  Process-wide setting, may be changed at any time; returns the previous value.
+ * Host worker threads of the host-buffer entry points.  They walk a contiguous mask piece by piece: a wide (int64 / int32 /
+ * float32) mask is narrowed to one byte per pixel before it crosses PCIe (AVX-512 where the CPU has it; 8x fewer bytes for
+ * the int64 mask torch.argmax produces), and the foreground extent of the rows is measured, which decides between the span
+ * pull and the per-pixel gather.  n < 0 (default): half the hardware threads, at most 16; n = 0: no host preparation, the
+ * mask is copied as it is and the foreground is gathered pixel by pixel; n > 0: that many.  The workers are parked threads
+ * of the calling thread (created on its first call).  Measured on the B200 boxes (16 / 32 hardware threads): worth it from
+ * 3 workers per rank upwards; a launcher that runs several ranks per box should divide the hardware threads between them
+ * (the Python mirror does that from LOCAL_WORLD_SIZE).  Process-wide setting, may be changed at any time; returns the
+ * previous value.
  */
 int pvv_set_host_workers(int n);
 int pvv_v3_host(const pvv_job *job, float confidence, int max_iter, float *out_kp_host,

@@ -91,12 +91,18 @@ def lib():
     L.pvv_probe_tflops.restype = C.c_double
     L.pvv_version.restype = C.c_char_p
     L.pvv_set_host_workers.argtypes = [I]
-    # several ranks on one host (torchrun sets LOCAL_WORLD_SIZE): divide the host cores between them; with fewer than 8
-    # workers per rank narrowing the mask on the host is slower than copying it wide (profiles/r02_e2e_host_threads.log)
+    # several ranks on one host (torchrun sets LOCAL_WORLD_SIZE): the ranks share the host's hardware threads.  Measured
+    # with the AVX-512 narrowing (round 2, `e2e` of bench.py, total images/s, off -> on): 2 ranks x 8 workers 25.3 k -> 37.5 k
+    # (6: 35.1 k, 4: 29.2 k, 2: 17.1 k), 4 ranks x 4 workers 31.4 k -> 44.0 k (3: 41.0 k), 8 ranks x 4 workers 51.0 k -> 51.6 k
+    # (2: 44.9 k).  So: every rank takes its share of ALL hardware threads, and prepares on the host when that is >= 3.
+    # PVV_HOST_WORKERS overrides (0 = off).
     ranks = int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1)
-    if ranks > 1:
-        per_rank = ((os.cpu_count() or 2) // 2) // ranks
-        L.pvv_set_host_workers(per_rank if per_rank >= 8 else 0)
+    forced = os.environ.get("PVV_HOST_WORKERS")
+    if forced is not None:
+        L.pvv_set_host_workers(int(forced))
+    elif ranks > 1:
+        per_rank = (os.cpu_count() or 2) // ranks
+        L.pvv_set_host_workers(min(per_rank, 16) if per_rank >= 3 else 0)
     _lib = L
     return L
 
