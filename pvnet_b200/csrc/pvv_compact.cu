@@ -250,6 +250,8 @@ __global__ void __launch_bounds__(kThreads) k_scan(pvv_dims d, pvv_ws ws)
     for (int i = threadIdx.x; i < d.b; i += kThreads) {
         const int n = ws.tn[i], cs = ws.chunk_start[i], rk = ws.img_rank[i];
         const int off0 = (int)ws.img_off[i];
+        PVV_CHECK(off0 >= 0 && (long long)off0 + n <= ws.cap && (off0 % PVV_POOL_ALIGN) == 0);
+        PVV_CHECK(cs >= 0 && cs + (n + PVV_CHUNK_PX - 1) / PVV_CHUNK_PX <= ws.cap / PVV_CHUNK_PX + d.b + 1);
         for (int p0 = 0, c = 0; p0 < n; p0 += PVV_CHUNK_PX, ++c)
             *reinterpret_cast<int3 *>(&ws.chunk_tab[cs + c]) =
                 make_int3(i, off0 + p0, min(PVV_CHUNK_PX, n - p0) | (c == 0 ? 1 << 15 : 0) | (rk << 16));
@@ -305,6 +307,7 @@ __global__ void __launch_bounds__(kThreads) k_scatter(pvv_dims d, const float *v
         // keypoints of its pixel
         const int vi0 = blockIdx.z * kKpPerCta, vi1 = min(d.vn, vi0 + kKpPerCta);
         for (int j = threadIdx.x; j < total; j += kThreads) {
+            PVV_CHECK(base + j >= 0 && base + j < ws.cap);
             if (blockIdx.z == 0) {
                 ws.pix_xy[base + j] = s_xy[j];
                 // the middle pixel of a voting chunk is the origin of that chunk's local frame in K3

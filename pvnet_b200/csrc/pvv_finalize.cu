@@ -269,6 +269,7 @@ __global__ void k_export_counts(pvv_dims d, pvv_ws ws, int32_t *counts_out)
     const long long r = e / d.vn;
     const int hi = (int)(r % d.hn);
     const int img = (int)(r / d.hn);
+    PVV_CHECK(img < d.b && vi < d.vn && hi < d.hn);
     counts_out[e] = ws.counts[((long long)img * d.vn + vi) * ws.hn_pad + hi];
 }
 

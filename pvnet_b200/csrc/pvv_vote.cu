@@ -213,6 +213,8 @@ __device__ __forceinline__ k3_item k3_decode_item(const pvv_dims &d, const pvv_w
     it.p0 = e.y + sub * span;
     it.n = max(0, min(span, (e.z & 0x7fff) - sub * span));  // 0: the chunk ends before this range (an empty item)
     // frame origin = the chunk's middle pixel: halves the extent P of the chunk around it, and with it the band
+    PVV_CHECK(ci >= 0 && ci < ws.chunk_start[d.b] && e.x >= 0 && e.x < d.b && e.y >= 0 && (long long)e.y + (e.z & 0x7fff) <= ws.cap &&
+              (e.z & 0x7fff) >= 1 && (e.z & 0x7fff) <= PVV_CHUNK_PX);
     it.ox = (int)((uint32_t)e.w & 0xffffu);
     it.oy = (int)((uint32_t)e.w >> 16);
     it.off = 0;   // p0 is a pool index already
@@ -392,6 +394,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
         // exact decision for one in-band test, correcting the provisional count (sign bit of m clear = counted)
         auto resolve = [&](int hbase, int t, int k, int j, float m) {
             const int h = hbase + k * HT + t;
+            PVV_CHECK(h >= 0 && h < d.hn && j >= 0 && j < n && k < H && t < HT);
             const float2 hv = ws.hyp[row + h];
             const float2 dir = rDir[j];
             const uint32_t xy = rXY[j];
@@ -500,6 +503,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_count(pvv_dims d, pvv_ws ws, 
                             const int grp = __ffs(m_k) - 1;
                             m_k &= m_k - 1;
                             if (q < K3_QCAP) {
+                                PVV_CHECK(q >= 0 && grp < PVV_CHUNK_PX / K3_GROUP);
                                 s_q[q] = ((uint32_t)grp << 16) | ((uint32_t)k << 8) | (uint32_t)ht;
                             } else {  // queue full (pathological inputs): resolve in line
                                 const float4 hl = make_float4(hx[k], hy[k], T[k], 0.f);

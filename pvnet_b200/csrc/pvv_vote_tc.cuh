@@ -542,6 +542,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 if (T.last) {  // the row's last unit: one global add per hypothesis, and the buffer is clean for its next row
                     for (int hl = ptid; hl < T.hcount; hl += TC_PRODS) {
                         const int c = R.cnt[hl];
+                        PVV_CHECK(T.cnt_row >= 0 && T.cnt_row + hl < (long long)d.b * d.vn * ws.hn_pad && c <= d.max_num + PVV_CHUNK_PX);
                         if (c) { atomicAdd(&ws.counts[T.cnt_row + hl], c); R.cnt[hl] = 0; }
                     }
                 }
