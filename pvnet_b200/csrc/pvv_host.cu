@@ -487,6 +487,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
         const int rpp = std::max(1, (int)(((size_t)1 << 16) / (size_t)j->w));    // rows per piece
         const int ppi = (j->h + rpp - 1) / rpp;                                  // pieces per image
         int img_lo[PVV_HOST_MAX_SUB + 1];
+        // equal sub-batches: tapered splits (a small first and last one) and 5 - 8 sub-batches all measured slower
         for (int s = 0; s <= nsub; ++s) img_lo[s] = (int)((long long)j->b * s / nsub);
         struct piece_info { long long count, span; };
         std::vector<piece_info> pieces((size_t)j->b * ppi);
