@@ -258,6 +258,17 @@ int pvv_voting_for_hypothesis_vanishing_point(const float *direct, const float *
 int pvv_uncertainty_pnp(const void *pts2d, const void *weights_or_cov, int mode, int f64_inputs, const double *pts3d,
                         int64_t pts3d_image_stride, const double *camera, int64_t camera_image_stride, int b, int vn,
                         double *out_pose, double *out_info, void *stream);
+/*
+ * The same with a stop rule.  pvv_uncertainty_pnp runs the Levenberg-Marquardt iteration to convergence (the minimiser
+ * Ceres approaches).  The reference sets no solver options (uncertainty_pnp.cpp:85-90), so Ceres stops at its defaults: 50
+ * iterations (unsuccessful steps included) or an accepted step that lowers the cost by less than 1e-6 x cost.  Passing
+ * max_iter = 50, function_tolerance = 1e-6 applies those two tests to this solver's own iteration; <= 0 switches a test
+ * off.  The damping schedule is this library's, not Ceres' trust-region policy (Ceres itself cannot be built or linked in
+ * this environment), so the early-stopped pose is close to, not identical with, what Ceres returns.
+ */
+int pvv_uncertainty_pnp_stop(const void *pts2d, const void *weights_or_cov, int mode, int f64_inputs, const double *pts3d,
+                             int64_t pts3d_image_stride, const double *camera, int64_t camera_image_stride, int b, int vn,
+                             int max_iter, double function_tolerance, double *out_pose, double *out_info, void *stream);
 
 /* The library's draw streams, materialised (for feeding the oracle / the reference wrapper the same draws). */
 int pvv_make_idxs(uint64_t seed, int64_t image_id_base, int b, int hn_total, int vn, const int32_t *tn /*device [b]*/,

@@ -44,7 +44,7 @@ SYMBOLS = [
     "pvv_workspace_bytes", "pvv_default_pool_capacity", "pvv_v3", "pvv_v3_noalloc", "pvv_static_workspace_bytes", "pvv_v5", "pvv_hypotheses", "pvv_motion", "pvv_cov", "pvv_workspace_bytes_host", "pvv_set_host_workers",
     "pvv_v3_host", "pvv_cov_host", "pvv_generate_hypothesis", "pvv_voting_for_hypothesis", "pvv_vote_counts",
     "pvv_generate_hypothesis_vanishing_point", "pvv_voting_for_hypothesis_vanishing_point",
-    "pvv_uncertainty_pnp", "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_probe_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
+    "pvv_uncertainty_pnp", "pvv_uncertainty_pnp_stop", "pvv_make_idxs", "pvv_make_selection", "pvv_fp32_peak_tflops", "pvv_probe_tflops", "pvv_last_launch_count", "pvv_last_cuda_error",
     "pvv_version",
 ]
 
@@ -83,6 +83,7 @@ def lib():
     L.pvv_voting_for_hypothesis_vanishing_point.argtypes = [V, V, V, V, I, I, I, F, V]
     L.pvv_vote_counts.argtypes = [V, V, V, I, I, I, F, V, V]
     L.pvv_uncertainty_pnp.argtypes = [V, V, I, I, V, C.c_int64, V, C.c_int64, I, I, V, V, V]
+    L.pvv_uncertainty_pnp_stop.argtypes = [V, V, I, I, V, C.c_int64, V, C.c_int64, I, I, I, C.c_double, V, V, V]
     L.pvv_make_idxs.argtypes = [C.c_uint64, C.c_int64, I, I, I, V, V, V]
     L.pvv_make_selection.argtypes = [C.c_uint64, C.c_int64, I, I, I, V, V]
     L.pvv_fp32_peak_tflops.argtypes = [I, V]

@@ -140,7 +140,8 @@ template <typename T>
 __global__ void __launch_bounds__(128) k_uncertainty_pnp(const T *__restrict__ pts2d, const T *__restrict__ w_or_cov,
                                                          int mode, const double *__restrict__ pts3d, long long pts3d_stride,
                                                          const double *__restrict__ Kmat, long long k_stride, int b, int vn,
-                                                         double *__restrict__ out_pose, double *__restrict__ out_info)
+                                                         double *__restrict__ out_pose, double *__restrict__ out_info,
+                                                         int max_iter, double function_tolerance)
 {
     const int img = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (img >= b) return;
@@ -249,7 +250,13 @@ __global__ void __launch_bounds__(128) k_uncertainty_pnp(const T *__restrict__ p
     };
     double cost = cost_of(R, t), lambda = 1e-4;
     int it = 0, status = ok ? 0 : 2;  // 0 converged, 1 iteration cap, 2 no usable start (pose left at the fallback)
-    for (; ok && it < kPnpMaxIter; ++it) {
+    // Stop rule.  Default (max_iter <= 0, function_tolerance <= 0): to convergence.  With the reference's solver options
+    // (uncertainty_pnp.cpp:85-90 sets none, so Ceres' defaults hold: 50 iterations, function tolerance 1e-6) the loop ends
+    // after max_iter damping trials or when an accepted step lowers the cost by less than function_tolerance x cost -- the
+    // test Ceres applies -- which is what makes "the pose the reference returns" differ from the minimiser on flat problems.
+    const int iter_cap = max_iter > 0 ? min(max_iter, kPnpMaxIter) : kPnpMaxIter;
+    int trials = 0;
+    for (; ok && it < iter_cap; ++it) {
         double H[21], g[6];
 #pragma unroll
         for (int i = 0; i < 21; ++i) H[i] = 0.0;
@@ -276,6 +283,7 @@ __global__ void __launch_bounds__(128) k_uncertainty_pnp(const T *__restrict__ p
         if (!(gmax > 1e-14 * (1.0 + cost))) break;  // stationary
         bool improved = false;
         for (int tries = 0; tries < 12 && !improved; ++tries) {
+            if (max_iter > 0 && trials++ >= max_iter) { status = 1; goto done; }   // Ceres counts unsuccessful steps too
             double A[6][6], d[6];
             int q = 0;
 #pragma unroll
@@ -301,6 +309,7 @@ __global__ void __launch_bounds__(128) k_uncertainty_pnp(const T *__restrict__ p
                     lambda = fmax(lambda / 3.0, 1e-12);
                     improved = true;
                     if (rel < 1e-15 || step2 < 1e-26) { ++it; goto done; }
+                    if (function_tolerance > 0.0 && rel < function_tolerance) { ++it; goto done; }
                     continue;
                 }
             }
@@ -309,7 +318,7 @@ __global__ void __launch_bounds__(128) k_uncertainty_pnp(const T *__restrict__ p
         if (!improved) break;  // no downhill step at any damping: at the minimum to working precision
     }
 done:
-    if (status == 0 && it >= kPnpMaxIter) status = 1;
+    if (status == 0 && it >= iter_cap) status = 1;
     if (lane == 0) {
         double *o = out_pose + (long long)img * 12;
         o[0] = R[0]; o[1] = R[1]; o[2] = R[2]; o[3] = t[0];
@@ -326,6 +335,15 @@ extern "C" int pvv_uncertainty_pnp(const void *pts2d, const void *weights_or_cov
                                    int64_t camera_image_stride, int b, int vn, double *out_pose, double *out_info,
                                    void *stream)
 {
+    return pvv_uncertainty_pnp_stop(pts2d, weights_or_cov, mode, f64_inputs, pts3d, pts3d_image_stride, camera,
+                                    camera_image_stride, b, vn, 0, 0.0, out_pose, out_info, stream);
+}
+
+extern "C" int pvv_uncertainty_pnp_stop(const void *pts2d, const void *weights_or_cov, int mode, int f64_inputs,
+                                        const double *pts3d, int64_t pts3d_image_stride, const double *camera,
+                                        int64_t camera_image_stride, int b, int vn, int max_iter, double function_tolerance,
+                                        double *out_pose, double *out_info, void *stream)
+{
     if (!pts2d || !weights_or_cov || !pts3d || !camera || !out_pose || b < 0 || vn < 4 || (mode != 0 && mode != 1))
         return PVV_ERR_INVALID;
     if (vn > PVV_MAX_VN) return PVV_ERR_UNSUPPORTED;
@@ -334,10 +352,12 @@ extern "C" int pvv_uncertainty_pnp(const void *pts2d, const void *weights_or_cov
     if (f64_inputs)
         k_uncertainty_pnp<double><<<grid, 128, 0, (cudaStream_t)stream>>>((const double *)pts2d, (const double *)weights_or_cov,
                                                                           mode, pts3d, pts3d_image_stride, camera,
-                                                                          camera_image_stride, b, vn, out_pose, out_info);
+                                                                          camera_image_stride, b, vn, out_pose, out_info,
+                                                                          max_iter, function_tolerance);
     else
         k_uncertainty_pnp<float><<<grid, 128, 0, (cudaStream_t)stream>>>((const float *)pts2d, (const float *)weights_or_cov,
                                                                          mode, pts3d, pts3d_image_stride, camera,
-                                                                         camera_image_stride, b, vn, out_pose, out_info);
+                                                                         camera_image_stride, b, vn, out_pose, out_info,
+                                                                         max_iter, function_tolerance);
     return cudaGetLastError() == cudaSuccess ? PVV_OK : PVV_ERR_CUDA;
 }

@@ -21,11 +21,15 @@ def _dev_f64(x, device):
     return torch.as_tensor(np.asarray(x, np.float64) if not isinstance(x, torch.Tensor) else x).to(device=device, dtype=torch.float64).contiguous()
 
 
-def uncertainty_pnp_batch(points_2d, cov_or_weights, points_3d, camera_matrix, weights=False, return_info=False):
+CERES_DEFAULT_STOP = (50, 1e-6)   # max_num_iterations, function_tolerance: what the reference's Solver::Options() holds
+
+
+def uncertainty_pnp_batch(points_2d, cov_or_weights, points_3d, camera_matrix, weights=False, return_info=False, stop=None):
     """points_2d [b,vn,2], cov_or_weights [b,vn,2,2] covariances (weights=False: evaluate_uncertainty's conversion is done
     on the device) or [b,vn,3] (wxx,wxy,wyy; weights=True), float32 or float64 CUDA tensors; points_3d [vn,3] or [b,vn,3];
     camera_matrix [3,3] or [b,3,3].  Returns poses [b,3,4] float64 on the same device (+ info [b,3]: cost, iterations,
-    status)."""
+    status).  `stop` = (max_iter, function_tolerance), e.g. CERES_DEFAULT_STOP, ends the iteration the way the reference's
+    solver options do (uncertainty_pnp.cpp:85-90); None runs to convergence."""
     if not torch.cuda.is_available():
         raise RuntimeError("pvnet_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     if not (isinstance(points_2d, torch.Tensor) and points_2d.is_cuda):
@@ -47,9 +51,11 @@ def uncertainty_pnp_batch(points_2d, cov_or_weights, points_3d, camera_matrix, w
     pose = torch.empty((b, 3, 4), dtype=torch.float64, device=dev)
     info = torch.empty((b, 3), dtype=torch.float64, device=dev)
     with torch.cuda.device(dev):
-        st = _lib.lib().pvv_uncertainty_pnp(p2.data_ptr(), cw.data_ptr(), 1 if weights else 0, 1 if f64 else 0, p3.data_ptr(),
-                                            p3_stride, K.data_ptr(), k_stride, b, vn, pose.data_ptr(), info.data_ptr(),
-                                            C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        mi, ft = (int(stop[0]), float(stop[1])) if stop is not None else (0, 0.0)
+        st = _lib.lib().pvv_uncertainty_pnp_stop(p2.data_ptr(), cw.data_ptr(), 1 if weights else 0, 1 if f64 else 0,
+                                                 p3.data_ptr(), p3_stride, K.data_ptr(), k_stride, b, vn, mi, ft,
+                                                 pose.data_ptr(), info.data_ptr(),
+                                                 C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
     _lib.check(st, "pvv_uncertainty_pnp")
     return (pose, info) if return_info else pose
 

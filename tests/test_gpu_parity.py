@@ -700,6 +700,29 @@ def test_uncertainty_pnp_is_stationary_for_the_reference_cost():
         assert float(r @ r) <= float(rw @ rw) * (1 + 1e-9) + 1e-12
 
 
+def test_uncertainty_pnp_stop_rule():
+    """N2: the reference sets no solver options (uncertainty_pnp.cpp:85-90), so Ceres stops after 50 iterations or when an
+    accepted step lowers the cost by less than 1e-6 x cost.  With that rule the solver stops earlier than at convergence and
+    returns a pose whose cost is within 1e-5 relative (+1e-12) of the minimum; one trial = exactly one step."""
+    from pvnet_b200 import uncertainty_pnp as up
+    rng = np.random.default_rng(99)
+    b, pn = 16, 9
+    cases = [synth.pnp_case(rng, pn, noise=2.0) for _ in range(b)]
+    K = cases[0][0]
+    Xs = np.stack([c[1] for c in cases])
+    x = torch.from_numpy(np.stack([c[3] for c in cases])).to(DEV)
+    cov = torch.from_numpy(np.stack([c[4] for c in cases]).astype(np.float64)).to(DEV)
+    full, info_f = up.uncertainty_pnp_batch(x, cov, Xs, K, return_info=True)
+    ceres, info_c = up.uncertainty_pnp_batch(x, cov, Xs, K, return_info=True, stop=up.CERES_DEFAULT_STOP)
+    one, info_1 = up.uncertainty_pnp_batch(x, cov, Xs, K, return_info=True, stop=(1, 0.0))
+    info_f, info_c, info_1 = info_f.cpu().numpy(), info_c.cpu().numpy(), info_1.cpu().numpy()
+    assert np.all(info_f[:, 2] == 0) and np.all(info_c[:, 2] == 0)
+    assert np.all(info_c[:, 1] <= info_f[:, 1]) and np.any(info_c[:, 1] < info_f[:, 1])        # stops earlier
+    assert np.all(info_c[:, 0] <= info_f[:, 0] * (1 + 1e-5) + 1e-12) and np.all(info_c[:, 0] >= info_f[:, 0] * (1 - 1e-12))
+    np.testing.assert_allclose(ceres.cpu().numpy(), full.cpu().numpy(), atol=5e-3)              # close to, not at, the minimiser
+    assert np.all(info_1[:, 1] <= 1) and np.all(info_1[:, 0] >= info_c[:, 0])
+
+
 def test_voting_to_pose_pipeline():
     """mask + vertex field -> v3 keypoints -> covariances -> uncertainty PnP, all on the device: the recovered pose
     reprojects the object's keypoints onto the voted ones."""
