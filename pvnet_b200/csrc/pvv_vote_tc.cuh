@@ -102,6 +102,16 @@ struct tc_stage {
                                       // of a pixel of the unit from it: |h - centre| + uext bounds ||h - pixel||
     int qn, stop, mbn, nbn, n, hcount, row, last;   // last: the row ends with this unit (its counts are flushed)
 };
+// -DPVV_TC_PROF: cycle stamps of CTA 0's first units, per role, printed when the kernel ends (development builds only)
+#ifdef PVV_TC_PROF
+#define TC_PROF_UNITS 48
+#define TC_PROF_SLOTS 20
+__device__ long long g_tc_prof[TC_PROF_UNITS][TC_PROF_SLOTS];
+#define TC_STAMP(k, slot) do { if (blockIdx.x == 0 && (k) < TC_PROF_UNITS) g_tc_prof[(k)][(slot)] = clock64(); } while (0)
+#else
+#define TC_STAMP(k, slot) ((void)0)
+#endif
+
 struct tc_smem {
     tc_row rows[TC_ROWS];
     tc_stage st[TC_STAGES];
@@ -317,19 +327,31 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
         for (uint32_t k = 0;; ++k) {
             const uint32_t s = k % TC_STAGES;
             tc_stage &T = S.st[s];
+            if (tid == 0) TC_STAMP(k, 8);
             tc_bar_wait(&S.bar_ab[s], (k / TC_STAGES) & 1u);
             if (T.stop) break;
+            if (tid == 0) TC_STAMP(k, 9);
             const int mbn = T.mbn, nbn = T.nbn, hcount = T.hcount;
             const float ext = T.ext, ucx = T.ucx, ucy = T.ucy, uext = T.uext;
             tc_row &R = S.rows[T.row];
             uint32_t dmask = 0u;  // bit mb*4 + nb*2 + g: flagged 16-pixel group of this thread's hypothesis in M-block mb
             const int abl = K3_ABLV;
             uint32_t v0[32], v1[32];
+#ifdef PVV_TC_PROF
+            long long pf_wait = 0, pf_ld = 0, pf_t;
+#define TC_PF_BEGIN() (pf_t = clock64())
+#define TC_PF_END(acc) (acc += clock64() - pf_t)
+#else
+#define TC_PF_BEGIN() ((void)0)
+#define TC_PF_END(acc) ((void)0)
+#endif
             auto full_wait = [&](uint32_t tt) {
+                TC_PF_BEGIN();
                 if (!(abl & 32)) tc_bar_wait(a_full + 8u * (tt & 1u), (tt >> 1) & 1u);
                 tc_fence_after();
+                TC_PF_END(pf_wait);
             };
-            auto landed = [&] { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); };
+            auto landed = [&] { TC_PF_BEGIN(); asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); TC_PF_END(pf_ld); };
             auto release = [&](uint32_t tt) {  // both groups of tile tt are in registers: its TMEM buffer is free
                 tc_fence_before();
                 if (lane0 && !(abl & 32)) tc_bar_arrive(a_empty + 8u * (tt & 1u));
@@ -394,6 +416,10 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     dmask |= dm << (mb * 4);
                 }
             }
+            if (tid == 0) TC_STAMP(k, 10);
+#ifdef PVV_TC_PROF
+            if (tid == 0 && blockIdx.x == 0 && k < TC_PROF_UNITS) { g_tc_prof[k][13] = pf_wait; g_tc_prof[k][14] = pf_ld; }
+#endif
             // queue the flagged (hypothesis, group) pairs for the producers' deferred passes: one reservation per warp
             if (K3_ABL(1)) dmask = 0u;
             const int mine = __popc(dmask);
@@ -431,6 +457,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
             }
             __syncwarp();
             if (lane == 0) tc_bar_arrive(&S.bar_done[s]);
+            if (tid == 0) TC_STAMP(k, 11);
         }
     } else {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TC_REGS_OTHER));
@@ -448,6 +475,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     tc_stage &T = S.st[s];
                     tc_bar_wait<TC_SLEEP_MMA>(&S.bar_ab[s], (k / TC_STAGES) & 1u);
                     if (T.stop) break;
+                    if (lane == 0) TC_STAMP(k, 12);
                     const int mbn = T.mbn, nbn = T.nbn;
                     const tc_row &R = S.rows[T.row];
                     tc_fence_after();
@@ -478,6 +506,13 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
             // ================= producers: operands of unit k, then the deferred passes of unit k - 2 =================
             const int ptid = tid - (TC_VOTERS + 32);
             auto pbar = [] { asm volatile("bar.sync 1, %0;" ::"n"(TC_PRODS) : "memory"); };
+            // With 7 producer warps the last one does not build operands: its first lane issues the look-ahead loads and the
+            // bulk copies of the next unit's inputs (~1500 cycles of one thread: address arithmetic, expect_tx, 3 - 4 bulk
+            // copies) while the other six build this unit's rows -- 256 pixels take two rounds with 192 threads as with 224.
+            // (Profile of CTA 0, -DPVV_TC_PROF: the staging used to sit on the critical path of thread 0, in front of its share
+            // of the rows.)  With 3 producer warps every thread is needed for the rows.
+            constexpr int SPT = PW == 7 ? TC_PRODS - 32 : 0;           // the staging thread
+            constexpr int TC_PB = PW == 7 ? TC_PRODS - 32 : TC_PRODS;  // threads that build operands: ptid < TC_PB
             unsigned long long amb_local = 0;
             const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};
 
@@ -499,6 +534,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 const tc_raw &W = S.raw[u % TC_RAWS];
                 tc_row &R = S.rows[T.row];
                 tc_bar_wait<TC_SLEEP_PROD>(&S.bar_done[s], (u / TC_STAGES) & 1u);
+                if (ptid == 0) TC_STAMP(u + 2, 6);
                 const int qtot = min(T.qn, K3_QCAP) * K3_SUB;
                 for (int idx = ptid; idx < qtot; idx += TC_PRODS) {
                     const uint32_t ent = T.q[idx / K3_SUB];
@@ -532,12 +568,14 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     }
                 }
                 pbar();
+                if (ptid == 0) TC_STAMP(u + 2, 15);
                 const int q2 = min(S.q2n, K3_QCAP);
                 for (int idx = ptid; idx < q2; idx += TC_PRODS) {
                     const uint32_t ent = S.q2[idx];
                     resolve(T, W, (int)(ent & 0xffffu), (int)(ent >> 16));
                 }
                 pbar();
+                if (ptid == 0) TC_STAMP(u + 2, 16);
                 if (ptid == 0) S.q2n = 0;
                 if (T.last) {  // the row's last unit: one global add per hypothesis, and the buffer is clean for its next row
                     for (int hl = ptid; hl < T.hcount; hl += TC_PRODS) {
@@ -584,7 +622,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
             // are rounded up to 16 bytes (the pool and a hypothesis row have that slack).
             auto stage_inputs = [&](uint32_t rg1, uint32_t k1, const int4 &e, long long off, bool new_row, int rowbuf) {
                 (void)off;
-                if (e.x >= 0 && !K3_ABL(1024) && ptid == 0) {
+                if (e.x >= 0 && !K3_ABL(1024) && ptid == SPT) {
                     const int vi = (int)rg1 / npass, hbase = ((int)rg1 % npass) * TC_PASS_H;
                     const long long pix = e.y;   // a pool index
                     const int n = e.z & 0x7fff;
@@ -602,7 +640,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 }
                 cp_async_commit();   // (the look-ahead ring of thread 0 still uses cp.async)
             };
-            if (ptid == 0) {
+            if (ptid == SPT) {
                 for (uint32_t i = 0; i < 3; ++i) fetch_entry(i, i);
                 cp_async_commit();
                 cp_async_wait_all();
@@ -619,8 +657,10 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
             for (;; ++k) {
                 const uint32_t s = k % TC_STAGES;
                 tc_stage &T = S.st[s];  // free: the deferred passes of unit k - 3 ended in the previous iteration
+                if (ptid == 0) TC_STAMP(k, 0);
                 cp_async_wait_all();
                 pbar();  // the look-ahead ring is up to date; everything of the previous iteration is complete
+                if (ptid == 0) TC_STAMP(k, 1);
                 e0 = S.ent[k & 7u];
                 const int4 e1 = S.ent[(k + 1) & 7u];
                 if (e0.x < 0) {
@@ -630,13 +670,15 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     break;
                 }
                 if (!K3_ABL(1024)) tc_bar_wait<TC_SLEEP_VOTER>(&S.bar_in[k % TC_RAWS], (k / TC_RAWS) & 1u);   // unit k's raw inputs landed
-                if (ptid == 0) { fetch_entry(3, k + 3); fetch_off(k + 2); }   // committed with the staging group below
+                if (ptid == 0) TC_STAMP(k, 2);
+                if (ptid == SPT) { fetch_entry(3, k + 3); fetch_off(k + 2); }   // committed with the staging group below
                 const long long off1 = S.off[(k + 1) & 7u];
                 uint32_t ci1, rg1;
                 unit_at(1, ci1, rg1);
                 const bool next_new_row = e1.x >= 0 && !(e1.x == e0.x && rg1 == rg);
                 const int next_rowbuf = next_new_row ? (rowbuf + 1) % TC_ROWS : rowbuf;
                 stage_inputs(rg1, k + 1, e1, off1, next_new_row, next_rowbuf);
+                if (ptid == SPT) TC_STAMP(k, 3);
                 const tc_raw &W = S.raw[k % TC_RAWS];
                 tc_row &R = S.rows[rowbuf];
                 const int vi = (int)rg / npass, hbase = ((int)rg % npass) * TC_PASS_H;
@@ -647,7 +689,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 if (new_row) {
                     // ---- a new row: frame origin = middle pixel of this chunk; hypotheses -> A rows (once per row) ----
                     ox = (int)((uint32_t)e0.w & 0xffffu); oy = (int)((uint32_t)e0.w >> 16);
-                    for (int hl = ptid; hl < mbn * 128 && !K3_ABL(64); hl += TC_PRODS) {
+                    for (int hl = ptid; hl < mbn * 128 && !K3_ABL(64) && ptid < TC_PB; hl += TC_PB) {
                         const float2 hv = hl < hcount ? R.raw[hl] : make_float2(0.f, 0.f);
                         float hx = __fsub_rn(hv.x, (float)ox), hy = __fsub_rn(hv.y, (float)oy);
                         float mm = __fadd_rn(fabsf(hx), fabsf(hy));
@@ -664,7 +706,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 // ---- pixel constants in the row's frame: FP32 (phase A) and their TF32 split as B rows ----
                 int ext = 0, uext = 0;
                 const int ucx = (int)((uint32_t)e0.w & 0xffffu) - ox, ucy = (int)((uint32_t)e0.w >> 16) - oy;  // the unit's centre
-                for (int j = ptid; j < nbn * TC_TILE_PX && !K3_ABL(256); j += TC_PRODS) {
+                for (int j = ptid; j < nbn * TC_TILE_PX && !K3_ABL(256) && ptid < TC_PB; j += TC_PB) {
                     px_consts c = never;
                     if (j < n && !K3_ABL(4)) {
                         const float4 pq = W.pq[j];
@@ -688,6 +730,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                     T.B[0][2 * j + 1] = make_uint4(ph, pl, ph, qh);
                     T.B[1][2 * j + 1] = make_uint4(ql, qh, rh, rl);
                 }
+                if (ptid == 0) TC_STAMP(k, 4);
                 ext = __reduce_max_sync(0xffffffffu, ext);
                 uext = __reduce_max_sync(0xffffffffu, uext);
                 if (lane == 0 && ext) { atomicMax(&S.ext, ext); atomicMax(&S.uext, uext); }
@@ -702,8 +745,10 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 }
                 __syncwarp();
                 if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
+                if (ptid == 0) TC_STAMP(k, 5);
                 // ---- deferred passes of the unit the voters finished last ----
                 if (k >= 2 && !K3_ABL(512)) deferred(k - 2);
+                if (ptid == 0) TC_STAMP(k, 7);
                 new_row = next_new_row; rowbuf = next_rowbuf; ci = ci1; rg = rg1;
             }
             // k units were published (0 .. k-1): finish the deferred passes of the last two
@@ -715,6 +760,17 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
     }
     tc_fence_before();
     __syncthreads();
+#ifdef PVV_TC_PROF
+    if (blockIdx.x == 0 && tid == 0) {
+        const long long t0 = g_tc_prof[0][0];
+        printf("unit: P start | pbar | raw in | staged next | B built | ab arrived | done[k-2] seen | deferred end || V wait ab | V got ab | V votes end | V done || M got ab || V cycles in full_wait | in wait::ld\n");
+        for (int u = 0; u < TC_PROF_UNITS; ++u) {
+            printf("%3d:", u);
+            for (int q = 0; q < 13; ++q) printf(" %7lld", g_tc_prof[u][q] ? g_tc_prof[u][q] - t0 : -1LL);
+            printf(" | %6lld %6lld | A end %7lld B end %7lld\n", g_tc_prof[u][13], g_tc_prof[u][14], g_tc_prof[u][15] - t0, g_tc_prof[u][16] - t0);
+        }
+    }
+#endif
     if (warp == TC_MMA_WARP)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_TMEM_COLS));
 }
