@@ -310,8 +310,7 @@ __global__ void __launch_bounds__(64, 32) k_pull_spans(const uint8_t *__restrict
                         for (int k = 0; k < 4; ++k)
                             if (p0 + k < planes) *reinterpret_cast<float4 *>(db + po[k] + xs) = v[k];
                     }
-                    continue;
-                }
+                } else
                 for (int xs = first & ~31; xs <= last; xs += 64) {
                     const int xa = xs + lane, xb = xa + 32;
                     const bool oka = xa >= first && xa <= last, okb = xb <= last;   // xb >= first always
