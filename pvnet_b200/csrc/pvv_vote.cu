@@ -713,8 +713,9 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
         e = cudaGetLastError();
     }
     else if (variant == 7 || variant == 8 || variant == 9) {
-        // producer warps by how often the deferred passes run (PVV_K3_VARIANT 8 / 9 force 7 / 3)
-        const bool few = variant == 9 || (variant == 7 && d.thresh <= 0.995f);
+        // 7 producer warps (variant 9 forces 3: until the seventh warp's lane took over the staging of the next unit's inputs
+        // they were 4 % faster where the deferred passes are rare, thresh <= 0.995; now 7 win there too: 293 against 299 us)
+        const bool few = variant == 9;
         e = few ? launch_count_tc<3>(d, ws, bc, sms, st) : launch_count_tc<7>(d, ws, bc, sms, st);
     }
     else if (variant == 10) e = launch_count_tc2<4>(d, ws, bc, sms, st, launches);

@@ -422,37 +422,29 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
 #endif
             // queue the flagged (hypothesis, group) pairs for the producers' deferred passes: one reservation per warp
             if (K3_ABL(1)) dmask = 0u;
-            const int mine = __popc(dmask);
-            if (__any_sync(0xffffffffu, mine)) {
-                int incl = mine;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int up = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += up;
-                }
-                int base = 0;
-                if (lane == 31) base = atomicAdd(&T.qn, incl);
-                int q = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
-                while (dmask) {
-                    const int bitn = __ffs(dmask) - 1;
-                    dmask &= dmask - 1;
-                    const int hl = (bitn >> 2) * 128 + q4 * 32 + lane;
-                    const int grp = ((bitn >> 1) & 1) * 8 + cq * 2 + (bitn & 1);  // 16-pixel group within the chunk
-                    if (q < K3_QCAP) {
-                        T.q[q] = ((uint32_t)grp << 16) | (uint32_t)hl;
-                    } else {  // queue full (pathological inputs): the reference's own decision for the whole group, in line
-                        const tc_raw &W = S.raw[k % TC_RAWS];
-                        const float2 hv = R.raw[hl];
-                        int c = 0;
-                        for (int j = grp * K3_GROUP; j < min(T.n, (grp + 1) * K3_GROUP); ++j) {
-                            const float2 dir = W.dir[j];
-                            const uint32_t xy = W.xy[j];
-                            c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
-                                                hv.x, hv.y, d.thresh) ? 1 : 0;
-                        }
-                        if (c) atomicAdd(&R.cnt[hl], c);
+            // (a lane with flagged groups reserves its queue slots itself: ~3.5 entries per warp and unit, so a handful of
+            // shared-memory atomics cost less than the warp-wide prefix sum + one atomic they replace -- every voter warp
+            // runs this tail at the same moment, so its latency is dead time for the whole SM.  Pulling the next unit's first
+            // tile in front of this tail, to overlap the two, was measured slower: 324 against 308 us)
+            while (dmask) {
+                const int bitn = __ffs(dmask) - 1;
+                dmask &= dmask - 1;
+                const int hl = (bitn >> 2) * 128 + q4 * 32 + lane;
+                const int grp = ((bitn >> 1) & 1) * 8 + cq * 2 + (bitn & 1);  // 16-pixel group within the chunk
+                const int q = atomicAdd(&T.qn, 1);
+                if (q < K3_QCAP) {
+                    T.q[q] = ((uint32_t)grp << 16) | (uint32_t)hl;
+                } else {  // queue full (pathological inputs): the reference's own decision for the whole group, in line
+                    const tc_raw &W = S.raw[k % TC_RAWS];
+                    const float2 hv = R.raw[hl];
+                    int c = 0;
+                    for (int j = grp * K3_GROUP; j < min(T.n, (grp + 1) * K3_GROUP); ++j) {
+                        const float2 dir = W.dir[j];
+                        const uint32_t xy = W.xy[j];
+                        c += pvv_exact_test(dir.x, dir.y, pvv_norm1(dir.x, dir.y), (float)(xy & 0xffffu), (float)(xy >> 16),
+                                            hv.x, hv.y, d.thresh) ? 1 : 0;
                     }
-                    ++q;
+                    if (c) atomicAdd(&R.cnt[hl], c);
                 }
             }
             __syncwarp();
