@@ -116,13 +116,12 @@ struct tc_smem {
     tc_row rows[TC_ROWS];
     tc_stage st[TC_STAGES];
     tc_raw raw[TC_RAWS];
-    uint32_t q2[K3_QCAP];             // phase B entries: (pixel << 16) | hypothesis within the pass
     unsigned long long bar_ab[TC_STAGES], bar_done[TC_STAGES], bar_full[2], bar_empty[2];
     unsigned long long bar_in[TC_RAWS];   // raw inputs of unit k have landed in raw[k % TC_RAWS] (bulk copies: complete_tx)
     long long off[8];                 // ring: pool offset of the image of unit k (slot k & 7), fetched two iterations ahead
     int4 ent[8];                      // ring: chunk-table entry of unit k, fetched three iterations ahead (x = -1: no unit)
     uint32_t tmem;
-    int ext, uext, q2n;
+    int ext, uext;
 };
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
@@ -301,7 +300,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
         tc_bar_init(&S.bar_full[0], 1); tc_bar_init(&S.bar_full[1], 1);
         tc_bar_init(&S.bar_empty[0], TC_VOTER_WARPS); tc_bar_init(&S.bar_empty[1], TC_VOTER_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        S.ext = 0; S.uext = 0; S.q2n = 0;
+        S.ext = 0; S.uext = 0;
     }
     for (int i = tid; i < TC_ROWS * TC_PASS_H; i += TC_THREADS) S.rows[i / TC_PASS_H].cnt[i % TC_PASS_H] = 0;
     if (warp == TC_MMA_WARP) {  // the MMA warp owns the TMEM allocation
@@ -550,25 +549,18 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                         if (!(fabsf(m1) > Tf)) inband |= 2u << (2 * p); else sure += m1 > 0.f;
                     }
                     if (sure) atomicAdd(&R.cnt[hl], sure);
+                    // (B) in line: a unit has a few dozen such tests, spread over a few warps -- a second queue, a barrier and a
+                    // pass of its own cost more than the divergence here (2 800 -> 2 200 cycles of the producers' 5 500 per unit
+                    // at 128 hypotheses, profiles/r02_k_count_tc_timeline.md)
                     while (inband) {
                         const int j = grp * K3_GROUP + 2 * u0 + __ffs(inband) - 1;
                         inband &= inband - 1;
                         if (j >= T.n) continue;  // padded pixels (m = -1e30) only get here when the band is infinite
-                        const int q = atomicAdd(&S.q2n, 1);
-                        if (q < K3_QCAP) S.q2[q] = ((uint32_t)j << 16) | (uint32_t)hl;
-                        else resolve(T, W, hl, j);
+                        resolve(T, W, hl, j);
                     }
                 }
                 pbar();
                 if (ptid == 0) TC_STAMP(u + 2, 15);
-                const int q2 = min(S.q2n, K3_QCAP);
-                for (int idx = ptid; idx < q2; idx += TC_PRODS) {
-                    const uint32_t ent = S.q2[idx];
-                    resolve(T, W, (int)(ent & 0xffffu), (int)(ent >> 16));
-                }
-                pbar();
-                if (ptid == 0) TC_STAMP(u + 2, 16);
-                if (ptid == 0) S.q2n = 0;
                 if (T.last) {  // the row's last unit: one global add per hypothesis, and the buffer is clean for its next row
                     for (int hl = ptid; hl < T.hcount; hl += TC_PRODS) {
                         const int c = R.cnt[hl];
@@ -698,6 +690,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 // ---- pixel constants in the row's frame: FP32 (phase A) and their TF32 split as B rows ----
                 int ext = 0, uext = 0;
                 const int ucx = (int)((uint32_t)e0.w & 0xffffu) - ox, ucy = (int)((uint32_t)e0.w >> 16) - oy;  // the unit's centre
+#pragma unroll 2
                 for (int j = ptid; j < nbn * TC_TILE_PX && !K3_ABL(256) && ptid < TC_PB; j += TC_PB) {
                     px_consts c = never;
                     if (j < n && !K3_ABL(4)) {
@@ -759,7 +752,7 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
         for (int u = 0; u < TC_PROF_UNITS; ++u) {
             printf("%3d:", u);
             for (int q = 0; q < 13; ++q) printf(" %7lld", g_tc_prof[u][q] ? g_tc_prof[u][q] - t0 : -1LL);
-            printf(" | %6lld %6lld | A end %7lld B end %7lld\n", g_tc_prof[u][13], g_tc_prof[u][14], g_tc_prof[u][15] - t0, g_tc_prof[u][16] - t0);
+            printf(" | %6lld %6lld | deferred pass over %7lld\n", g_tc_prof[u][13], g_tc_prof[u][14], g_tc_prof[u][15] - t0);
         }
     }
 #endif
