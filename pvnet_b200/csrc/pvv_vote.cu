@@ -614,17 +614,18 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
     return cudaGetLastError();
 }
 
-// Which kernel counts (measured, profiles/r01_sweep.md): above 256 hypotheses the tensor-pipe kernel (pvv_vote_tc.cuh:
-// tcgen05 tf32 MMA for the two linear forms, CUDA cores for the sign count and the band) is 15-20 % faster than the
-// FP32-pipe kernel; at 128 and 256 the FP32-pipe kernel with 32- / 64-thread CTAs (every thread owns 4 hypotheses, one
-// pass covers 4 * THREADS of them) wins, because a 128-row MMA tile and the per-unit operand staging are not amortised.
-// pvv_debug.k3_variant overrides the choice (n > 0 forces variant n - 1; 0..6: FP32-pipe shapes, 7: tensor pipe, 8 / 9:
-// tensor pipe with 7 / 3 producer warps): a tuning and test knob (tools/k3_variants.py, tests/test_gpu_parity.py).
-// -1: the exact-only kernel.
+// Which kernel counts (measured, profiles/r02_k3_kernel_crossover_by_hn.log, tools/crossover_small.py): above 128 hypotheses
+// the tensor-pipe kernel (pvv_vote_tc.cuh: tcgen05 tf32 MMA for the two linear forms, CUDA cores for the sign count and the
+// band) -- since its producer warps work as two groups side by side it wins from 160 hypotheses on at every batch size (1 - 32
+// images: 25 against 44 us, 189 against 214 us) and is 15 - 25 % faster at 512; at 128 the FP32-pipe kernel with one-warp CTAs
+// (every thread owns 4 hypotheses) is level with it on large batches (142 against 153 us with the pre-pass) and stays.
+// pvv_debug.k3_variant overrides the choice (n > 0 forces variant n - 1; 0..6 and 11..13: FP32-pipe shapes, 7 / 8: tensor
+// pipe, 9: tensor pipe with 3 producer warps, 10: the experimental queue-and-defer pair): a tuning and test knob
+// (tools/k3_variants.py, tests/test_gpu_parity.py).  -1: the exact-only kernel.
 static int pvv_count_variant(const pvv_dims &d, int force_exact, int k3_variant, band_consts *bc)
 {
     if (force_exact || !pvv_band_for(d.thresh, bc)) return -1;
-    int v = k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 ? 2 : d.hn <= 256 ? 1 : 7);
+    int v = k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 ? 2 : 7);
     // the second-generation tensor-pipe kernel indexes hyp / counts with 32 bits in its queue entries
     if (v == 10 && (long long)d.b * d.vn * ((d.hn + 3) / 4 * 4) >= (1LL << 31)) v = 7;
     return v;

@@ -117,6 +117,7 @@ struct tc_smem {
     tc_stage st[TC_STAGES];
     tc_raw raw[TC_RAWS];
     unsigned long long bar_ab[TC_STAGES], bar_done[TC_STAGES], bar_full[2], bar_empty[2];
+    unsigned long long bar_free[TC_STAGES];   // (7 producer warps) the deferred pass of the stage's unit is over: the stage can be rebuilt
     unsigned long long bar_in[TC_RAWS];   // raw inputs of unit k have landed in raw[k % TC_RAWS] (bulk copies: complete_tx)
     long long off[8];                 // ring: pool offset of the image of unit k (slot k & 7), fetched two iterations ahead
     int4 ent[8];                      // ring: chunk-table entry of unit k, fetched three iterations ahead (x = -1: no unit)
@@ -287,6 +288,13 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
 {
     constexpr int TC_PROD_WARPS = PW, TC_PRODS = tc_cfg<PW>::prods, TC_THREADS = tc_cfg<PW>::threads;
     constexpr int TC_REGS_VOTER = tc_cfg<PW>::regs_voter, TC_REGS_OTHER = tc_cfg<PW>::regs_other;
+    // Seven producer warps work as two groups side by side: five build the operands of unit k (four build rows, the fifth's
+    // first lane stages the inputs of unit k + 1), two run the deferred pass of the unit the voters finished last.  One after
+    // the other these took ~3 700 cycles per unit (profiles/r02_k_count_tc_timeline.md), which bounded the kernel below 256
+    // hypotheses; side by side the longer of the two (~2 200) does.
+    constexpr bool SPLIT = PW == 7;
+    constexpr int TC_ROW_WARPS = 5, TC_DEF_WARPS = 2;            // SPLIT only
+    constexpr int TC_ROWG = TC_ROW_WARPS * 32, TC_DEFG = TC_DEF_WARPS * 32;
     extern __shared__ __align__(128) unsigned char tc_smem_raw[];
     tc_smem &S = *reinterpret_cast<tc_smem *>(tc_smem_raw);
     static_assert(K3_GROUP == 16 && PVV_CHUNK_PX == 256 && TC_TILE_PX == 128, "tile / group geometry");
@@ -295,7 +303,11 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
-        for (int i = 0; i < TC_STAGES; ++i) { tc_bar_init(&S.bar_ab[i], TC_PROD_WARPS); tc_bar_init(&S.bar_done[i], TC_VOTER_WARPS); }
+        for (int i = 0; i < TC_STAGES; ++i) {
+            tc_bar_init(&S.bar_ab[i], SPLIT ? TC_ROW_WARPS : TC_PROD_WARPS);
+            tc_bar_init(&S.bar_done[i], TC_VOTER_WARPS);
+            tc_bar_init(&S.bar_free[i], TC_DEF_WARPS);
+        }
         for (int i = 0; i < TC_RAWS; ++i) tc_bar_init(&S.bar_in[i], 1);
         tc_bar_init(&S.bar_full[0], 1); tc_bar_init(&S.bar_full[1], 1);
         tc_bar_init(&S.bar_empty[0], TC_VOTER_WARPS); tc_bar_init(&S.bar_empty[1], TC_VOTER_WARPS);
@@ -496,14 +508,19 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
         } else {
             // ================= producers: operands of unit k, then the deferred passes of unit k - 2 =================
             const int ptid = tid - (TC_VOTERS + 32);
-            auto pbar = [] { asm volatile("bar.sync 1, %0;" ::"n"(TC_PRODS) : "memory"); };
+            // barrier 1: the operand group (all producers when the roles are not split); barrier 2: the deferred-pass group
+            auto pbar = [] { asm volatile("bar.sync 1, %0;" ::"n"(SPLIT ? TC_ROWG : TC_PRODS) : "memory"); };
+            auto dbar = [] { asm volatile("bar.sync 2, %0;" ::"n"(TC_DEFG) : "memory"); };
+            const bool def_role = SPLIT && ptid >= TC_ROWG;           // this thread belongs to the deferred-pass group
+            const int gt = def_role ? ptid - TC_ROWG : ptid;          // thread index within the group that runs a deferred pass
+            constexpr int GN = SPLIT ? TC_DEFG : TC_PRODS;            // ... and that group's size
             // With 7 producer warps the last one does not build operands: its first lane issues the look-ahead loads and the
             // bulk copies of the next unit's inputs (~1500 cycles of one thread: address arithmetic, expect_tx, 3 - 4 bulk
             // copies) while the other six build this unit's rows -- 256 pixels take two rounds with 192 threads as with 224.
             // (Profile of CTA 0, -DPVV_TC_PROF: the staging used to sit on the critical path of thread 0, in front of its share
             // of the rows.)  With 3 producer warps every thread is needed for the rows.
-            constexpr int SPT = PW == 7 ? TC_PRODS - 32 : 0;           // the staging thread
-            constexpr int TC_PB = PW == 7 ? TC_PRODS - 32 : TC_PRODS;  // threads that build operands: ptid < TC_PB
+            constexpr int SPT = SPLIT ? TC_ROWG - 32 : 0;              // the staging thread
+            constexpr int TC_PB = SPLIT ? TC_ROWG - 32 : TC_PRODS;     // threads that build operands: ptid < TC_PB
             unsigned long long amb_local = 0;
             const px_consts never = {0.f, 0.f, -1e30f, 0.f, 0.f, -1e30f};
 
@@ -525,9 +542,9 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 const tc_raw &W = S.raw[u % TC_RAWS];
                 tc_row &R = S.rows[T.row];
                 tc_bar_wait<TC_SLEEP_PROD>(&S.bar_done[s], (u / TC_STAGES) & 1u);
-                if (ptid == 0) TC_STAMP(u + 2, 6);
+                if (gt == 0) TC_STAMP(u + 2, 6);
                 const int qtot = min(T.qn, K3_QCAP) * K3_SUB;
-                for (int idx = ptid; idx < qtot; idx += TC_PRODS) {
+                for (int idx = gt; idx < qtot; idx += GN) {
                     const uint32_t ent = T.q[idx / K3_SUB];
                     constexpr int PAIRS = K3_GROUP / 2 / K3_SUB;
                     const int hl = (int)(ent & 0xffffu), grp = (int)(ent >> 16), u0 = (idx % K3_SUB) * PAIRS;
@@ -559,10 +576,10 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                         resolve(T, W, hl, j);
                     }
                 }
-                pbar();
-                if (ptid == 0) TC_STAMP(u + 2, 15);
+                if (SPLIT) dbar(); else pbar();
+                if (gt == 0) TC_STAMP(u + 2, 15);
                 if (T.last) {  // the row's last unit: one global add per hypothesis, and the buffer is clean for its next row
-                    for (int hl = ptid; hl < T.hcount; hl += TC_PRODS) {
+                    for (int hl = gt; hl < T.hcount; hl += GN) {
                         const int c = R.cnt[hl];
                         PVV_CHECK(T.cnt_row >= 0 && T.cnt_row + hl < (long long)d.b * d.vn * ws.hn_pad && c <= d.max_num + PVV_CHUNK_PX);
                         if (c) { atomicAdd(&ws.counts[T.cnt_row + hl], c); R.cnt[hl] = 0; }
@@ -624,6 +641,18 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 }
                 cp_async_commit();   // (the look-ahead ring of thread 0 still uses cp.async)
             };
+            if (def_role) {
+                // ---- deferred-pass group: unit after unit, as soon as the voters are through with it ----
+                for (uint32_t u = 0;; ++u) {
+                    const uint32_t s = u % TC_STAGES;
+                    tc_bar_wait<TC_SLEEP_PROD>(&S.bar_ab[s], (u / TC_STAGES) & 1u);   // the stage's contents are those of unit u
+                    if (S.st[s].stop) break;
+                    deferred(u);
+                    dbar();   // every thread of the group is through with the stage: it may be rebuilt
+                    if (lane == 0) tc_bar_arrive(&S.bar_free[s]);
+                }
+                if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
+            } else {
             if (ptid == SPT) {
                 for (uint32_t i = 0; i < 3; ++i) fetch_entry(i, i);
                 cp_async_commit();
@@ -647,6 +676,8 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 if (ptid == 0) TC_STAMP(k, 1);
                 e0 = S.ent[k & 7u];
                 const int4 e1 = S.ent[(k + 1) & 7u];
+                // the deferred pass of unit k - 3 is over: stage s, and the raw-input buffer unit k + 1 is staged into, are free
+                if (SPLIT && k >= TC_STAGES) tc_bar_wait<TC_SLEEP_PROD>(&S.bar_free[s], (k / TC_STAGES - 1u) & 1u);
                 if (e0.x < 0) {
                     if (ptid == 0) T.stop = 1;
                     __syncwarp();
@@ -731,16 +762,19 @@ __global__ void __launch_bounds__(tc_cfg<PW>::threads, 1) k_count_tc(pvv_dims d,
                 __syncwarp();
                 if (lane == 0) tc_bar_arrive(&S.bar_ab[s]);
                 if (ptid == 0) TC_STAMP(k, 5);
-                // ---- deferred passes of the unit the voters finished last ----
-                if (k >= 2 && !K3_ABL(512)) deferred(k - 2);
+                // ---- deferred passes of the unit the voters finished last (the other group's job when the roles are split) ----
+                if (!SPLIT && k >= 2 && !K3_ABL(512)) deferred(k - 2);
                 if (ptid == 0) TC_STAMP(k, 7);
                 new_row = next_new_row; rowbuf = next_rowbuf; ci = ci1; rg = rg1;
             }
-            // k units were published (0 .. k-1): finish the deferred passes of the last two
-            if (k >= 2) deferred(k - 2);
-            pbar();
-            if (k >= 1) deferred(k - 1);
-            if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
+            if (!SPLIT) {
+                // k units were published (0 .. k-1): finish the deferred passes of the last two
+                if (k >= 2) deferred(k - 2);
+                pbar();
+                if (k >= 1) deferred(k - 1);
+                if (amb_local) atomicAdd((unsigned long long *)&ws.counters[PVV_CTR_AMB_LO], amb_local);
+            }
+            }
         }
     }
     tc_fence_before();
