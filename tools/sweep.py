@@ -115,7 +115,7 @@ def main():
 
     # ---- configs[4]: sweep foreground fraction x hypotheses x keypoints ----
     fracs = [0.01, 0.10, 0.60] if a.quick else [0.01, 0.03, 0.10, 0.30, 0.60]
-    hns = [128, 2048] if a.quick else [128, 512, 2048]
+    hns = [128, 2048] if a.quick else [128, 256, 512, 2048]
     vns = [9, 17] if a.quick else [9, 13, 17]
     b = 8
     for vn in vns:
