@@ -1,9 +1,11 @@
 // pvv_host.cu -- host-buffer entry points (pvv_v3_host / pvv_cov_host), the library's draw streams materialised
 // (pvv_make_idxs / pvv_make_selection) and the FP32 roofline probe.  Built only on the public C ABI.
 //
-// Host path: the mask is copied to the device; a PINNED vertex tensor is not copied at all -- the scatter kernel
-// of K1 reads the foreground vectors straight out of host memory over PCIe (UVA), so only ~fg/(h*w) of the
-// [b,h,w,vn,2] tensor crosses the bus.  A pageable vertex tensor is staged with one full copy.
+// Host path: pageable inputs are staged with full copies; pinned inputs go through a pipeline of
+// sub-batches -- host worker threads narrow the mask to bytes and measure its rows, the byte mask crosses the bus as one copy,
+// a pull kernel stages the foreground row spans of the vertex tensor in device memory (or, for layouts it does not know and
+// for sparse foreground, the scatter kernel of K1 reads the foreground vectors straight out of host memory over PCIe), and
+// the sub-batch is voted on while the next one is on its way.
 #include <stdlib.h>
 #include <string.h>
 
@@ -79,6 +81,7 @@ struct pinned_stage {
     }
 };
 thread_local pinned_stage t_stage;
+thread_local pinned_stage t_small;   // status words / pixel counts of a host-buffer call
 
 // -DPVV_HOST_TRACE: timeline of a host-buffer call on stderr (development builds only, tools/build_variant.sh)
 #ifdef PVV_HOST_TRACE
@@ -415,7 +418,7 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     cudaStream_t st = (cudaStream_t)j->stream;
     char *base = (char *)j->workspace;
     int64_t h2d = 0, d2h = 0;
-    cudaError_t e;
+    [[maybe_unused]] cudaError_t e = cudaSuccess;
     pvv_job dj = *j;
     dj.workspace_bytes = P.dev_ws;
     dj.mask = base + P.o_mask;
@@ -657,23 +660,27 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
     }
     if ((e = cudaMemcpyAsync(out_host, out_dev, out_bytes, cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
     d2h += (int64_t)out_bytes;
-    int32_t status_host[PVV_HOST_MAX_SUB] = {0};
-    if ((e = cudaMemcpyAsync(status_host, status_dev, sizeof(status_host), cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
-    d2h += (int64_t)sizeof(status_host);
-    if (P.vertex_zero_copy && h2d_bytes) {
-        // account the foreground vectors the scatter kernel pulled over the bus: sum(tn) * vn * 8 bytes
-        int *tn_host = (int *)malloc(sizeof(int) * j->b);
-        if (!tn_host) return PVV_ERR_INVALID;
-        e = cudaMemcpyAsync(tn_host, tn_dev, sizeof(int) * j->b, cudaMemcpyDeviceToHost, st);
-        if (!e) e = cudaStreamSynchronize(st);
+    // status words (and, when some images were gathered in place, their pixel counts for the byte accounting) come back
+    // through a small pinned buffer of the calling thread: asynchronous copies, ONE synchronisation for the whole call
+    // (copies into pageable memory each block the host until the stream has drained)
+    bool any_gathered = false;
+    for (int i = 0; i < j->b; ++i) any_gathered |= gathered[i] != 0;
+    const bool want_tn = P.vertex_zero_copy && h2d_bytes && any_gathered;
+    int32_t *small = (int32_t *)t_small.get(sizeof(int32_t) * (PVV_HOST_MAX_SUB + (size_t)j->b));
+    if (!small) return PVV_ERR_CUDA;
+    int32_t *status_host = small, *tn_host = small + PVV_HOST_MAX_SUB;
+    if ((e = cudaMemcpyAsync(status_host, status_dev, sizeof(int32_t) * PVV_HOST_MAX_SUB, cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
+    d2h += (int64_t)sizeof(int32_t) * PVV_HOST_MAX_SUB;
+    if (want_tn) {
+        if ((e = cudaMemcpyAsync(tn_host, tn_dev, sizeof(int) * j->b, cudaMemcpyDeviceToHost, st))) return PVV_ERR_CUDA;
+        d2h += (int64_t)sizeof(int) * j->b;
+    }
+    if ((e = cudaStreamSynchronize(st))) return PVV_ERR_CUDA;
+    if (want_tn) {
+        // the foreground vectors the scatter kernel pulled over the bus itself: sum(tn) * vn * 8 bytes
         long long sum = 0;
         for (int i = 0; i < j->b; ++i) sum += gathered[i] ? tn_host[i] : 0;
-        free(tn_host);
-        if (e) return PVV_ERR_CUDA;
         h2d += sum * j->vn * 8;
-        d2h += (int64_t)sizeof(int) * j->b;
-    } else {
-        if ((e = cudaStreamSynchronize(st))) return PVV_ERR_CUDA;
     }
     HOST_TRACE(tr, "synchronised");
 #ifdef PVV_HOST_TRACE
