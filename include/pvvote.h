@@ -119,8 +119,10 @@ typedef struct pvv_debug {
     uint64_t *amb_count;  /* [1] number of tests that took the exact path */
     float *stage_ms;      /* HOST pointer [5] or NULL: device time of compaction, hypotheses, counting, finalise and the
                              whole call, from CUDA events on job->stream.  Setting it makes the call synchronise. */
-    int32_t k3_variant;   /* 0: the library picks the inlier-counting kernel; n > 0: force variant n - 1 (tests and tuning:
-                             0..6 FP32-pipe CTA shapes, 7 tensor pipe, 8 / 9 tensor pipe with a fixed builder-warp count) */
+    int32_t k3_variant;   /* 0: the library picks the inlier-counting kernel (FP32-pipe up to 128 hypotheses, tensor pipe
+                             above); n > 0: force variant n - 1 (tests and tuning: 0..6 and 11..13 FP32-pipe CTA shapes,
+                             7 / 8 tensor pipe, 9 tensor pipe with 3 producer warps, 10 the experimental queue-and-defer
+                             pair).  Results are bit-identical for every value. */
     const float *hyp_inject; /* device [b,hn_total,vn,2] or NULL: use these hypotheses instead of intersecting pixel pairs
                              (tests only: places hypotheses on the decision cone, tests/test_gpu_parity.py) */
 } pvv_debug;
