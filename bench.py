@@ -444,7 +444,7 @@ def run_ours(args):
     except Exception:
         pass
     k1_bytes = mask.nbytes + tn_total * VN * 8 + tn_total * (4 + VN * 8) + 2 * (mask.size // 8)  # mask once; bitmask w+r
-    roofline = {"kernel": "k_hypotheses_and_consts + k_count_tc (K3 fused inlier counting, tensor-pipe kernel: hn > 256, raw inputs staged by 1-D TMA bulk copies; the time includes K2, which shares the pre-pass launch)", "bound": "fp32",
+    roofline = {"kernel": "k_hypotheses_and_consts + k_count_tc (K3 fused inlier counting, tensor-pipe kernel: hn > 128, raw inputs staged by 1-D TMA bulk copies; the time includes K2, which shares the pre-pass launch)", "bound": "fp32",
                 "achieved": achieved, "peak": peak,
                 "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
                 "bound_note": "the metric stays SURVEY 8(d)'s: 12 FLOP per test against the FFMA peak.  The shipped kernel takes the two "
