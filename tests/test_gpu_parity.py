@@ -813,8 +813,8 @@ def test_random_cases_vs_reference_cuda_kernels():
 
 
 def test_k3_kernel_variants_agree_with_exact_kernel():
-    """K3 ships two guard-banded kernels and picks by hypothesis count: the FP32-pipe kernel (hn <= 256) and the
-    tensor-pipe kernel (tcgen05 tf32 MMA + TMEM, hn > 256).  `k3_variant` (pvv_debug.k3_variant) forces one; every variant must reproduce the
+    """K3 ships two guard-banded kernels and picks by hypothesis count: the FP32-pipe kernel (hn <= 128) and the
+    tensor-pipe kernel (tcgen05 tf32 MMA + TMEM, hn > 128).  `k3_variant` (pvv_debug.k3_variant) forces one; every variant must reproduce the
     exact-only kernel's counts bit for bit on random ragged shapes (tiny images, partial chunks, hypothesis counts that
     are not multiples of 128, far / on-pixel keypoints, scaled and zero directions), on the adversarial field, and on
     the 4096-hypothesis covariance path (8 passes per chunk in the tensor-pipe kernel)."""
@@ -850,7 +850,9 @@ def test_k3_kernel_variants_agree_with_exact_kernel():
                                        force_exact=True)[1]["counts"].clone() for m, v, hn, th, c in cases]
     mean = pv.ransac_voting_layer_v3(cm, cv, 512, 0.99, seed=1)
     cov_x, dbg_x = pv.estimate_voting_distribution_with_mean(cm, cv, mean, seed=2, return_debug=True, force_exact=True)[1:]
-    for variant in (0, 1, 2, 7, 8, 9, 10):   # 8 / 9: the tensor-pipe kernel with its two fixed producer-warp counts; 10: k_count_tc2
+    # 8 / 9: the tensor-pipe kernel with 7 (two groups) / 3 producer warps; 10: k_count_tc2; 11 - 13: FP32-pipe shapes whose warp
+    # groups share the hypotheses and split the pixels
+    for variant in (0, 1, 2, 7, 8, 9, 10, 11, 12, 13):
         for (m, v, hn, th, c), want in zip(cases, exact):
             got = pv.ransac_voting_layer_v3(m, v, hn, th, seed=c, min_num=5, max_num=10 ** 6, return_debug=True,
                                             k3_variant=variant)[1]
