@@ -199,7 +199,7 @@ size_t pvv_workspace_bytes_host(const pvv_job *job);
  * Host worker threads of the host-buffer entry points.  They walk a contiguous mask piece by piece: a wide (int64 / int32 /
  * float32) mask is narrowed to one byte per pixel before it crosses PCIe (AVX-512 where the CPU has it; 8x fewer bytes for
  * the int64 mask torch.argmax produces), and the foreground extent of the rows is measured, which decides between the span
- * pull and the per-pixel gather.  n < 0 (default): half the hardware threads, at most 16; n = 0: no host preparation, the
+ * pull and the per-pixel gather.  n < 0 (default): three quarters of the hardware threads, at most 16; n = 0: no host preparation, the
  * mask is copied as it is and the foreground is gathered pixel by pixel; n > 0: that many.  The workers are parked threads
  * of the calling thread (created on its first call).  Measured on the B200 boxes (16 / 32 hardware threads): worth it from
  * 3 workers per rank upwards; a launcher that runs several ranks per box should divide the hardware threads between them

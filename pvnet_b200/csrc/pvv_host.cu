@@ -519,10 +519,10 @@ int run_host(const pvv_job *j, bool cov, float confidence, int max_iter, const f
             }
         };
         unsigned hw = std::thread::hardware_concurrency();
-#ifndef PVV_HOST_THREADS_DIV
-#define PVV_HOST_THREADS_DIV 2   // measured on the 16-thread host of a B200 box: 8 workers beat 12 and 4 (profiles/r02_e2e_host_threads.log)
-#endif
-        int nthreads = workers_cfg > 0 ? workers_cfg : (int)(hw / PVV_HOST_THREADS_DIV);
+        // default: three quarters of the hardware threads (the calling thread and the driver's threads need the rest).
+        // Measured on the 16-thread host of a B200 box with the AVX-512 narrowing (bench.py e2e, two runs each): 8 workers
+        // 24.7 - 24.8 k images/s, 10: 25.0 k, 12: 25.0 - 25.2 k, 14: slower (1.39 against 1.28 ms per call)
+        int nthreads = workers_cfg > 0 ? workers_cfg : (int)(hw * 3 / 4);
         nthreads = nthreads < 1 ? 1 : nthreads > 16 ? 16 : nthreads;
         if ((size_t)nthreads > npieces) nthreads = (int)npieces;
         HOST_TRACE(tr, "inputs enqueued");
