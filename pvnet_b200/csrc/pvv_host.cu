@@ -226,13 +226,18 @@ public:
         bool waited = false;
         job_guard(worker_pool &pool, int n, const std::function<void()> *f) : p(pool)
         {
-            std::lock_guard<std::mutex> lk(p.m);
-            while ((int)p.th.size() < n) {
-                const int id = (int)p.th.size();
-                p.th.emplace_back([&pool, id] { pool.loop(id); });
+            {
+                std::lock_guard<std::mutex> lk(p.m);
+                while ((int)p.th.size() < n) {
+                    const int id = (int)p.th.size();
+                    try { p.th.emplace_back([&pool, id] { pool.loop(id); }); }
+                    catch (...) { break; }   // the system has no more threads: work with those there are
+                }
+                n = std::min(n, (int)p.th.size());
+                p.job = f; p.njob = n; p.active = n; ++p.gen;
+                p.cv.notify_all();
             }
-            p.job = f; p.njob = n; p.active = n; ++p.gen;
-            p.cv.notify_all();
+            if (n == 0) (*f)();   // no worker at all: the calling thread does the job itself, before it goes on
         }
         void wait()
         {
