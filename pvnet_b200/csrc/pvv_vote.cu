@@ -618,14 +618,21 @@ static cudaError_t launch_count_t(const pvv_dims &d, const pvv_ws &ws, const ban
 // the tensor-pipe kernel (pvv_vote_tc.cuh: tcgen05 tf32 MMA for the two linear forms, CUDA cores for the sign count and the
 // band) -- since its producer warps work as two groups side by side it wins from 160 hypotheses on at every batch size (1 - 32
 // images: 25 against 44 us, 189 against 214 us) and is 15 - 25 % faster at 512; at 128 the FP32-pipe kernel with one-warp CTAs
-// (every thread owns 4 hypotheses) is level with it on large batches (142 against 153 us with the pre-pass) and stays.
+// (every thread owns 4 hypotheses) is level with it on large batches (142 against 153 us with the pre-pass) and stays for
+// those; small jobs of any hypothesis count go to the tensor-pipe kernel (see pvv_count_variant).
 // pvv_debug.k3_variant overrides the choice (n > 0 forces variant n - 1; 0..6 and 11..13: FP32-pipe shapes, 7 / 8: tensor
 // pipe, 9: tensor pipe with 3 producer warps, 10: the experimental queue-and-defer pair): a tuning and test knob
 // (tools/k3_variants.py, tests/test_gpu_parity.py).  -1: the exact-only kernel.
-static int pvv_count_variant(const pvv_dims &d, int force_exact, int k3_variant, band_consts *bc)
+static int pvv_count_variant(const pvv_dims &d, const pvv_ws &ws, int force_exact, int k3_variant, band_consts *bc)
 {
     if (force_exact || !pvv_band_for(d.thresh, bc)) return -1;
-    int v = k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 ? 2 : 7);
+    // Up to 128 hypotheses the choice goes by job size.  The host only knows an upper bound of the pooled pixels (the pool's
+    // capacity), hence of the units of work: where even that bound is small the tensor-pipe kernel wins (b = 1: 24 against
+    // 35 us for K2 + K3; the reference's shipped setting, 128 hypotheses and max_num = 100, at b = 32: 20 against 25 us); on
+    // large batches with full pools the one-warp FP32-pipe CTAs do (b = 32: 142 against 153 us).  tools/crossover_tiny.py,
+    // tools/crossover_small.py; the crossing is near 16 images of configs[1] = a bound of ~17 000 units.
+    const long long units_bound = (ws.cap / PVV_CHUNK_PX + d.b) * d.vn;
+    int v = k3_variant > 0 ? k3_variant - 1 : (d.hn <= 128 && units_bound > 9000 ? 2 : 7);
     // the second-generation tensor-pipe kernel indexes hyp / counts with 32 bits in its queue entries
     if (v == 10 && (long long)d.b * d.vn * ((d.hn + 3) / 4 * 4) >= (1LL << 31)) v = 7;
     return v;
@@ -638,7 +645,7 @@ cudaError_t pvv_launch_hypotheses(const pvv_dims &d, const int32_t *idxs, const 
 {
     band_consts bc = {};
     const int hyp_bx = (d.vn * d.hn + 255) / 256;
-    const int cv = pvv_count_variant(d, force_exact, k3_variant, &bc);
+    const int cv = pvv_count_variant(d, ws, force_exact, k3_variant, &bc);
     if (cv >= 7 && cv <= 10) {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
@@ -704,7 +711,7 @@ cudaError_t pvv_launch_count(const pvv_dims &d, const pvv_ws &ws, int force_exac
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     band_consts bc = {};
-    const int variant = pvv_count_variant(d, force_exact, k3_variant, &bc);
+    const int variant = pvv_count_variant(d, ws, force_exact, k3_variant, &bc);
     const bool fast = variant >= 0;
     cudaError_t e;
     if (!fast) {
