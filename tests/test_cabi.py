@@ -230,3 +230,25 @@ def test_logits_job_and_eval_wrapper_surface(built_lib):
     sig = inspect.signature(EvalWrapper.forward)
     assert [(n, p.default) for n, p in list(sig.parameters.items())[1:]] == [
         ("seg_pred", inspect._empty), ("vertex_pred", inspect._empty), ("use_argmax", True), ("use_uncertainty", False)]
+
+
+def test_host_worker_policy_of_the_python_mirror():
+    """pvnet_b200/_lib.py divides the host's hardware threads between the ranks of one box (LOCAL_WORLD_SIZE) and lets
+    PVV_HOST_WORKERS override; pvv_set_host_workers returns the previous setting (no GPU needed)."""
+    import subprocess
+    import sys
+    code = ("import os; from pvnet_b200 import _lib; L = _lib.lib(); print(L.pvv_set_host_workers(-1), os.cpu_count())")
+
+    def run(env):
+        e = {k: v for k, v in os.environ.items() if k not in ("LOCAL_WORLD_SIZE", "PVV_HOST_WORKERS")}
+        e.update(env)
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=ROOT, env=e, check=True).stdout.split()
+        return int(out[0]), int(out[1])
+
+    prev, ncpu = run({})
+    assert prev == -1                                    # one rank: the library's own default
+    assert run({"PVV_HOST_WORKERS": "5"})[0] == 5
+    assert run({"PVV_HOST_WORKERS": "0", "LOCAL_WORLD_SIZE": "2"})[0] == 0
+    for ranks in (2, 4, 8, 64):
+        share = ncpu // ranks
+        assert run({"LOCAL_WORLD_SIZE": str(ranks)})[0] == (min(share, 16) if share >= 3 else 0)
